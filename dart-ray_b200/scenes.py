@@ -1,0 +1,413 @@
+"""Synthetic inputs for the ray-tracing path: adaptive Cartesian grids + opacities + sources.
+
+The reference ships no grid files, so the bench/test inputs are generated
+here.  The builder follows the structure of the reference grid programs
+(create_adap_grid_trustI.f90:157-395: level-by-level subdivision, children appended as contiguous
+blocks of base**3 cells with x fastest, 2:1 face balance through `subdivide_neighbour_cells`,
+`cindex` packing at :344-348) so that the arrays have exactly the invariants the hot path relies
+on.  Grid creation itself is OUT of the hot-path scope; this is harness code.
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+
+# single-precision pi of the reference (smooth_grid_routines.f90:311-315)
+HALFPI = float(np.float32(np.arcsin(np.float32(1.0))))
+PI = 2 * HALFPI
+PARSEC = float(np.float32(3.08567758e16))
+CSPEED = float(np.float32(2.99792458e8))
+
+
+def _powi(x: float, n: int) -> float:
+    """libgcc __powidf2 (what gfortran emits for real**integer)."""
+    m = abs(n)
+    r = x if (m & 1) else 1.0
+    m >>= 1
+    while m:
+        x = x * x
+        if m & 1:
+            r = r * x
+        m >>= 1
+    return r if n >= 0 else 1.0 / r
+
+
+@dataclass
+class Grid:
+    modelsize: float
+    base: tuple
+    max_lvl: int
+    cchild: np.ndarray
+    lvl: np.ndarray
+    cindex: np.ndarray
+    ccoord: np.ndarray  # (N,3) C order == Fortran (3,N)
+    csize: np.ndarray
+    dens: np.ndarray  # extinction coefficient at the reference wavelength [1/pc]
+    dens_stars: np.ndarray
+    csize_arr: np.ndarray = field(default=None)
+    carea_arr: np.ndarray = field(default=None)
+    cvol_arr: np.ndarray = field(default=None)
+
+    @property
+    def ncell(self):
+        return int(self.cchild.shape[0])
+
+    @property
+    def leaves(self):
+        return np.nonzero(self.cchild == -1)[0]
+
+
+class _Builder:
+    """Restatement of the grid-creation loop (create_adap_grid_trustI.f90:157-395 and the
+    tree helpers of smooth_grid_routines.f90:608-852)."""
+
+    def __init__(self, modelsize, base, max_lvl, calc_dens, subdivision, max_ncell=4_000_000):
+        self.modelsize = float(modelsize)
+        self.base = (int(base[0]), int(base[1]))
+        self.max_lvl = int(max_lvl)
+        self.calc_dens = calc_dens
+        self.subdivision = subdivision
+        self.max_ncell = max_ncell
+        self.baseinv = (1.0 / self.base[0], 1.0 / self.base[1])
+        self.basediv = []
+        for b in self.base:  # set_base smooth_grid_routines.f90:622-649
+            j = 0
+            while not (b ** 3 < 2 ** j):
+                j += 1
+            self.basediv.append(2 ** j)
+        self.basemask = [d - 1 for d in self.basediv]
+        self.cchild = [-1]
+        self.lvl = [0]
+        self.cindex = [0]
+        self.ccoord = [(0.0, 0.0, 0.0)]
+        self.csize = [self.modelsize]
+        d, s = calc_dens(0.0, 0.0, 0.0, self.modelsize)
+        self.dens = [d]
+        self.dens_stars = [s]
+
+    def cellsize(self, clvl):  # calc_cellsize :608-619
+        if clvl > 0:
+            return self.modelsize * self.baseinv[0] * _powi(self.baseinv[1], clvl - 1)
+        return self.modelsize
+
+    def cindex_to_ccindd(self, nc, clvl):  # :793-813
+        cc = [[0, 0, 0] for _ in range(self.max_lvl + 1)]
+        ci = self.cindex[nc]
+        for i in range(1, clvl + 1):
+            if i > 1:
+                ib = 1
+                j = ((ci // (self.basediv[0] * self.basediv[1] ** (i - 2))) & self.basemask[1]) - 1
+            else:
+                ib = 0
+                j = (ci & self.basemask[0]) - 1
+            b = self.base[ib]
+            cc[i] = [j % b, (j // b) % b, (j // (b * b)) % b]
+        return cc
+
+    def ccindd_to_cc(self, cc):  # :820-852
+        l = 1
+        for i in range(1, self.max_lvl + 1):
+            b = self.base[1 if i > 1 else 0]
+            k = (cc[i][2] * b + cc[i][1]) * b + cc[i][0] + 1
+            l = l + k - 1
+            if self.cchild[l] == -1:
+                return l, i
+            l = self.cchild[l]
+        return -1, -1
+
+    def find_neighbour(self, nc, isel, inc):  # find_neighbours :656-743
+        clvl = self.lvl[nc]
+        cc = self.cindex_to_ccindd(nc, clvl)
+        for a in range(3):
+            if a == isel:
+                k = inc
+                for j in range(clvl, 0, -1):
+                    b = self.base[1 if j > 1 else 0]
+                    v = cc[j][a] + k
+                    if v >= b:
+                        v = 0
+                    elif v < 0:
+                        v = b - 1
+                    else:
+                        k = 0
+                    cc[j][a] = v
+                if k != 0:
+                    return -1
+                for j in range(clvl + 1, self.max_lvl + 1):
+                    b = self.base[1 if j > 1 else 0]
+                    cc[j][a] = 0 if inc == 1 else b - 1
+            else:
+                bcoord = 0.5 * self.cellsize(clvl)
+                for j in range(clvl + 1, self.max_lvl + 1):
+                    cs = self.cellsize(j)
+                    cc[j][a] = int(math.floor(bcoord / cs))
+                    bcoord = math.fmod(bcoord, cs)
+        cell, _ = self.ccindd_to_cc(cc)
+        return cell
+
+    def subdivide_cell(self, cc, nlevel_cc):  # :318-395
+        self.cchild[cc] = len(self.cchild)
+        ib = 1 if nlevel_cc > 0 else 0
+        b = self.base[ib]
+        if len(self.cchild) + b ** 3 > self.max_ncell:
+            raise RuntimeError("too many cells")
+        cellsize = self.cellsize(nlevel_cc + 1)
+        x0, y0, z0 = self.ccoord[cc]
+        par = (x0, y0, z0)
+        for iz in range(b):
+            for iy in range(b):
+                for ix in range(b):
+                    code = (iz * b + iy) * b + ix + 1
+                    if nlevel_cc > 0:
+                        ci = self.cindex[cc] | (code * self.basediv[0] * self.basediv[1] ** (nlevel_cc - 1))
+                    else:
+                        ci = self.cindex[cc] | code
+                    ii = (ix, iy, iz)
+                    if b % 2 == 1:
+                        pos = tuple(par[j] + cellsize * float(ii[j] - b // 2) for j in range(3))
+                    else:
+                        pos = tuple(par[j] + cellsize * float(ii[j] - b // 2 + 0.5) for j in range(3))
+                    d, s = self.calc_dens(pos[0], pos[1], pos[2], cellsize)
+                    self.cindex.append(ci)
+                    self.csize.append(cellsize)
+                    self.lvl.append(nlevel_cc + 1)
+                    self.ccoord.append(pos)
+                    self.dens.append(d)
+                    self.dens_stars.append(s)
+                    self.cchild.append(-1)
+
+    def subdivide_neighbours(self, ncurr, nlevel):  # :287-316 + check_level_jump :774-787
+        for isel in range(3):
+            for inc in (1, -1):
+                cc = self.find_neighbour(ncurr, isel, inc)
+                if cc < 0:
+                    continue
+                lc, ln = self.lvl[cc], self.lvl[ncurr]
+                jump = (ln == nlevel and ln > lc) or (ln < nlevel and ln > lc + 1)
+                if jump:
+                    self.subdivide_cell(cc, lc)
+
+    def run(self):  # subdivision_loop :157-283
+        nlevel = 0
+        nstart = [0, 1]
+        while True:
+            for ncurr in range(nstart[nlevel], nstart[nlevel + 1]):
+                x, y, z = self.ccoord[ncurr]
+                cellsize = self.cellsize(nlevel)
+                user = nlevel < self.max_lvl and self.subdivision(x, y, z, cellsize, nlevel, self.dens[ncurr], self.dens_stars[ncurr])
+                if user or self.lvl[ncurr] < nlevel:
+                    if self.lvl[ncurr] > 1:
+                        self.subdivide_neighbours(ncurr, nlevel)
+                    if self.lvl[ncurr] == nlevel and self.cchild[ncurr] == -1:
+                        self.subdivide_cell(ncurr, nlevel)
+            nlevel += 1
+            nstart.append(len(self.cchild))
+            if nlevel < self.max_lvl:
+                continue
+            break
+        a, b = nstart[nlevel], nstart[nlevel + 1]
+        while True:
+            for ncurr in range(a, b):
+                if self.lvl[ncurr] < nlevel and self.lvl[ncurr] > 1:
+                    self.subdivide_neighbours(ncurr, nlevel)
+            a, b = b, len(self.cchild)
+            if b - a > 0:
+                continue
+            break
+        return self.finish()
+
+    def finish(self) -> Grid:
+        g = Grid(
+            modelsize=self.modelsize, base=self.base, max_lvl=self.max_lvl,
+            cchild=np.asarray(self.cchild, dtype=np.int32), lvl=np.asarray(self.lvl, dtype=np.int32),
+            cindex=np.asarray(self.cindex, dtype=np.int64),
+            ccoord=np.ascontiguousarray(np.asarray(self.ccoord, dtype=np.float64)),
+            csize=np.asarray(self.csize, dtype=np.float64), dens=np.asarray(self.dens, dtype=np.float64),
+            dens_stars=np.asarray(self.dens_stars, dtype=np.float64))
+        # make_csize_arr io_routines.f90:669-696
+        cs = [self.modelsize]
+        for i in range(1, self.max_lvl + 1):
+            cs.append(self.modelsize * (self.baseinv[0] * _powi(self.baseinv[1], i - 1)))
+        g.csize_arr = np.asarray(cs, dtype=np.float64)
+        g.carea_arr = g.csize_arr * g.csize_arr
+        g.cvol_arr = g.csize_arr * g.csize_arr * g.csize_arr
+        return g
+
+
+def build_grid(modelsize, base, max_lvl, calc_dens, subdivision, max_ncell=4_000_000) -> Grid:
+    return _Builder(modelsize, base, max_lvl, calc_dens, subdivision, max_ncell).run()
+
+
+# --------------------------------------------------------------------------------------
+# per-wavelength scattering resolution: set_npix_arr rt_routines.f90:5235-5315
+# --------------------------------------------------------------------------------------
+def set_kp_sca(gsca, kp_sca_max):
+    nmin = 5
+    g_th = float(np.float32(2) * np.float32(1e-3))
+    kp = np.zeros(len(gsca), dtype=np.int32)
+    for i, gg in enumerate(gsca):
+        g = abs(float(gg))
+        if g < g_th:
+            kp[i] = -1
+            continue
+        pmax = (1 - g ** 2) / (1 + g ** 2 - 2 * g) ** 1.5
+        pmin = (1 - g ** 2) / (1 + g ** 2 + 2 * g) ** 1.5
+        cos_hm = ((2 * (1 - g ** 2) / (pmax + pmin)) ** float(np.float32(2.0) / np.float32(3.0)) - (1 + g ** 2)) / (-2 * g)
+        fwhm = 2 * math.acos(cos_hm)
+        delta_min = fwhm / nmin
+        k_min = int(1 / (2 * math.log10(2.0)) * math.log10(4 * PI / (12 * delta_min ** 2)))
+        kp[i] = min(k_min, kp_sca_max)
+    return kp
+
+
+@dataclass
+class Scene:
+    name: str
+    grid: Grid
+    lambda_um: np.ndarray
+    dens_arr: np.ndarray      # (N,L) C order == Fortran dens_arr(L,N)
+    ksca_norm: np.ndarray
+    gsca: np.ndarray
+    kp_sca: np.ndarray
+    dir_i_out: np.ndarray     # (2,ndir) C order == Fortran dir_i_out(ndir,2)
+    lumcell: np.ndarray       # (N,L)
+    ccoord_p_src: np.ndarray  # (S,3)
+    lum_p_src: np.ndarray     # (S,L)
+    src_cell: np.ndarray      # (N) int32, -1 = none
+    cell_src: np.ndarray      # (S)
+    bm_par: int = 5
+    bm_par_sca: int = 5
+    bm_par_max: int = 200
+    rad_lim: float = 0.1
+    accuracy: float = 0.1
+    conv_en_lim: float = 0.01
+    wall_on: tuple = (0, 0, 0)
+    wall_coord: tuple = (0.0, 0.0, 0.0, 0.0, 0.0, 0.0)  # model units (after set_walls)
+    ccoord_obs: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+
+    @property
+    def lnum(self):
+        return int(self.dens_arr.shape[1])
+
+    @property
+    def ndir(self):
+        return int(self.dir_i_out.shape[1])
+
+    @property
+    def nsrc(self):
+        return int(self.ccoord_p_src.shape[0])
+
+    @property
+    def npix_hp(self):
+        return np.where(self.kp_sca < 0, 1, 12 * 4 ** np.maximum(self.kp_sca, 0)).astype(np.int32)
+
+    @property
+    def npix(self):
+        return (self.npix_hp + self.ndir).astype(np.int32)
+
+    def en_lim(self):
+        """set_en_lim rt_routines.f90:3137-3158"""
+        tot_sources = int((self.grid.cchild == -1).sum()) + self.nsrc
+        return self.accuracy / (tot_sources * 0.25)
+
+    def cs(self):
+        return CSPEED / PARSEC  # set_units rt_routines.f90:5192
+
+
+def prepare_p_src(grid: Grid, pos):
+    """prepare_p_src + fix_ccoord_p_src rt_routines.f90:535-601"""
+    pos = np.array(pos, dtype=np.float64).reshape(-1, 3).copy()
+    tol_p = float(np.float32(1e-6))
+    src_cell = np.full(grid.ncell, -1, dtype=np.int32)
+    cell_src = np.full(pos.shape[0], -1, dtype=np.int32)
+    leaves = grid.leaves
+    for i in range(pos.shape[0]):
+        rel = pos[i][None, :] - grid.ccoord[leaves]
+        inside = (np.abs(rel) < (1.0 + tol_p) * grid.csize[leaves][:, None] / 2.0).all(axis=1)
+        idx = np.nonzero(inside)[0]
+        if len(idx) == 0:
+            raise RuntimeError("host cell not found")
+        j = int(leaves[idx[0]])
+        src_cell[j] = i
+        cell_src[i] = j
+        r = pos[i] - grid.ccoord[j]
+        cs = grid.csize[j]
+        for a in range(3):
+            if abs(r[a]) >= cs / 2.0:
+                pos[i, a] += -tol_p * cs if r[a] > 0 else tol_p * cs
+    return pos, src_cell, cell_src
+
+
+def _load_table(name):
+    with open(os.path.join(_DATA, name + ".json")) as f:
+        return json.load(f)
+
+
+def _cache_path(tag):
+    d = os.environ.get("DARTRAY_CACHE", "/tmp/dartray_b200_cache")
+    os.makedirs(d, exist_ok=True)
+    return os.path.join(d, tag + ".npz")
+
+
+def _grid_cached(tag, make):
+    p = _cache_path(tag)
+    if os.path.exists(p):
+        z = np.load(p)
+        return Grid(modelsize=float(z["modelsize"]), base=tuple(int(x) for x in z["base"]), max_lvl=int(z["max_lvl"]),
+                    cchild=z["cchild"], lvl=z["lvl"], cindex=z["cindex"], ccoord=z["ccoord"], csize=z["csize"],
+                    dens=z["dens"], dens_stars=z["dens_stars"], csize_arr=z["csize_arr"], carea_arr=z["carea_arr"],
+                    cvol_arr=z["cvol_arr"])
+    g = make()
+    np.savez(p, modelsize=g.modelsize, base=np.asarray(g.base), max_lvl=g.max_lvl, cchild=g.cchild, lvl=g.lvl,
+             cindex=g.cindex, ccoord=g.ccoord, csize=g.csize, dens=g.dens, dens_stars=g.dens_stars,
+             csize_arr=g.csize_arr, carea_arr=g.carea_arr, cvol_arr=g.cvol_arr)
+    return g
+
+
+def trusti_grid(tau_z=0.01, base=(10, 2), max_lvl=4, min_lvl=1, modelsize=10.0) -> Grid:
+    """TRUST-I slab grid: create_adap_grid_trustI.f90:56-100 + user_routines_trustI.f90:167-221
+    (slab x,y in [-5,5], z in [-5,-2]; `subdivision` 'standard' with min_lvl_in = 0)."""
+    z0, z1 = -5.0, -2.0
+    ndust = tau_z / 3.0
+
+    def calc_dens(x, y, z, cs):
+        inside = (-5.0 <= x <= 5.0) and (-5.0 <= y <= 5.0) and (z0 <= z <= z1)
+        return (ndust if inside else 0.0), 0.0
+
+    def crit(x, y, z, cs, nlevel, dens, dens_stars):
+        return (abs(z + cs / 2.0 - z1) / abs(z1) < float(np.float32(1e-5))) or (nlevel < min_lvl)
+
+    tag = f"trusti_t{tau_z}_b{base[0]}_{base[1]}_l{max_lvl}_m{min_lvl}"
+    return _grid_cached(tag, lambda: build_grid(modelsize, base, max_lvl, calc_dens, crit))
+
+
+def trusti_scene(tau_z=0.01, base=(10, 2), max_lvl=4, lnum=None, kp_sca_max=1, name="trustI") -> Scene:
+    """C1: TRUSTI_GRIDS/input_trustI_tau0.01_LD.in — 1 point source at (0,0,4), 7 directions."""
+    g = trusti_grid(tau_z, base, max_lvl)
+    t = _load_table("trusti")
+    L = len(t["lambda_um"]) if lnum is None else lnum
+    sel = np.arange(len(t["lambda_um"]))
+    if lnum is not None:  # sub-sample wavelengths evenly (small test cases)
+        sel = np.unique(np.linspace(0, len(t["lambda_um"]) - 1, lnum).round().astype(int))
+        L = len(sel)
+    kscale = np.asarray(t["kext_scale"])[sel]
+    dens_arr = np.ascontiguousarray(g.dens[:, None] * kscale[None, :])
+    gsca = np.asarray(t["gsca"])[sel]
+    theta = np.arange(7) * (math.pi / 6)
+    theta = np.array([float("%.6g" % v) for v in theta])  # the file stores 6 significant digits
+    dir_i_out = np.ascontiguousarray(np.stack([theta, np.zeros(7)]))
+    pos, src_cell, cell_src = prepare_p_src(g, [[0.0, 0.0, 4.0]])
+    ms = g.modelsize
+    return Scene(name=name, grid=g, lambda_um=np.asarray(t["lambda_um"])[sel], dens_arr=dens_arr,
+                 ksca_norm=np.asarray(t["ksca_norm"])[sel], gsca=gsca, kp_sca=set_kp_sca(gsca, kp_sca_max),
+                 dir_i_out=dir_i_out, lumcell=np.zeros((g.ncell, L)), ccoord_p_src=pos,
+                 lum_p_src=np.ascontiguousarray(np.asarray(t["lum_p_src"])[sel][None, :]),
+                 src_cell=src_cell, cell_src=cell_src, bm_par=10, bm_par_sca=5, bm_par_max=200, rad_lim=0.1,
+                 accuracy=0.1, conv_en_lim=0.01, wall_on=(0, 0, 1),
+                 wall_coord=(0.0, 0.0, 0.0, 0.0, 0.0 * ms - ms / 2.0, 0.3 * ms - ms / 2.0))

@@ -1,0 +1,166 @@
+/* dartray_engine.h — C ABI of the B200 ray-tracing engine that replaces the
+ * DART-Ray hot path.
+ *
+ * The reference has no FFI: the path sits behind four argument-less Fortran
+ * procedures whose state is module variables.  Each entry point below names the
+ * reference procedure (file:line under /root/reference) it replaces.  All
+ * arrays are caller-owned, column-major exactly as the Fortran arrays
+ * (first index fastest), 0-based cell/wavelength/pixel ids, fp64 reals,
+ * int32 integers except `cindex` (int64).
+ *
+ *   dre_run_pass   <- rt_loop            rt_routines.f90:985-1058 (+ main_dir_loop
+ *                                        :1343-1467, ray_tracing :1618-1857,
+ *                                        deposit :2362-2557, ray_list.f90)
+ *   dre_run_iobs   <- rt_loop_iobs       rt_routines.f90:1470-1603
+ *   dre_allreduce  <- rt_mpi + reduce_*  io_routines.f90:3667-3881
+ *   dre_prepare_scatt <- rt_prepare(rtt_scatt) + calc_total_luminosity_sca
+ *                                        dartray_hub.f90:432-457, rt_routines.f90:663-758
+ *
+ * Return value: 0 on success, non-zero on error (message via dre_last_error);
+ * the Fortran wrapper calls stop_prc (smooth_grid_routines.f90:869) on non-zero.
+ * Not re-entrant; one engine per GPU / MPI rank; call from the master thread
+ * outside any OpenMP region.
+ */
+#ifndef DARTRAY_ENGINE_H
+#define DARTRAY_ENGINE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* rt_type ids, rt_routines.f90:193-231 */
+enum {
+  DRE_RTT_PRECALC_CELL   = 1,
+  DRE_RTT_PRECALC_SRC    = 2,
+  DRE_RTT_DIR_CELL       = 5,
+  DRE_RTT_I_OBS_DIR_CELL = 6,
+  DRE_RTT_DIR_SRC        = 7,
+  DRE_RTT_I_OBS_DIR_SRC  = 8,
+  DRE_RTT_SCATT          = 10,
+  DRE_RTT_I_OBS          = 11
+};
+
+#define DRE_NCCL_ID_BYTES 128
+
+typedef struct dre_engine dre_engine;
+
+/* Scalars of the path (module variables of rt_routines.f90). */
+typedef struct dre_params {
+  int32_t bm_par;        /* rt_routines.f90:16 (caller passes bm_par_sca during scattering, dartray_hub.f90:442) */
+  int32_t bm_par_max;    /* :20 */
+  int32_t pabs_max;      /* :22, = int(10*modelsize) io_routines.f90:678 */
+  int32_t print_psel_av; /* :268 */
+  double  rad_lim;       /* :24 */
+  double  en_lim;        /* :26, set_en_lim :3137 */
+  double  cs;            /* :121, set_units :5192 */
+  double  modelsize;     /* smooth_grid_routines.f90 */
+  int32_t wall_on[3];    /* x_wall_on.. rt_routines.f90:499-515 */
+  int32_t reserved0;
+  double  wall_coord[6]; /* x(1:2), y(1:2), z(1:2) in model units (after set_walls :2600) */
+} dre_params;
+
+/* Event counters of one pass (the roofline is computed from these). */
+typedef struct dre_counters {
+  int64_t sources;        /* sources processed (leaf, luminous) */
+  int64_t rays;           /* ray_tracing calls */
+  int64_t intersections;  /* iterations of the main loop rt_routines.f90:1689 */
+  int64_t deposits;       /* intersections reaching :2445 / :2499 */
+  int64_t beam_tests;     /* intersections entering the too-coarse branch :2473 */
+  int64_t splits;         /* rays sent to the high list */
+  int64_t merges;         /* rays sent to the low list */
+  int64_t sca_elems;      /* scaspe elements updated (sum of P(lambda) over deposits) */
+  int64_t active_lambda;  /* sum over deposits+beam tests of active wavelengths */
+  int64_t steps;          /* resolution steps executed (wavefront launches) */
+  double  kernel_ms;      /* device time of the ray-march kernel(s), CUDA events */
+  double  pass_ms;        /* device time of the whole pass */
+  uint64_t isect_hash;    /* order-independent hash of (unit, cell, isel, psel bits) */
+} dre_counters;
+
+/* One recorded intersection (debug/parity mode, dre_set_record). */
+typedef struct dre_isect {
+  int32_t unit;    /* source_ordinal*48 + sector (i_obs passes: source_ordinal*ndir + j) */
+  int32_t step;    /* resolution step within the unit's sector loop */
+  int32_t ray;     /* ordinal of the ray within (unit, step), reference processing order */
+  int32_t k;       /* intersection ordinal along the ray */
+  int32_t cell;    /* cc */
+  int32_t isel;    /* 1,2,3 */
+  double  psel;
+} dre_isect;
+
+/* ---- lifetime ---------------------------------------------------------- */
+int  dre_get_unique_id(void* id128);  /* ncclGetUniqueId, rank 0 only; initialize_mpi io_routines.f90:3610 */
+int  dre_create(dre_engine** out, int device, int rank, int nranks, const void* nccl_id128);
+void dre_destroy(dre_engine*);
+const char* dre_last_error(const dre_engine*);
+
+/* ---- static inputs (copied to HBM) -------------------------------------- */
+/* grid arrays of smooth_grid_routines.f90:41-70, csize_arr/carea_arr/cvol_arr io_routines.f90:669-696 */
+int dre_set_grid(dre_engine*, int32_t tot_ncell, int32_t max_lvl, const int32_t base[2],
+                 const int32_t* cchild, const int32_t* lvl, const int64_t* cindex,
+                 const double* ccoord /*(3,N)*/, const double* csize /*(N)*/,
+                 const double* csize_arr /*(0:max_lvl)*/, const double* carea_arr, const double* cvol_arr);
+/* dens_arr smooth_grid_routines.f90:62; ksca_arr_norm/gsca_arr slices at i0 (set_i_opacity_arrays
+ * rt_routines.f90:5074); kp_sca_arr rt_routines.f90:185 (-1 = isotropic); dir_i_out (ndir,2) */
+int dre_set_opacity(dre_engine*, int32_t lnum, const double* dens_arr /*(L,N)*/,
+                    const double* ksca_arr_norm /*(L)*/, const double* gsca_arr /*(L)*/,
+                    const int32_t* kp_sca_arr /*(L)*/, int32_t tot_ndir_scaspe,
+                    const double* dir_i_out /*(ndir,2): theta col, phi col*/);
+/* lumcell :188, point sources :94,:167,:182,:185 (prepare_p_src rt_routines.f90:535) */
+int dre_set_sources(dre_engine*, const double* lumcell /*(L,N) or NULL*/, int32_t tot_p_src,
+                    const double* ccoord_p_src /*(3,S)*/, const double* lum_p_src_arr /*(L,S)*/,
+                    const int32_t* src_cell /*(N)*/, const int32_t* cell_src /*(S)*/);
+int dre_set_params(dre_engine*, const dre_params*);
+
+/* ---- device-resident state (mirrors of u_fest_arr, u_final_arr, scaspe_arr,
+ *      scaspe_prev_arr, scaspe_tot_arr, lum_lost, psel_av_arr) ----------------- */
+enum { DRE_ARR_U_FEST = 0, DRE_ARR_U_FINAL = 1, DRE_ARR_SCASPE = 2, DRE_ARR_SCASPE_PREV = 3,
+       DRE_ARR_SCASPE_TOT = 4, DRE_ARR_LUM_LOST = 5, DRE_ARR_PSEL_AV = 6, DRE_ARR_LUMCELL = 7,
+       DRE_ARR_I_OBS = 8, DRE_ARR_I_OBS_IN = 9 };
+/* (L,N) arrays: `planes` = pointer to the array.  scaspe arrays: `planes` = array of L
+ * pointers, plane l is (P(l),N) pixel-fastest, as scaspe_arr(l)%a. */
+int dre_upload  (dre_engine*, int which, const void* planes);
+int dre_download(dre_engine*, int which, void* planes);
+int dre_zero    (dre_engine*, int which);
+
+/* ---- passes -------------------------------------------------------------- */
+/* rt_loop on device-resident state; accumulates into u_fest (precalc) or u_final+scaspe+lum_lost. */
+int dre_run_pass_resident(dre_engine*, int rt_type, int iterations, dre_counters* out);
+/* rt_loop with HOST arrays: upload -> pass -> download (the drop-in call). */
+int dre_run_pass(dre_engine*, int rt_type, int iterations,
+                 const double* u_fest /*(L,N) in*/, double* u_accum /*(L,N) inout*/,
+                 double* const* scaspe /*L ptrs inout or NULL*/, const double* const* scaspe_prev /*in or NULL*/,
+                 double* lum_lost /*(L) inout or NULL*/, double* psel_av /*(N+S) out or NULL*/,
+                 dre_counters* out);
+/* rt_loop_iobs; i_obs (L, N+S, ndir) += , i_obs_in (L, N+S, ndir_in) += */
+int dre_run_iobs(dre_engine*, int rt_type, const double* const* scaspe_tot /*L ptrs or NULL*/,
+                 int32_t tot_ndir_in, const double* ccoord_obs /*(3,ndir_in)*/,
+                 double* i_obs, double* i_obs_in, dre_counters* out);
+/* rt_mpi: combine the per-rank accumulators (NCCL all-reduce, fp64 sum). */
+int dre_allreduce(dre_engine*, int rt_type);
+/* rt_prepare(rtt_scatt): u_fest<-u_final, lum_lost_prev<-lum_lost, scaspe_prev<-scaspe,
+ * lumcell(l,c)=sum_{p<npix_hp} scaspe, tot_rad_en at iteration 1, convergence flag,
+ * sequential: scaspe_tot += scaspe (iterations>1), scaspe = 0. */
+int dre_prepare_scatt(dre_engine*, int iterations, double conv_en_lim,
+                      double* tot_rad_en /*(L) inout*/, int32_t* cnflag /*out*/);
+
+/* ---- separate small kernels (north star: cell-list and bounding-box kernels) */
+/* leaf && sum(lum)>0 gate of rt_loop rt_routines.f90:1016; returns the list length */
+int dre_build_source_list(dre_engine*, int rt_type, int32_t* n_sources, int32_t* list_out /*(N) or NULL*/);
+/* find_cc_new2 rt_routines.f90:1962: locate points; cell_out=-1 when outside the model */
+int dre_locate_points(dre_engine*, int32_t npts, const double* xyz /*(3,npts)*/,
+                      const int32_t* cc_old /*(npts)*/, int32_t* cell_out /*(npts)*/);
+/* pix2ang_nest + calc_cproj (healpix_routines.f90:30, rt_routines.f90:1945) */
+int dre_pix2vec(dre_engine*, int32_t nside, int32_t npix, const int32_t* ipix,
+                double* theta, double* phi, double* vec /*(3,npix)*/);
+
+/* ---- parity / debug ------------------------------------------------------- */
+int dre_set_record(dre_engine*, int64_t max_records);   /* 0 disables */
+int dre_get_records(dre_engine*, dre_isect* out, int64_t cap, int64_t* n);
+int dre_set_option(dre_engine*, const char* name, double value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DARTRAY_ENGINE_H */

@@ -1,0 +1,1199 @@
+// dartray_oracle.cpp — CPU restatement of the DART-Ray ray-tracing hot path.
+//
+// TEST INFRASTRUCTURE ONLY.  Imported/linked only by tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference legs.  The product (dart-ray_b200/)
+// never calls it.
+//
+// PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for this
+// path and cannot be compiled here (Fortran 90 + MPI + HDF5, no
+// Fortran compiler in the image).  This file is a function-by-function transcription
+// with the reference file:line beside each block; its own fidelity is protected by the
+// substitute pins in tests/ (HEALPix round trips, tree round trips, chord-length and
+// optically-thin analytic cases, energy conservation).
+//
+// All paths below are under /root/reference.  Compile: g++ -O2 -ffp-contract=off -fopenmp
+// (no FMA contraction: gfortran on baseline x86-64 emits none).
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <cstdio>
+#include <vector>
+#include <string>
+#include <algorithm>
+#include <chrono>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+#include "../include/dartray_engine.h"
+#include "../include/dartray_hash.h"
+
+namespace {
+
+// ---- constants: smooth_grid_routines.f90:311-317, healpix_routines.f90:13 ---------
+// halfpi=asin(1.) is a default-real (single precision) constant promoted to real64.
+const double HALFPI = (double)1.57079637050628662109375f;  // float(pi/2)
+const double PI = 2 * HALFPI;
+const double TWOPI = 2 * PI;
+const double TWOTHIRD = (double)(2.f / 3.f);
+const double GLEPSILON = (double)1.0e-7f;   // rt_routines.f90:76
+const int NSIDE_MIN = 4;                    // rt_routines.f90:60
+const int NPIX_MAIN = 12;                   // rt_routines.f90:62
+const int MAXL = 16;                        // max tree depth supported by the oracle
+
+// ray types ray_list.f90:48-59 ; ray status rt_routines.f90:254-264
+enum { RT_HIGH = 0, RT_LOW = 1, RT_RECO = 2, RT_GONE = 3, RT_IOBS = 4, RT_IOBS_IN = 5 };
+enum { RAS_GO_HIGH = 0, RAS_GONE = 1, RAS_GO_LOW = 2, RAS_FIRST = 3, RAS_RELAUNCH = 4 };
+
+// ---- HEALPix: healpix_routines.f90 -------------------------------------------------
+int pix2x[1024], pix2y[1024], x2pix1[128], y2pix1[128];
+bool hp_init_done = false;
+
+void mk_pix2xy() {  // :145-175
+  for (int kpix = 0; kpix < 1024; kpix++) {
+    int jpix = kpix, ix = 0, iy = 0, ip = 1;
+    while (jpix != 0) {
+      int id = jpix % 2; jpix /= 2; ix = id * ip + ix;
+      id = jpix % 2; jpix /= 2; iy = id * ip + iy;
+      ip = 2 * ip;
+    }
+    pix2x[kpix] = ix; pix2y[kpix] = iy;
+  }
+}
+void mk_xy2pix1() {  // :351-386
+  for (int i = 0; i < 128; i++) {
+    int j = i, k = 0, ip = 1;
+    while (j != 0) { int id = j % 2; j /= 2; k = ip * id + k; ip *= 4; }
+    x2pix1[i] = k; y2pix1[i] = 2 * k;
+  }
+}
+void hp_init() { if (!hp_init_done) { mk_pix2xy(); mk_xy2pix1(); hp_init_done = true; } }
+
+// pix2ang_nest :30-136 (nside <= 8192 branch)
+void pix2ang_nest(int nside, int ipix, double& theta, double& phi) {
+  static const int jrll[12] = {2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4};
+  static const int jpll[12] = {1, 3, 5, 7, 0, 2, 4, 6, 1, 3, 5, 7};
+  int npface = nside * nside;
+  int nl4 = 4 * nside;
+  int face_num = ipix / npface;
+  int ipf = ipix % npface;
+  double fn = (double)nside;
+  double fact1 = 1.0 / (3.0 * fn * fn);
+  double fact2 = 2.0 / (3.0 * fn);
+  int ip_low = ipf & 1023;
+  int ip_trunc = ipf / 1024;
+  int ip_med = ip_trunc & 1023;
+  int ip_hi = ip_trunc / 1024;
+  int ix = 1024 * pix2x[ip_hi] + 32 * pix2x[ip_med] + pix2x[ip_low];
+  int iy = 1024 * pix2y[ip_hi] + 32 * pix2y[ip_med] + pix2y[ip_low];
+  int jrt = ix + iy;
+  int jpt = ix - iy;
+  int jr = jrll[face_num] * nside - jrt - 1;
+  int nr, kshift; double z;
+  if (jr < nside) {
+    nr = jr; z = 1.0 - nr * fact1 * nr; kshift = 0;
+  } else if (jr <= 3 * nside) {
+    nr = nside; z = (2 * nside - jr) * fact2; kshift = (jr - nside) & 1;
+  } else {
+    nr = nl4 - jr; z = -1.0 + nr * fact1 * nr; kshift = 0;
+  }
+  theta = acos(z);
+  int jp = (jpll[face_num] * nr + jpt + 1 + kshift) / 2;
+  if (jp > nl4) jp -= nl4;
+  if (jp < 1) jp += nl4;
+  phi = (jp - (kshift + 1) * 0.5) * (HALFPI / nr);
+}
+
+// Fortran MODULO(a,p) for reals as gfortran expands it: fmod, then shift into the sign of p
+inline double f_modulo(double a, double p) {
+  double r = fmod(a, p);
+  if (r != 0 && ((r < 0) != (p < 0))) r += p;
+  return r;
+}
+
+// ang2pix_nest :238-348
+int ang2pix_nest(int nside, double theta, double phi) {
+  double z = cos(theta);
+  double za = fabs(z);
+  double tt = f_modulo(phi, TWOPI) / HALFPI;
+  int face_num, ix, iy;
+  if (za <= TWOTHIRD) {
+    int jp = (int)(nside * (0.5 + tt - z * 0.75));
+    int jm = (int)(nside * (0.5 + tt + z * 0.75));
+    int ifp = jp / nside, ifm = jm / nside;
+    if (ifp == ifm) face_num = (ifp & 3) + 4;
+    else if (ifp < ifm) face_num = (ifp & 3);
+    else face_num = (ifm & 3) + 8;
+    ix = jm & (nside - 1);
+    iy = nside - (jp & (nside - 1)) - 1;
+  } else {
+    int ntt = (int)tt;
+    if (ntt >= 4) ntt = 3;
+    double tp = tt - ntt;
+    double tmp = sqrt(3.0 * (1.0 - za));
+    int jp = (int)(nside * tp * tmp);
+    int jm = (int)(nside * (1.0 - tp) * tmp);
+    jp = std::min(nside - 1, jp);
+    jm = std::min(nside - 1, jm);
+    if (z >= 0) { face_num = ntt; ix = nside - jm - 1; iy = nside - jp - 1; }
+    else { face_num = ntt + 8; ix = jp; iy = jm; }
+  }
+  int ix_low = ix & 127, iy_low = iy & 127;
+  int ipf = x2pix1[ix_low] + y2pix1[iy_low] + (x2pix1[ix / 128] + y2pix1[iy / 128]) * 16384;
+  return ipf + face_num * nside * nside;
+}
+
+// ---- ray list element: ray_list.f90:7-27 ---------------------------------------------
+struct Ray {
+  double theta, phi;
+  std::vector<double> src_lum;
+  int nside;
+  double dplane, prev;
+  int isel;
+  int ray_type;
+  int cc_old;
+};
+
+// ---- context ---------------------------------------------------------------------------
+struct Ctx {
+  // grid (smooth_grid_routines.f90:41-70)
+  int N = 0, max_lvl = 0, base[2] = {0, 0};
+  std::vector<int> cchild, lvl;
+  std::vector<int64_t> cindex;
+  std::vector<double> ccoord, csize, csize_arr, carea_arr, cvol_arr;
+  int64_t basediv[2]; int basemask[2];
+  // opacity
+  int L = 0, ndir = 0;
+  std::vector<double> dens_arr, ksca_norm, gsca, dir_i_out;
+  std::vector<int> kp_sca, ik_sca, npix_hp_arr, npix_arr;
+  int dim_npix_unique = 0;
+  std::vector<int> kp_unique, npix_hp_unique, npix_unique;
+  std::vector<std::vector<double>> sin_theta_sca, cos_theta_sca, sin_phi_sca, cos_phi_sca;
+  // sources
+  std::vector<double> lumcell, ccoord_p_src, lum_p_src;
+  std::vector<int> src_cell, cell_src;
+  int S = 0;
+  dre_params par;
+  // record
+  int64_t max_records = 0;
+  std::vector<dre_isect> records;
+  std::string err;
+};
+
+// set_base smooth_grid_routines.f90:622-649
+void set_base(Ctx& c) {
+  for (int i = 0; i < 2; i++) {
+    int j = 0; int64_t base3 = (int64_t)c.base[i] * c.base[i] * c.base[i];
+    while (!(base3 < ((int64_t)1 << j))) j++;
+    c.basediv[i] = (int64_t)1 << j;
+    c.basemask[i] = (int)(c.basediv[i] - 1);
+  }
+}
+
+inline int64_t ipow64(int64_t b, int e) { int64_t r = 1; for (int i = 0; i < e; i++) r *= b; return r; }
+
+// cindex_to_ccindd smooth_grid_routines.f90:793-813 ; ccindd[axis 0..2][level 1..max_lvl]
+void cindex_to_ccindd(const Ctx& c, int nc, int clvl, int ccindd[3][MAXL + 1]) {
+  for (int i = 1; i <= clvl; i++) {
+    int ib; int64_t j;
+    if (i > 1) { ib = 1; j = ((c.cindex[nc] / (c.basediv[0] * ipow64(c.basediv[1], i - 2))) & c.basemask[1]) - 1; }
+    else { ib = 0; j = ((c.cindex[nc] / ipow64(c.basediv[0], i - 1)) & c.basemask[0]) - 1; }
+    int b = c.base[ib];
+    ccindd[0][i] = (int)(j % b);
+    ccindd[1][i] = (int)((j / b) % b);
+    ccindd[2][i] = (int)((j / ((int64_t)b * b)) % b);
+  }
+}
+
+// ccindd_to_cc smooth_grid_routines.f90:820-852
+bool ccindd_to_cc(const Ctx& c, const int ccindd[3][MAXL + 1], int& cc, int& clvl) {
+  int l = 1;
+  for (int i = 1; i <= c.max_lvl; i++) {
+    int b = c.base[i > 1 ? 1 : 0];
+    int k = (ccindd[2][i] * b + ccindd[1][i]) * b + ccindd[0][i] + 1;
+    l = l + k - 1;
+    if (c.cchild[l] == -1) { cc = l; clvl = i; return true; }
+    l = c.cchild[l];
+  }
+  return false;
+}
+
+// increment smooth_grid_routines.f90:751-769
+inline void increment(const Ctx& c, int ilvl, int& val, int inc, int& ovr) {
+  int b = c.base[ilvl > 1 ? 1 : 0];
+  val = val + inc;
+  ovr = inc;
+  if (val >= b) val = 0;
+  else if (val < 0) val = b - 1;
+  else ovr = 0;
+}
+
+// (continued below)
+
+// ---- per-thread state: the THREADPRIVATE list at rt_routines.f90:527-528, ray_list.f90:61 ----
+struct Th {
+  const Ctx* c;
+  int rt_type, iterations;
+  bool multi;                      // >1 thread: shared accumulators use atomics (lock_cell>1 branch)
+  // accumulators (shared between threads)
+  const double* u_fest; double* u_accum; double* const* scaspe; const double* const* scaspe_prev;
+  const double* const* scaspe_tot;
+  double src_ccoord[3];
+  int nside;
+  int ccindd_nc[3][MAXL + 1], ccindd[3][MAXL + 1];
+  int clvl_old;
+  double pabs_arr[3];
+  double psel_av; int64_t ipsel_av;
+  std::vector<double> lum_lost_temp, i_obs_temp;
+  double vec_mod;
+  std::vector<char> iq_a;
+  std::vector<int> iq;
+  std::vector<double> ray_intensity_dep;
+  int lnum_a, lnum_a_old;
+  std::vector<std::vector<double>> ffn_arr_mw, ffn_arr, ads_arr, scaspe_temp_arr;
+  std::vector<Ray> high, low, ext;
+  bool no_ray;
+  // bookkeeping
+  dre_counters cnt;
+  std::vector<dre_isect> rec;
+  int64_t max_rec;
+  int unit, step, ray_ord;
+};
+
+inline void atomic_add(bool multi, double* p, double v) {
+  if (multi) {
+#pragma omp atomic
+    *p += v;
+  } else {
+    *p += v;
+  }
+}
+
+// calc_cproj rt_routines.f90:1945-1953
+inline void calc_cproj(double al, double dl, double cproj[3]) {
+  cproj[0] = sin(dl) * cos(al);
+  cproj[1] = sin(dl) * sin(al);
+  cproj[2] = cos(dl);
+}
+
+// calc_outcube rt_routines.f90:2072-2085
+inline int calc_outcube_sum(const double rel_vec[3], double cellsize) {
+  int s = 0;
+  for (int i = 0; i < 3; i++)
+    if (fabs(rel_vec[i]) > (double)(1.0f + 1E-7f) * cellsize / 2.0) s++;  // (1+1E-7) is single precision
+  return s;
+}
+
+// find_cc_new2 rt_routines.f90:1962-2066
+bool find_cc_new2(Th& t, int cc_old, int& cc_new, const double cproj[3], double prev_ray, bool& out, int& clvl) {
+  const Ctx& c = *t.c;
+  out = false;
+  double prev = prev_ray;
+  double pcoord[3], rel_vec[3], norm_pcoord[3];
+  for (int i = 0; i < 3; i++) pcoord[i] = t.src_ccoord[i] + prev * cproj[i];
+  for (int i = 0; i < 3; i++)
+    if (fabs(pcoord[i]) > c.par.modelsize / 2.) { out = true; return true; }
+  for (int i = 0; i < 3; i++) rel_vec[i] = pcoord[i] - c.ccoord[3 * (size_t)cc_old + i];
+  double cellsize = c.csize[cc_old];
+  if (calc_outcube_sum(rel_vec, cellsize) == 0) {
+    clvl = c.lvl[cc_old];
+    cc_new = cc_old;
+    cindex_to_ccindd(c, cc_new, clvl, t.ccindd);
+    return true;
+  }
+  for (int i = 0; i < 3; i++) norm_pcoord[i] = pcoord[i] + c.par.modelsize / 2.;
+  for (int i = 1; i <= c.max_lvl; i++) {
+    int b = c.base[i > 1 ? 1 : 0];
+    for (int a = 0; a < 3; a++) t.ccindd[a][i] = (int)(norm_pcoord[a] / c.csize_arr[i]);
+    for (int a = 0; a < 3; a++) if (t.ccindd[a][i] == b) t.ccindd[a][i] = b - 1;
+    for (int a = 0; a < 3; a++) norm_pcoord[a] = norm_pcoord[a] - t.ccindd[a][i] * c.csize_arr[i];
+  }
+  if (!ccindd_to_cc(c, t.ccindd, cc_new, clvl)) return false;  // 'cell not found in find_cc_new2'
+  for (int i = 0; i < 3; i++) rel_vec[i] = pcoord[i] - c.ccoord[3 * (size_t)cc_new + i];
+  cellsize = c.csize_arr[clvl];
+  return calc_outcube_sum(rel_vec, cellsize) == 0;  // else 'host cell not found'
+}
+
+// calc_ads_arr rt_routines.f90:2288-2297
+void calc_ads_arr(Th& t, double sin_dl, double cos_dl, double sin_al, double cos_al) {
+  const Ctx& c = *t.c;
+  for (int i = 0; i < c.dim_npix_unique; i++)
+    for (int p = 0; p < c.npix_unique[i]; p++)
+      t.ads_arr[i][p] = (c.cos_theta_sca[i][p] * cos_dl +
+                         c.sin_theta_sca[i][p] * sin_dl * (c.cos_phi_sca[i][p] * cos_al + c.sin_phi_sca[i][p] * sin_al));
+}
+
+// calc_ffn_arr rt_routines.f90:2186-2281.  For nside<=256 the reference reads the
+// precomputed table ads_arrNNN(:,ipix) built at :2129-2148 from pix2ang_nest(nside, ipix);
+// the same values are produced here on the fly.
+void calc_ffn_arr(Th& t, double al, double dl, int ipix) {
+  const Ctx& c = *t.c;
+  if (t.nside <= 256) {
+    double theta, phi;
+    pix2ang_nest(t.nside, ipix, theta, phi);
+    calc_ads_arr(t, sin(theta), cos(theta), sin(phi), cos(phi));
+  } else if (c.dim_npix_unique > 0) {
+    calc_ads_arr(t, sin(dl), cos(dl), sin(al), cos(al));
+  }
+  int k = 0;
+  for (int i = 0; i < c.L; i++) {
+    if (t.iq_a[i]) {
+      int ik_sca = c.ik_sca[i];
+      if (ik_sca != -1) {
+        double g = c.gsca[i];
+        double cst = (1.0 - g * g) / c.npix_hp_arr[i];
+        std::vector<double>& f = t.ffn_arr[ik_sca];
+        int np = c.npix_unique[ik_sca];
+        for (int p = 0; p < np; p++) f[p] = pow(1.0 + g * g - 2.0 * g * t.ads_arr[ik_sca][p], -1.5);
+        for (int p = 0; p < np; p++) f[p] = cst * f[p];
+        double tot_hg = 0;
+        for (int p = 0; p < c.npix_hp_arr[i]; p++) tot_hg += f[p];
+        for (int p = 0; p < np; p++) f[p] = f[p] / tot_hg;
+        for (int p = 0; p < np; p++) t.ffn_arr_mw[k][p] = f[p];
+      } else {
+        // integer division 1/npix_hp_arr with npix_hp=1 (:2266)
+        for (int p = 0; p < c.npix_arr[i]; p++) t.ffn_arr_mw[k][p] = (double)(1 / c.npix_hp_arr[i]);
+      }
+    }
+    k++;
+  }
+}
+
+// set_iq_list rt_routines.f90:1860-1893
+void set_iq_list(Th& t, const std::vector<double>& ray_intensity, bool flag_beam) {
+  const Ctx& c = *t.c;
+  for (int i = 0; i < c.L; i++) if (ray_intensity[i] > 0) t.iq_a[i] = 1;
+  t.lnum_a = 0;
+  for (int i = 0; i < c.L; i++) t.lnum_a += t.iq_a[i] ? 1 : 0;
+  if (flag_beam) t.lnum_a_old = (int)t.iq.size();
+  if (t.lnum_a_old != t.lnum_a || flag_beam) {
+    t.iq.clear();
+    for (int i = 0; i < c.L; i++) if (t.iq_a[i]) t.iq.push_back(i);
+    t.ray_intensity_dep.resize(t.lnum_a);
+    for (int k = 0; k < t.lnum_a; k++) t.ray_intensity_dep[k] = ray_intensity[t.iq[k]];
+    t.lnum_a_old = t.lnum_a;
+  }
+}
+
+// calc_psel rt_routines.f90:2307-2351
+void calc_psel(Th& t, const int incvec[3], double& psel, double pabs[3], int& isel, int clvl, int cc, const double cproj[3]) {
+  const Ctx& c = *t.c;
+  for (int a = 0; a < 3; a++) pabs[a] = (double)c.par.pabs_max;
+  const double* cco = &c.ccoord[3 * (size_t)cc];
+  if (clvl == t.clvl_old) {
+    for (int a = 0; a < 3; a++) if (incvec[a] != 0) pabs[a] = cproj[a] * cco[a] + t.pabs_arr[a];
+  } else {
+    for (int a = 0; a < 3; a++)
+      if (incvec[a] != 0) pabs[a] = cproj[a] * (cco[a] - t.src_ccoord[a] + 0.5 * (double)incvec[a] * c.csize_arr[clvl]);
+    for (int a = 0; a < 3; a++) t.pabs_arr[a] = cproj[a] * ((-t.src_ccoord[a]) + 0.5 * (double)incvec[a] * c.csize_arr[clvl]);
+  }
+  if (pabs[0] < pabs[2]) {
+    if (pabs[0] < pabs[1]) { psel = pabs[0]; isel = 1; } else { psel = pabs[1]; isel = 2; }
+  } else {
+    if (pabs[2] < pabs[1]) { psel = pabs[2]; isel = 3; } else { psel = pabs[1]; isel = 2; }
+  }
+}
+
+// check_wall_hit rt_routines.f90:2572-2596
+bool check_wall_hit(const Th& t, int cc) {
+  const Ctx& c = *t.c;
+  bool wall_hit = false;
+  if (t.rt_type == DRE_RTT_DIR_SRC) return wall_hit;
+  for (int a = 0; a < 3; a++)
+    if (c.par.wall_on[a]) {
+      double x = c.ccoord[3 * (size_t)cc + a];
+      if (x < c.par.wall_coord[2 * a] || x > c.par.wall_coord[2 * a + 1]) wall_hit = true;
+    }
+  return wall_hit;
+}
+
+// process_scatt_rad rt_routines.f90:2638-2726 (no_communications, sequential_scattering)
+void process_scatt_rad(Th& t, int cc, const std::vector<double>& en_sca) {
+  const Ctx& c = *t.c;
+  double s = 0;
+  for (int iw = 0; iw < t.lnum_a; iw++) s += en_sca[iw];
+  if (s == 0.) return;
+  for (int iw = 0; iw < t.lnum_a; iw++) {
+    int il = t.iq[iw];
+    double en_sca_out = en_sca[iw];
+    int np = c.npix_arr[il];
+    double* row = t.scaspe[il] + (size_t)np * cc;
+    const std::vector<double>& f = t.ffn_arr_mw[il];
+    for (int p = 0; p < np; p++) atomic_add(t.multi, &row[p], en_sca_out * f[p]);
+    t.cnt.sca_elems += np;
+  }
+}
+
+// deposit rt_routines.f90:2362-2557 ; ray_intensity is the compact (iq) array
+void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, int nc, double psel,
+             int& ray_status, bool flag_beam) {
+  const Ctx& c = *t.c;
+  const dre_params& P = c.par;
+  const int La = t.lnum_a;
+  const int L = c.L;
+  int npix_beam = 12 * (t.nside * t.nside);
+  std::vector<double> tau_c(La), exp_tau_c(La), i_av(La);
+  for (int k = 0; k < La; k++) tau_c[k] = c.dens_arr[t.iq[k] + (size_t)L * cc] * length;
+  for (int k = 0; k < La; k++) exp_tau_c[k] = exp(-tau_c[k]);
+  int clvl = c.lvl[nc];
+  double csize_i = c.csize_arr[clvl];
+  double area_i = c.carea_arr[clvl];
+  double beam_i = 4 * PI / npix_beam;
+  clvl = c.lvl[cc];
+  double csize_f = c.csize_arr[clvl];
+  double vol_f = c.cvol_arr[clvl];
+  double beam_f = c.carea_arr[clvl] / (psel * psel);
+  const double TINY = (double)1E-008f;
+  if (cc != nc) {
+    for (int k = 0; k < La; k++) {
+      if (tau_c[k] < TINY || ray_intensity[k] == 0) i_av[k] = ray_intensity[k];
+      else i_av[k] = ray_intensity[k] / tau_c[k] * (1 - exp_tau_c[k]);
+    }
+  } else {
+    for (int k = 0; k < La; k++) {
+      if (tau_c[k] < TINY || ray_intensity[k] == 0) i_av[k] = ray_intensity[k];
+      else if (t.rt_type != DRE_RTT_PRECALC_SRC && t.rt_type != DRE_RTT_DIR_SRC) {
+        tau_c[k] = c.dens_arr[t.iq[k] + (size_t)L * cc] * csize_i;
+        exp_tau_c[k] = exp(-tau_c[k]);
+        i_av[k] = ray_intensity[k] / (tau_c[k] * tau_c[k]) * (exp_tau_c[k] + tau_c[k] - 1);
+      } else {
+        i_av[k] = ray_intensity[k] / (c.dens_arr[t.iq[k] + (size_t)L * cc] * length) * (1 - exp_tau_c[k]);
+      }
+    }
+  }
+  switch (t.rt_type) {
+    case DRE_RTT_PRECALC_SRC:
+    case DRE_RTT_PRECALC_CELL:
+      if (psel > P.rad_lim * P.modelsize) { ray_status = RAS_GONE; return; }
+      if ((beam_f / P.bm_par <= beam_i) && !flag_beam) { ray_status = RAS_GO_HIGH; return; }
+      if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
+        for (int k = 0; k < La; k++)
+          atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
+        t.cnt.deposits++; t.cnt.active_lambda += La;
+      } else { ray_status = RAS_GO_LOW; return; }
+      break;
+    case DRE_RTT_DIR_SRC:
+    case DRE_RTT_DIR_CELL:
+    case DRE_RTT_SCATT:
+      if ((beam_f / P.bm_par <= beam_i) && !flag_beam) {
+        t.cnt.beam_tests++; t.cnt.active_lambda += La;
+        bool any_pos = false;
+        for (int k = 0; k < La; k++) {
+          double u_beam = i_av[k] * csize_f / P.cs / vol_f * area_i * beam_f;
+          if (u_beam < P.en_lim * t.u_fest[t.iq[k] + (size_t)L * cc]) {
+            ray_intensity[k] = 0;
+            t.lum_lost_temp[t.iq[k]] = t.lum_lost_temp[t.iq[k]] + i_av[k] * beam_i * csize_i * csize_i;
+          }
+        }
+        for (int k = 0; k < La; k++) if (ray_intensity[k] > 0) any_pos = true;
+        bool wall_hit = check_wall_hit(t, cc);
+        if (any_pos && !wall_hit) { ray_status = RAS_GO_HIGH; return; }
+        ray_status = RAS_GONE;
+        return;
+      } else if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
+        for (int k = 0; k < La; k++)
+          atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
+        t.cnt.deposits++; t.cnt.active_lambda += La;
+        std::vector<double> en_sca(La, 0.0);
+        if (cc != nc) {
+          for (int k = 0; k < La; k++) {
+            if (tau_c[k] > TINY) en_sca[k] = ray_intensity[k] * (1.0 - exp_tau_c[k]) * c.ksca_norm[t.iq[k]] * area_i * beam_i;
+            else en_sca[k] = ray_intensity[k] * tau_c[k] * c.ksca_norm[t.iq[k]] * area_i * beam_i;
+          }
+        } else {
+          for (int k = 0; k < La; k++) {
+            if (tau_c[k] > TINY) en_sca[k] = ray_intensity[k] / (tau_c[k]) * (exp_tau_c[k] + tau_c[k] - 1) * c.ksca_norm[t.iq[k]] * area_i * beam_i;
+            else en_sca[k] = ray_intensity[k] * tau_c[k] / 2 * c.ksca_norm[t.iq[k]] * area_i * beam_i;
+          }
+        }
+        process_scatt_rad(t, cc, en_sca);
+      } else { ray_status = RAS_GO_LOW; return; }
+      break;
+    default: break;  // i_obs passes: attenuation only
+  }
+  // update ray_intensity :2543-2555
+  if (cc != nc) {
+    for (int k = 0; k < La; k++) ray_intensity[k] = ray_intensity[k] * exp_tau_c[k];
+  } else {
+    for (int k = 0; k < La; k++)
+      if (!(tau_c[k] < TINY)) ray_intensity[k] = ray_intensity[k] / (tau_c[k]) * (1 - exp_tau_c[k]);
+  }
+}
+// (continued below)
+
+// add_to_high_ray_list ray_list.f90:463-521
+void add_to_high_ray_list(Th& t, double theta, double phi, int nside, double prev, int isel_old, double dplane,
+                          const std::vector<double>& src_lum, int cc, int ray_type) {
+  Ray r;
+  r.theta = theta; r.phi = phi; r.nside = nside;
+  if (isel_old != 0) { r.dplane = dplane; r.prev = prev; } else { r.dplane = 0.; r.prev = 0.; }
+  r.isel = isel_old; r.src_lum = src_lum; r.ray_type = ray_type; r.cc_old = cc;
+  t.high.push_back(std::move(r));
+}
+
+// add_to_low_ray_list ray_list.f90:532-579 ; cproj is the INVERTED direction array (Q8)
+void add_to_low_ray_list(Th& t, double theta, double phi, int nside, double prev, int isel_old, const double cproj[3],
+                         const std::vector<double>& src_lum, int cc) {
+  Ray r;
+  r.theta = theta; r.phi = phi; r.nside = nside;
+  // isel_old==0 would index cproj(0) (out of bounds) in the reference; unreachable because
+  // flag_beam forbids go_low in the launch cell.  Guarded, not reproduced.
+  r.dplane = (isel_old != 0) ? prev / cproj[isel_old - 1] : 0.;
+  r.prev = prev; r.isel = isel_old; r.src_lum = src_lum; r.ray_type = RT_LOW; r.cc_old = cc;
+  t.low.push_back(std::move(r));
+}
+
+inline void record_isect(Th& t, int k, int cc, int isel, double psel) {
+  uint64_t bits; memcpy(&bits, &psel, 8);
+  t.cnt.isect_hash += dre_isect_mix(t.unit, t.step, t.ray_ord, k, cc, isel, bits);
+  if ((int64_t)t.rec.size() < t.max_rec) {
+    dre_isect r; r.unit = t.unit; r.step = t.step; r.ray = t.ray_ord; r.k = k; r.cell = cc; r.isel = isel; r.psel = psel;
+    t.rec.push_back(r);
+  }
+}
+
+// ray_tracing rt_routines.f90:1618-1857.  Returns false on the reference's STOP conditions.
+bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vector<double>& src_lum, double dplane_ray,
+                 double prev_ray, int isel_ray, int ray_type, int ipix, int cc_old) {
+  const Ctx& c = *t.c;
+  const int L = c.L;
+  (void)dplane_ray;
+  t.cnt.rays++;
+  double cproj[3];
+  calc_cproj(al, dl, cproj);
+  int cc, isel = 0, isel_old, cc_new, ray_status;
+  double prev;
+  bool flag_beam;
+  if (cc_old == nc) {
+    cc = nc; prev = 0.0; ray_status = RAS_FIRST; isel_old = 0; flag_beam = true; t.clvl_old = -1;
+    memcpy(t.ccindd, t.ccindd_nc, sizeof(t.ccindd)); cc_new = -1;
+  } else {
+    bool out;
+    if (!find_cc_new2(t, cc_old, cc_new, cproj, prev_ray, out, clvl)) return false;
+    prev = prev_ray;
+    if (out) { t.ray_ord++; return true; }
+    cc = cc_new; ray_status = RAS_RELAUNCH; isel_old = isel_ray; flag_beam = true; t.clvl_old = -1;
+  }
+  int incvec[3];
+  for (int i = 0; i < 3; i++) incvec[i] = std::max(std::min((int)(cproj[i] / GLEPSILON), 1), -1);
+  for (int i = 0; i < 3; i++) cproj[i] = 1 / cproj[i];
+  std::vector<double> ray_intensity(L);
+  for (int i = 0; i < L; i++) ray_intensity[i] = src_lum[i] / (4 * PI * c.csize[nc] * c.csize[nc]);
+  std::fill(t.iq_a.begin(), t.iq_a.end(), 0);
+  set_iq_list(t, ray_intensity, flag_beam);
+  const bool dep_pass = (t.rt_type == DRE_RTT_DIR_SRC || t.rt_type == DRE_RTT_DIR_CELL || t.rt_type == DRE_RTT_SCATT);
+  if (dep_pass) calc_ffn_arr(t, al, dl, ipix);
+  const bool iobs_pass = (t.rt_type == DRE_RTT_I_OBS_DIR_CELL || t.rt_type == DRE_RTT_I_OBS_DIR_SRC || t.rt_type == DRE_RTT_I_OBS);
+  int kint = 0;
+  bool ok = true;
+  for (;;) {
+    if (dep_pass) set_iq_list(t, ray_intensity, flag_beam);
+    double psel, pabs[3];
+    calc_psel(t, incvec, psel, pabs, isel, clvl, cc, cproj);
+    t.cnt.intersections++;
+    record_isect(t, kint++, cc, isel, psel);
+    double length = psel - prev;
+    if (fabs(length) < (double)1E-5f * c.csize_arr[clvl]) length = 0;
+    if (length < 0) { ok = false; break; }  // 'what ? Something wrong in ray_tracing'
+    if (cc != nc && cc != cc_new) flag_beam = false;
+    if (length != 0.) {
+      deposit(t, cc, t.ray_intensity_dep, length, nc, psel, ray_status, flag_beam);
+      for (int k = 0; k < t.lnum_a; k++) ray_intensity[t.iq[k]] = t.ray_intensity_dep[k];
+    }
+    if (ray_status == RAS_GO_HIGH) {
+      std::vector<double> sl(L);
+      for (int i = 0; i < L; i++) sl[i] = ray_intensity[i] * (4 * PI * c.csize[nc] * c.csize[nc]);
+      double dpl = (isel_old != 0) ? prev / cproj[isel_old - 1] : 0.;  // Q11: guard cproj(0)
+      add_to_high_ray_list(t, dl, al, t.nside, prev, isel_old, dpl, sl, cc, RT_HIGH);
+      t.cnt.splits++;
+      break;
+    } else if (ray_status == RAS_GONE) {
+      t.ipsel_av++; t.psel_av += psel;
+      break;
+    } else if (ray_status == RAS_GO_LOW) {
+      std::vector<double> sl(L);
+      for (int i = 0; i < L; i++) sl[i] = ray_intensity[i] * (4 * PI * c.csize[nc] * c.csize[nc]);
+      add_to_low_ray_list(t, dl, al, t.nside, prev, isel_old, cproj, sl, cc);
+      t.cnt.merges++;
+      break;
+    }
+    if (ray_type == RT_IOBS_IN) {
+      if ((t.vec_mod >= prev) && (t.vec_mod <= psel)) {
+        for (int i = 0; i < L; i++) t.i_obs_temp[i] = ray_intensity[i] * exp(c.dens_arr[i + (size_t)L * cc] * (psel - t.vec_mod));
+        break;
+      }
+    }
+    prev = psel; isel_old = isel; t.clvl_old = clvl;
+    // next cell :1778-1841
+    bool left = false;
+    for (int i = 1; i <= 3; i++) {
+      int a = i - 1;
+      if (i == isel) {
+        int k = incvec[a];
+        for (int j = clvl; j >= 1; j--) { increment(c, j, t.ccindd[a][j], k, k); if (k == 0) break; }
+        if (k != 0) {
+          t.ipsel_av++; t.psel_av += psel;
+          if (iobs_pass) for (int q = 0; q < L; q++) t.i_obs_temp[q] = ray_intensity[q];
+          left = true; break;
+        }
+        for (int j = clvl + 1; j <= c.max_lvl; j++) {
+          int b = c.base[j > 1 ? 1 : 0];
+          if (incvec[a] == 1) t.ccindd[a][j] = 0;
+          else if (incvec[a] == -1) t.ccindd[a][j] = b - 1;
+        }
+      } else {
+        double cellsize = c.csize_arr[clvl];
+        double b = psel / cproj[a] + (t.src_ccoord[a] - c.ccoord[3 * (size_t)cc + a] + 0.5 * cellsize);
+        for (int j = clvl + 1; j <= c.max_lvl; j++) {
+          int bb = c.base[j > 1 ? 1 : 0];
+          cellsize = c.csize_arr[j];
+          t.ccindd[a][j] = (int)(b / cellsize);
+          if (t.ccindd[a][j] == bb) t.ccindd[a][j] = bb - 1;
+          b = fmod(b, cellsize);
+        }
+      }
+    }
+    if (left) break;
+    if (!ccindd_to_cc(c, t.ccindd, cc, clvl)) { ok = false; break; }  // 'Here you should never get'
+  }
+  t.ray_ord++;
+  return ok;
+}
+// (continued below)
+
+// extract_ray_list ray_list.f90:110-306
+void extract_ray_list(Th& t, int nside) {
+  const int L = t.c->L;
+  t.no_ray = false;
+  t.ext.clear();
+  if (!t.high.empty()) {
+    std::vector<Ray> keep;
+    for (auto& r : t.high) {
+      if (r.nside == nside / 2) t.ext.push_back(std::move(r)); else keep.push_back(std::move(r));
+    }
+    if (t.ext.empty()) { t.high.swap(keep); t.no_ray = true; return; }
+    t.high.swap(keep);  // compress_high_list :361-403
+  } else if (!t.low.empty()) {
+    std::vector<Ray> keep;
+    bool any = false;
+    for (auto& r : t.low) if (r.nside == nside * 2) { any = true; break; }
+    if (!any) { t.no_ray = true; return; }
+    for (auto& r : t.low) {
+      if (r.nside == nside * 2) t.ext.push_back(std::move(r)); else keep.push_back(std::move(r));
+    }
+    t.low.swap(keep);   // compress_low_list :406-451 (done at the end in the reference; order-independent)
+    const int ni = (int)t.ext.size();
+    std::vector<int> ipix_arr(ni);
+    for (int i = 0; i < ni; i++) ipix_arr[i] = ang2pix_nest(nside, t.ext[i].theta, t.ext[i].phi);
+    for (int i = 0; i < ni; i++) {
+      int ic_arr[5] = {-1, -1, -1, -1, -1};
+      if (t.ext[i].ray_type == RT_GONE) continue;
+      double dplane_ray = t.ext[i].dplane;
+      int isel_ray = t.ext[i].isel;
+      int ipix = ipix_arr[i];
+      double theta, phi;
+      pix2ang_nest(nside, ipix, theta, phi);
+      int icount = 1;
+      ic_arr[icount] = i;
+      for (int j = i + 1; j < ni; j++) {
+        double dplane_ray_add = t.ext[j].dplane;
+        int isel_ray_add = t.ext[j].isel;
+        int ipix_add = ipix_arr[j];
+        if ((ipix_add == ipix) && (isel_ray == isel_ray_add) &&
+            (fabs(dplane_ray - dplane_ray_add) / fabs(dplane_ray) < (double)0.001f)) {
+          icount++;
+          ic_arr[icount] = j;
+        }
+        if (icount == 4) break;
+      }
+      if (icount == 4) {
+        t.ext[i].nside = nside; t.ext[i].theta = theta; t.ext[i].phi = phi;
+        for (int iw = 0; iw < L; iw++) {
+          for (int ic = 2; ic <= 4; ic++) t.ext[i].src_lum[iw] = t.ext[i].src_lum[iw] + t.ext[ic_arr[ic]].src_lum[iw];
+          t.ext[i].src_lum[iw] = t.ext[i].src_lum[iw] / 4;
+        }
+        double s = 0;
+        for (int ic = 1; ic <= 4; ic++) s += t.ext[ic_arr[ic]].prev;
+        t.ext[i].prev = s / 4;
+        for (int ic = 2; ic <= 4; ic++) t.ext[ic_arr[ic]].ray_type = RT_GONE;
+      } else {
+        for (int j = 1; j <= icount; j++) {
+          Ray& e = t.ext[ic_arr[j]];
+          add_to_high_ray_list(t, e.theta, e.phi, nside, e.prev, e.isel, e.dplane, e.src_lum, e.cc_old, RT_RECO);
+          e.ray_type = RT_GONE;
+        }
+      }
+    }
+  }
+}
+
+// assign_src_lum rt_routines.f90:3043-3071 (the dead code after :3071 is not restated)
+void assign_src_lum(Th& t, double theta, double phi, std::vector<double>& src_lum) {
+  const Ctx& c = *t.c;
+  std::vector<int> ip_arr(std::max(1, c.dim_npix_unique));
+  for (int i = 0; i < c.dim_npix_unique; i++) ip_arr[i] = ang2pix_nest(1 << c.kp_unique[i], theta, phi);
+  if (t.rt_type == DRE_RTT_SCATT || t.rt_type == DRE_RTT_I_OBS) {
+    for (int il = 0; il < c.L; il++) {
+      int ik = c.ik_sca[il];
+      int ip = (ik != -1) ? ip_arr[ik] : 0;
+      src_lum[il] = t.scaspe_temp_arr[il][ip] * c.npix_hp_arr[il];
+    }
+  }
+}
+
+// src_lum_value rt_routines.f90:1897-1919
+void src_lum_value(const Th& t, int id, std::vector<double>& out) {
+  const Ctx& c = *t.c;
+  const int L = c.L;
+  int rt = t.rt_type;
+  if (rt == DRE_RTT_PRECALC_SRC || rt == DRE_RTT_DIR_SRC || rt == DRE_RTT_I_OBS_DIR_SRC) {
+    if (c.S > 0 && c.src_cell[id] != -1) for (int l = 0; l < L; l++) out[l] = c.lum_p_src[l + (size_t)L * c.src_cell[id]];
+    else for (int l = 0; l < L; l++) out[l] = 0;
+  } else {
+    for (int l = 0; l < L; l++) out[l] = c.lumcell[l + (size_t)L * id];
+  }
+}
+
+// calc_src_ccoord rt_routines.f90:1922-1939
+void calc_src_ccoord(Th& t, int id) {
+  const Ctx& c = *t.c;
+  int rt = t.rt_type;
+  if (rt == DRE_RTT_PRECALC_SRC || rt == DRE_RTT_DIR_SRC || rt == DRE_RTT_I_OBS_DIR_SRC)
+    for (int a = 0; a < 3; a++) t.src_ccoord[a] = c.ccoord_p_src[3 * (size_t)c.src_cell[id] + a];
+  else
+    for (int a = 0; a < 3; a++) t.src_ccoord[a] = c.ccoord[3 * (size_t)id + a];
+}
+
+// main_dir_loop rt_routines.f90:1343-1467.  `sector_ok(unit)` implements the engine's
+// (source, sector) work-unit sharding for the multi-rank tests; the reference shards by
+// cell (rt_routines.f90:1005) — sums over ranks are identical either way.
+bool main_dir_loop(Th& t, int src_id, int src_ord, const std::vector<double>& src_lum_in, double* lum_lost,
+                   int rank, int nranks) {
+  const Ctx& c = *t.c;
+  const int L = c.L;
+  std::vector<double> src_lum = src_lum_in, src_lum_ray(L);
+  for (int idir = 0; idir < NPIX_MAIN; idir++) {
+    for (int idir2 = 0; idir2 < 4; idir2++) {
+      t.unit = src_ord * 48 + idir * 4 + idir2;
+      if (t.unit % nranks != rank) continue;
+      t.step = 0;
+      t.nside = NSIDE_MIN;
+      std::fill(t.lum_lost_temp.begin(), t.lum_lost_temp.end(), 0.0);
+      // create_high_ray_list ray_list.f90:71-106
+      {
+        int nside_low = t.nside / 2;
+        int ipix = (int)(idir * nside_low * nside_low + idir2 * nside_low * nside_low / 4.);
+        Ray r;
+        pix2ang_nest(nside_low, ipix, r.theta, r.phi);
+        r.nside = nside_low; r.dplane = 0; r.prev = 0; r.isel = 0; r.src_lum = src_lum; r.ray_type = RT_HIGH; r.cc_old = src_id;
+        t.high.clear(); t.low.clear();
+        t.high.push_back(std::move(r));
+      }
+      for (;;) {
+        extract_ray_list(t, t.nside);
+        int next = t.no_ray ? 0 : (int)t.ext.size();
+        t.ray_ord = 0;
+        for (int i_ext = 0; i_ext < next; i_ext++) {
+          Ray& e = t.ext[i_ext];
+          int nside_ray = e.nside;
+          double theta = e.theta, phi = e.phi;
+          src_lum_ray = e.src_lum;
+          double dplane_ray = e.dplane, prev_ray = e.prev;
+          int isel_ray = e.isel, ray_type = e.ray_type, cc_old = e.cc_old;
+          int i0 = 0, i1 = -1;
+          if (ray_type == RT_HIGH) { i0 = ang2pix_nest(nside_ray, theta, phi); i0 = i0 * 4; i1 = i0 + 3; }
+          if (ray_type == RT_RECO) { i0 = 1; i1 = 1; }
+          if (ray_type == RT_LOW) { i0 = ang2pix_nest(t.nside, theta, phi); i1 = i0; }
+          if (ray_type == RT_GONE) continue;
+          for (int ipix = i0; ipix <= i1; ipix++) {
+            if (ray_type == RT_HIGH) pix2ang_nest(t.nside, ipix, theta, phi);
+            if (t.rt_type == DRE_RTT_SCATT && cc_old == src_id) {
+              assign_src_lum(t, theta, phi, src_lum);
+              src_lum_ray = src_lum;
+            }
+            int clvl = c.lvl[src_id];
+            if (!ray_tracing(t, src_id, phi, theta, clvl, src_lum_ray, dplane_ray, prev_ray, isel_ray, ray_type, ipix, cc_old))
+              return false;
+          }
+        }
+        t.step++;
+        t.cnt.steps++;
+        // define_next_level rt_routines.f90:2745-2770
+        if (!t.high.empty()) t.nside = t.nside * 2;
+        else if (!t.low.empty()) t.nside = t.nside / 2;
+        else break;
+      }
+      if (t.rt_type == DRE_RTT_DIR_SRC || t.rt_type == DRE_RTT_DIR_CELL || t.rt_type == DRE_RTT_SCATT)
+        for (int i = 0; i < L; i++) atomic_add(t.multi, &lum_lost[i], t.lum_lost_temp[i]);
+    }
+  }
+  return true;
+}
+
+void th_init(Th& t, const Ctx& c, int rt_type, int iterations, bool multi) {
+  t.c = &c; t.rt_type = rt_type; t.iterations = iterations; t.multi = multi;
+  const int L = c.L;
+  t.lum_lost_temp.assign(L, 0.0); t.i_obs_temp.assign(L, 0.0);
+  t.iq_a.assign(L, 0); t.iq.clear(); t.ray_intensity_dep.clear();
+  t.lnum_a = t.lnum_a_old = 0;
+  t.ffn_arr_mw.resize(L); t.scaspe_temp_arr.resize(L);
+  for (int l = 0; l < L; l++) { t.ffn_arr_mw[l].assign(c.npix_arr[l], 0.0); t.scaspe_temp_arr[l].assign(c.npix_arr[l], 0.0); }
+  t.ffn_arr.resize(c.dim_npix_unique); t.ads_arr.resize(c.dim_npix_unique);
+  for (int i = 0; i < c.dim_npix_unique; i++) { t.ffn_arr[i].assign(c.npix_unique[i], 0.0); t.ads_arr[i].assign(c.npix_unique[i], 0.0); }
+  memset(&t.cnt, 0, sizeof(t.cnt));
+  t.max_rec = c.max_records; t.rec.clear();
+  t.vec_mod = 0; t.psel_av = 0; t.ipsel_av = 0; t.clvl_old = -1;
+  memset(t.ccindd, 0, sizeof(t.ccindd)); memset(t.ccindd_nc, 0, sizeof(t.ccindd_nc));
+  t.unit = t.step = t.ray_ord = 0;
+}
+
+void cnt_add(dre_counters& a, const dre_counters& b) {
+  a.sources += b.sources; a.rays += b.rays; a.intersections += b.intersections; a.deposits += b.deposits;
+  a.beam_tests += b.beam_tests; a.splits += b.splits; a.merges += b.merges; a.sca_elems += b.sca_elems;
+  a.active_lambda += b.active_lambda; a.steps += b.steps; a.isect_hash += b.isect_hash;
+}
+
+}  // namespace
+// (continued below)
+
+struct orc_ctx { Ctx c; };
+
+extern "C" {
+
+orc_ctx* orc_create() { hp_init(); orc_ctx* o = new orc_ctx(); memset(&o->c.par, 0, sizeof(dre_params)); return o; }
+void orc_destroy(orc_ctx* o) { delete o; }
+const char* orc_last_error(orc_ctx* o) { return o->c.err.c_str(); }
+
+int orc_set_grid(orc_ctx* o, int32_t N, int32_t max_lvl, const int32_t base[2], const int32_t* cchild, const int32_t* lvl,
+                 const int64_t* cindex, const double* ccoord, const double* csize, const double* csize_arr,
+                 const double* carea_arr, const double* cvol_arr) {
+  Ctx& c = o->c;
+  if (max_lvl > MAXL) { c.err = "max_lvl too large"; return 1; }
+  c.N = N; c.max_lvl = max_lvl; c.base[0] = base[0]; c.base[1] = base[1];
+  c.cchild.assign(cchild, cchild + N); c.lvl.assign(lvl, lvl + N); c.cindex.assign(cindex, cindex + N);
+  c.ccoord.assign(ccoord, ccoord + 3 * (size_t)N); c.csize.assign(csize, csize + N);
+  c.csize_arr.assign(csize_arr, csize_arr + max_lvl + 1);
+  c.carea_arr.assign(carea_arr, carea_arr + max_lvl + 1);
+  c.cvol_arr.assign(cvol_arr, cvol_arr + max_lvl + 1);
+  set_base(c);
+  return 0;
+}
+
+// set_npix_arr class bookkeeping rt_routines.f90:5289-5311 and create_scaspe :2827-2848
+int orc_set_opacity(orc_ctx* o, int32_t L, const double* dens_arr, const double* ksca_norm, const double* gsca,
+                    const int32_t* kp_sca, int32_t ndir, const double* dir_i_out) {
+  Ctx& c = o->c;
+  c.L = L; c.ndir = ndir;
+  c.dens_arr.assign(dens_arr, dens_arr + (size_t)L * c.N);
+  c.ksca_norm.assign(ksca_norm, ksca_norm + L); c.gsca.assign(gsca, gsca + L); c.kp_sca.assign(kp_sca, kp_sca + L);
+  c.dir_i_out.assign(dir_i_out, dir_i_out + 2 * (size_t)ndir);
+  c.npix_hp_arr.resize(L); c.npix_arr.resize(L); c.ik_sca.assign(L, -1);
+  int kmax = -1;
+  for (int l = 0; l < L; l++) {
+    c.npix_hp_arr[l] = (kp_sca[l] < 0) ? 1 : 12 * (1 << (2 * kp_sca[l]));
+    c.npix_arr[l] = c.npix_hp_arr[l] + ndir;
+    kmax = std::max(kmax, kp_sca[l]);
+  }
+  c.kp_unique.clear(); c.npix_hp_unique.clear(); c.npix_unique.clear();
+  for (int k = 0; k <= kmax; k++) {
+    bool inc = false;
+    for (int l = 0; l < L; l++) if (kp_sca[l] == k) inc = true;
+    if (inc) {
+      for (int l = 0; l < L; l++) if (kp_sca[l] == k) c.ik_sca[l] = (int)c.kp_unique.size();
+      c.kp_unique.push_back(k); c.npix_hp_unique.push_back(12 * (1 << (2 * k))); c.npix_unique.push_back(12 * (1 << (2 * k)) + ndir);
+    }
+  }
+  c.dim_npix_unique = (int)c.kp_unique.size();
+  c.sin_theta_sca.assign(c.dim_npix_unique, {}); c.cos_theta_sca = c.sin_theta_sca; c.sin_phi_sca = c.sin_theta_sca; c.cos_phi_sca = c.sin_theta_sca;
+  for (int i = 0; i < c.dim_npix_unique; i++) {
+    int np = c.npix_unique[i], nhp = c.npix_hp_unique[i];
+    std::vector<double> th(np), ph(np);
+    for (int j = 0; j < nhp; j++) pix2ang_nest(1 << c.kp_unique[i], j, th[j], ph[j]);
+    for (int j = 0; j < ndir; j++) { th[nhp + j] = dir_i_out[j]; ph[nhp + j] = dir_i_out[ndir + j]; }
+    c.sin_theta_sca[i].resize(np); c.cos_theta_sca[i].resize(np); c.sin_phi_sca[i].resize(np); c.cos_phi_sca[i].resize(np);
+    for (int j = 0; j < np; j++) {
+      c.sin_theta_sca[i][j] = sin(th[j]); c.cos_theta_sca[i][j] = cos(th[j]);
+      c.sin_phi_sca[i][j] = sin(ph[j]); c.cos_phi_sca[i][j] = cos(ph[j]);
+    }
+  }
+  return 0;
+}
+
+int orc_set_sources(orc_ctx* o, const double* lumcell, int32_t S, const double* ccoord_p_src, const double* lum_p_src,
+                    const int32_t* src_cell, const int32_t* cell_src) {
+  Ctx& c = o->c;
+  if (lumcell) c.lumcell.assign(lumcell, lumcell + (size_t)c.L * c.N); else c.lumcell.assign((size_t)c.L * c.N, 0.0);
+  c.S = S;
+  if (S > 0) {
+    c.ccoord_p_src.assign(ccoord_p_src, ccoord_p_src + 3 * (size_t)S);
+    c.lum_p_src.assign(lum_p_src, lum_p_src + (size_t)c.L * S);
+    c.src_cell.assign(src_cell, src_cell + c.N); c.cell_src.assign(cell_src, cell_src + S);
+  } else { c.src_cell.assign(c.N, -1); c.cell_src.clear(); }
+  return 0;
+}
+
+int orc_set_params(orc_ctx* o, const dre_params* p) { o->c.par = *p; return 0; }
+int orc_set_record(orc_ctx* o, int64_t n) { o->c.max_records = n; return 0; }
+int orc_get_records(orc_ctx* o, dre_isect* out, int64_t cap, int64_t* n) {
+  int64_t m = std::min<int64_t>(cap, (int64_t)o->c.records.size());
+  if (out && m > 0) memcpy(out, o->c.records.data(), m * sizeof(dre_isect));
+  *n = (int64_t)o->c.records.size();
+  return 0;
+}
+
+// rt_loop rt_routines.f90:985-1058.  psel_sum/ipsel (N+S): per-source sums (the reference stores
+// psel_av/ipsel_av at :1459-1460; the ratio is taken by the caller so sharded runs can be added).
+int orc_run_pass(orc_ctx* o, int rt_type, int iterations, const double* u_fest, double* u_accum, double* const* scaspe,
+                 const double* const* scaspe_prev, double* lum_lost, double* psel_sum, int64_t* ipsel, int nthreads,
+                 int rank, int nranks, dre_counters* out) {
+  Ctx& c = o->c;
+  const int L = c.L, N = c.N;
+  if (nthreads < 1) nthreads = 1;
+  c.records.clear();
+  dre_counters tot; memset(&tot, 0, sizeof(tot));
+  std::vector<double> dummy_lost(L, 0.0);
+  if (!lum_lost) lum_lost = dummy_lost.data();
+  // ordinal of each source among processed sources (unit numbering)
+  std::vector<int> src_ord(N, -1);
+  {
+    Th t0; th_init(t0, c, rt_type, iterations, false);
+    std::vector<double> sl(L);
+    int n = 0;
+    for (int i = 0; i < N; i++) {
+      src_lum_value(t0, i, sl);
+      double s = 0; for (int l = 0; l < L; l++) s += sl[l];
+      if (c.cchild[i] != -1 || s == 0) continue;
+      src_ord[i] = n++;
+    }
+    tot.sources = n;
+  }
+  int chunk = std::max(1, N / (nthreads * nthreads));
+  int failed = 0;
+  auto t_start = std::chrono::steady_clock::now();
+#pragma omp parallel num_threads(nthreads)
+  {
+    Th t; th_init(t, c, rt_type, iterations, nthreads > 1);
+    t.u_fest = u_fest; t.u_accum = u_accum; t.scaspe = scaspe; t.scaspe_prev = scaspe_prev; t.scaspe_tot = nullptr;
+    std::vector<double> src_lum(L);
+#pragma omp for schedule(dynamic, chunk)
+    for (int i = 0; i < N; i++) {
+      if (failed) continue;
+      if (src_ord[i] < 0) continue;
+      src_lum_value(t, i, src_lum);
+      int src_id = i;
+      t.ipsel_av = 0; t.psel_av = 0;
+      calc_src_ccoord(t, i);
+      int sid = (rt_type == DRE_RTT_DIR_SRC) ? N + c.src_cell[i] : i;
+      cindex_to_ccindd(c, src_id, c.lvl[src_id], t.ccindd_nc);
+      if (rt_type == DRE_RTT_SCATT)  // assign_scaspe_temp_arr :1161-1163
+        for (int il = 0; il < L; il++)
+          for (int p = 0; p < c.npix_arr[il]; p++) t.scaspe_temp_arr[il][p] = scaspe_prev[il][p + (size_t)c.npix_arr[il] * i];
+      if (!main_dir_loop(t, src_id, src_ord[i], src_lum, lum_lost, rank, nranks)) {
+#pragma omp atomic write
+        failed = 1;
+      }
+      if (rt_type == DRE_RTT_DIR_SRC || rt_type == DRE_RTT_DIR_CELL || rt_type == DRE_RTT_SCATT) {
+        if (psel_sum) psel_sum[sid] += t.psel_av;
+        if (ipsel) ipsel[sid] += t.ipsel_av;
+      }
+    }
+#pragma omp critical
+    {
+      cnt_add(tot, t.cnt);
+      for (auto& r : t.rec) if ((int64_t)c.records.size() < c.max_records) c.records.push_back(r);
+    }
+  }
+  auto t_end = std::chrono::steady_clock::now();
+  tot.pass_ms = std::chrono::duration<double, std::milli>(t_end - t_start).count();
+  tot.kernel_ms = tot.pass_ms;
+  if (out) *out = tot;
+  if (failed) { c.err = "ray_tracing: reference STOP condition hit (negative length / cell not found)"; return 2; }
+  return 0;
+}
+
+// rt_loop_iobs rt_routines.f90:1470-1603
+int orc_run_iobs(orc_ctx* o, int rt_type, const double* const* scaspe_tot, int32_t ndir_in, const double* ccoord_obs,
+                 double* i_obs, double* i_obs_in, int nthreads, dre_counters* out) {
+  Ctx& c = o->c;
+  const int L = c.L, N = c.N, S = c.S;
+  if (nthreads < 1) nthreads = 1;
+  c.records.clear();
+  dre_counters tot; memset(&tot, 0, sizeof(tot));
+  if (rt_type == DRE_RTT_I_OBS) {  // calc_total_luminosity_sca case(rtt_i_obs) :760-771
+    c.lumcell.assign((size_t)L * N, 0.0);
+    for (int i = 0; i < N; i++) {
+      if (c.cchild[i] != -1) continue;
+      for (int j = 0; j < L; j++) {
+        double s = 0;
+        for (int p = 0; p < c.npix_arr[j]; p++) s += scaspe_tot[j][p + (size_t)c.npix_arr[j] * i];
+        c.lumcell[j + (size_t)L * i] = s;
+      }
+    }
+  }
+  std::vector<int> src_ord(N, -1);
+  {
+    Th t0; th_init(t0, c, rt_type, 0, false);
+    std::vector<double> sl(L); int n = 0;
+    for (int i = 0; i < N; i++) {
+      src_lum_value(t0, i, sl);
+      double s = 0; for (int l = 0; l < L; l++) s += sl[l];
+      if (c.cchild[i] != -1 || s == 0) continue;
+      src_ord[i] = n++;
+    }
+    tot.sources = n;
+  }
+  const int ndir = c.ndir;
+  const int nunit = ndir + ndir_in;
+  int chunk = std::max(1, N / (nthreads * nthreads));
+  int failed = 0;
+  auto t_start = std::chrono::steady_clock::now();
+#pragma omp parallel num_threads(nthreads)
+  {
+    Th t; th_init(t, c, rt_type, 0, nthreads > 1);
+    t.u_fest = nullptr; t.u_accum = nullptr; t.scaspe = nullptr; t.scaspe_prev = nullptr; t.scaspe_tot = scaspe_tot;
+    std::vector<double> src_lum_ray(L), src_lum(L);
+#pragma omp for schedule(dynamic, chunk)
+    for (int i = 0; i < N; i++) {
+      if (failed || src_ord[i] < 0) continue;
+      src_lum_value(t, i, src_lum_ray);
+      int src_id = i;
+      calc_src_ccoord(t, i);
+      int sid = (rt_type == DRE_RTT_I_OBS_DIR_SRC) ? N + c.src_cell[i] : i;
+      cindex_to_ccindd(c, src_id, c.lvl[src_id], t.ccindd_nc);
+      if (rt_type == DRE_RTT_I_OBS)
+        for (int il = 0; il < L; il++)
+          for (int p = 0; p < c.npix_arr[il]; p++) t.scaspe_temp_arr[il][p] = scaspe_tot[il][p + (size_t)c.npix_arr[il] * i];
+      t.nside = NSIDE_MIN;  // not used by i_obs deposits
+      for (int j = 0; j < ndir; j++) {
+        std::fill(t.i_obs_temp.begin(), t.i_obs_temp.end(), 0.0);
+        double theta = c.dir_i_out[j], phi = c.dir_i_out[ndir + j];
+        if (rt_type == DRE_RTT_I_OBS)
+          for (int il = 0; il < L; il++) src_lum_ray[il] = t.scaspe_temp_arr[il][c.npix_hp_arr[il] + j] * c.npix_hp_arr[il];
+        int clvl = c.lvl[src_id];
+        t.unit = src_ord[i] * nunit + j; t.step = 0; t.ray_ord = 0;
+        if (!ray_tracing(t, src_id, phi, theta, clvl, src_lum_ray, 0., 0., 0, RT_IOBS, 0, src_id)) {
+#pragma omp atomic write
+          failed = 1;
+        }
+        double* dst = i_obs + (size_t)L * (sid + (size_t)(N + S) * j);
+        for (int l = 0; l < L; l++) dst[l] += t.i_obs_temp[l];
+      }
+      for (int j = 0; j < ndir_in; j++) {
+        std::fill(t.i_obs_temp.begin(), t.i_obs_temp.end(), 0.0);
+        // find_theta_phi_obs_in rt_routines.f90:3164-3217
+        double vec[3], theta, phi;
+        for (int a = 0; a < 3; a++) vec[a] = ccoord_obs[3 * (size_t)j + a] - t.src_ccoord[a];
+        t.vec_mod = sqrt(vec[0] * vec[0] + vec[1] * vec[1] + vec[2] * vec[2]);
+        const double E8 = (double)1E-8f;
+        if (t.vec_mod > E8) {
+          double theta_ratio = (0 * vec[0] + 0 * vec[1] + 1 * vec[2]) / t.vec_mod;
+          if (fabs(theta_ratio - 1.0) < E8) theta_ratio = 1.0;
+          if (fabs(theta_ratio + 1.0) < E8) theta_ratio = -1.0;
+          theta = acos(theta_ratio);
+          double vec_xy = sin(theta), phi_ratio;
+          if (vec_xy > E8) phi_ratio = vec[0] / (t.vec_mod * vec_xy); else phi_ratio = 1.;
+          if (fabs(phi_ratio - 1.0) < E8) phi_ratio = 1.0;
+          if (fabs(phi_ratio + 1.0) < E8) phi_ratio = -1.0;
+          phi = acos(phi_ratio);
+          if (vec[1] < 0) phi = 2 * PI - phi;
+        } else { theta = 0; phi = 0; t.vec_mod = 0; }
+        if (rt_type == DRE_RTT_I_OBS) { assign_src_lum(t, theta, phi, src_lum); src_lum_ray = src_lum; }
+        int clvl = c.lvl[src_id];
+        t.unit = src_ord[i] * nunit + ndir + j; t.step = 0; t.ray_ord = 0;
+        if (!ray_tracing(t, src_id, phi, theta, clvl, src_lum_ray, 0., 0., 0, RT_IOBS_IN, 0, src_id)) {
+#pragma omp atomic write
+          failed = 1;
+        }
+        double* dst = i_obs_in + (size_t)L * (sid + (size_t)(N + S) * j);
+        for (int l = 0; l < L; l++) dst[l] += t.i_obs_temp[l];
+      }
+    }
+#pragma omp critical
+    {
+      cnt_add(tot, t.cnt);
+      for (auto& r : t.rec) if ((int64_t)c.records.size() < c.max_records) c.records.push_back(r);
+    }
+  }
+  auto t_end = std::chrono::steady_clock::now();
+  tot.pass_ms = std::chrono::duration<double, std::milli>(t_end - t_start).count();
+  tot.kernel_ms = tot.pass_ms;
+  if (out) *out = tot;
+  if (failed) { c.err = "ray_tracing: reference STOP condition hit"; return 2; }
+  return 0;
+}
+
+// rt_prepare(rtt_scatt) dartray_hub.f90:432-457 + calc_total_luminosity_sca rt_routines.f90:663-758
+// (no_communications + sequential_scattering).  lumcell is stored in the context for the next pass.
+int orc_prepare_scatt(orc_ctx* o, int iterations, double conv_en_lim, double* u_fest, const double* u_final,
+                      double* lum_lost_prev, const double* lum_lost, double* const* scaspe, double* const* scaspe_prev,
+                      double* const* scaspe_tot, double* tot_rad_en, int32_t* cnflag) {
+  Ctx& c = o->c;
+  const int L = c.L, N = c.N;
+  memcpy(u_fest, u_final, sizeof(double) * (size_t)L * N);
+  if (lum_lost_prev && lum_lost) memcpy(lum_lost_prev, lum_lost, sizeof(double) * L);
+  for (int l = 0; l < L; l++) memcpy(scaspe_prev[l], scaspe[l], sizeof(double) * (size_t)c.npix_arr[l] * N);
+  if (iterations == 1) {
+    for (int i = 0; i < L; i++) {
+      double s = 0;   // sum(scaspe_arr(k)%a(0:npix_hp-1,:)) : column-major order
+      for (int cc = 0; cc < N; cc++) for (int p = 0; p < c.npix_hp_arr[i]; p++) s += scaspe[i][p + (size_t)c.npix_arr[i] * cc];
+      tot_rad_en[i] = s;
+    }
+  }
+  c.lumcell.assign((size_t)L * N, 0.0);
+  for (int i = 0; i < N; i++) {
+    if (c.cchild[i] != -1) continue;
+    for (int j = 0; j < L; j++) {
+      double s = 0;
+      for (int p = 0; p < c.npix_hp_arr[j]; p++) s += scaspe[j][p + (size_t)c.npix_arr[j] * i];
+      c.lumcell[j + (size_t)L * i] = s;
+    }
+  }
+  double sum_tot = 0; for (int i = 0; i < L; i++) sum_tot += tot_rad_en[i];
+  int flag;
+  if (sum_tot > 0) {
+    flag = 1;
+    for (int i = 0; i < L; i++) {
+      double tl = 0; for (int cc = 0; cc < N; cc++) tl += c.lumcell[i + (size_t)L * cc];
+      if (!(tl / tot_rad_en[i] < conv_en_lim)) flag = 0;
+    }
+  } else flag = 1;
+  *cnflag = flag;
+  if (iterations > 1)
+    for (int l = 0; l < L; l++) { size_t n = (size_t)c.npix_arr[l] * N; for (size_t k = 0; k < n; k++) scaspe_tot[l][k] += scaspe[l][k]; }
+  for (int l = 0; l < L; l++) memset(scaspe[l], 0, sizeof(double) * (size_t)c.npix_arr[l] * N);
+  return 0;
+}
+
+int orc_get_lumcell(orc_ctx* o, double* out) { memcpy(out, o->c.lumcell.data(), sizeof(double) * o->c.lumcell.size()); return 0; }
+
+void orc_pix2ang_nest(int nside, int n, const int32_t* ipix, double* theta, double* phi) {
+  hp_init();
+  for (int i = 0; i < n; i++) pix2ang_nest(nside, ipix[i], theta[i], phi[i]);
+}
+void orc_ang2pix_nest(int nside, int n, const double* theta, const double* phi, int32_t* ipix) {
+  hp_init();
+  for (int i = 0; i < n; i++) ipix[i] = ang2pix_nest(nside, theta[i], phi[i]);
+}
+void orc_pix2vec(int nside, int n, const int32_t* ipix, double* vec) {
+  hp_init();
+  for (int i = 0; i < n; i++) { double th, ph; pix2ang_nest(nside, ipix[i], th, ph); calc_cproj(ph, th, vec + 3 * (size_t)i); }
+}
+int orc_cindex_roundtrip(orc_ctx* o, int32_t cell, int32_t* cell_out, int32_t* lvl_out) {
+  int cc[3][MAXL + 1]; memset(cc, 0, sizeof(cc));
+  cindex_to_ccindd(o->c, cell, o->c.lvl[cell], cc);
+  int a, b; bool ok = ccindd_to_cc(o->c, cc, a, b);
+  *cell_out = ok ? a : -1; *lvl_out = ok ? b : -1; return 0;
+}
+// find_cc_new2 for arbitrary points: src=(0,0,0), prev=1, cproj=point
+int orc_locate_points(orc_ctx* o, int32_t npts, const double* xyz, const int32_t* cc_old, int32_t* cell_out) {
+  Th t; th_init(t, o->c, DRE_RTT_DIR_CELL, 0, false);
+  t.src_ccoord[0] = t.src_ccoord[1] = t.src_ccoord[2] = 0;
+  for (int i = 0; i < npts; i++) {
+    int cc_new = -1, clvl = 0; bool out = false;
+    bool ok = find_cc_new2(t, cc_old[i], cc_new, xyz + 3 * (size_t)i, 1.0, out, clvl);
+    cell_out[i] = (out || !ok) ? -1 : cc_new;
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,166 @@
+"""ctypes binding of the CPU oracle (oracle/dartray_oracle.cpp).
+
+TEST INFRASTRUCTURE: import only from tests/, __graft_entry__.smoke() and bench.py's CPU legs.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(_HERE))
+from dartray_b200 import abi  # noqa: E402
+
+_LIB = os.path.join(_HERE, "_build", "liboracle.so")
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "dartray_oracle.cpp")
+    if force or not os.path.exists(_LIB) or (os.path.exists(src) and os.path.getmtime(_LIB) < os.path.getmtime(src)):
+        os.makedirs(os.path.dirname(_LIB), exist_ok=True)
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_LIB)
+        _lib.orc_create.restype = C.c_void_p
+        _lib.orc_last_error.restype = C.c_char_p
+        for n in ("orc_destroy", "orc_last_error", "orc_set_grid", "orc_set_opacity", "orc_set_sources", "orc_set_params",
+                  "orc_set_record", "orc_get_records", "orc_run_pass", "orc_run_iobs", "orc_prepare_scatt",
+                  "orc_get_lumcell", "orc_cindex_roundtrip", "orc_locate_points"):
+            getattr(_lib, n).argtypes = None
+    return _lib
+
+
+class State:
+    """Host copies of the accumulators of the path (u_fest_arr, u_final_arr, scaspe_arr, ...)."""
+
+    def __init__(self, scene):
+        N, L = scene.grid.ncell, scene.lnum
+        self.u_fest = np.zeros((N, L))
+        self.u_final = np.zeros((N, L))
+        self.scaspe = [np.zeros((N, int(p))) for p in scene.npix]
+        self.scaspe_prev = [np.zeros((N, int(p))) for p in scene.npix]
+        self.scaspe_tot = [np.zeros((N, int(p))) for p in scene.npix]
+        self.lum_lost = np.zeros(L)
+        self.lum_lost_prev = np.zeros(L)
+        self.psel_sum = np.zeros(N + scene.nsrc)
+        self.ipsel = np.zeros(N + scene.nsrc, dtype=np.int64)
+        self.tot_rad_en = np.zeros(L)
+        self.i_obs = np.zeros((scene.ndir, N + scene.nsrc, L))
+        nin = scene.ccoord_obs.shape[0]
+        self.i_obs_in = np.zeros((max(nin, 1), N + scene.nsrc, L))
+        self.lumcell = scene.lumcell.copy()
+
+
+class Oracle:
+    def __init__(self, scene, nthreads=1):
+        self.scene = scene
+        self.nthreads = nthreads
+        self.l = lib()
+        self.h = C.c_void_p(self.l.orc_create())
+        g = scene.grid
+        base = (C.c_int32 * 2)(*g.base)
+        self._keep = [g.cchild, g.lvl, g.cindex, g.ccoord, g.csize]
+        self.l.orc_set_grid(self.h, C.c_int32(g.ncell), C.c_int32(g.max_lvl), base, abi.iptr(g.cchild), abi.iptr(g.lvl),
+                            abi.lptr(g.cindex), abi.dptr(g.ccoord), abi.dptr(g.csize), abi.dptr(g.csize_arr),
+                            abi.dptr(g.carea_arr), abi.dptr(g.cvol_arr))
+        self.l.orc_set_opacity(self.h, C.c_int32(scene.lnum), abi.dptr(scene.dens_arr), abi.dptr(scene.ksca_norm),
+                               abi.dptr(scene.gsca), abi.iptr(scene.kp_sca), C.c_int32(scene.ndir), abi.dptr(scene.dir_i_out))
+        self.set_sources(scene.lumcell)
+
+    def __del__(self):
+        try:
+            self.l.orc_destroy(self.h)
+        except Exception:
+            pass
+
+    def set_sources(self, lumcell):
+        s = self.scene
+        lumcell = np.ascontiguousarray(lumcell)
+        self.l.orc_set_sources(self.h, abi.dptr(lumcell), C.c_int32(s.nsrc), abi.dptr(s.ccoord_p_src), abi.dptr(s.lum_p_src),
+                               abi.iptr(s.src_cell), abi.iptr(s.cell_src))
+
+    def set_record(self, n):
+        self.l.orc_set_record(self.h, C.c_int64(n))
+
+    def records(self):
+        n = C.c_int64(0)
+        self.l.orc_get_records(self.h, None, C.c_int64(0), C.byref(n))
+        out = np.zeros(n.value, dtype=abi.ISECT_DTYPE)
+        if n.value:
+            self.l.orc_get_records(self.h, out.ctypes.data_as(C.c_void_p), C.c_int64(n.value), C.byref(n))
+        return out
+
+    def run_pass(self, rt_type, iterations, st, rank=0, nranks=1, nthreads=None):
+        p = abi.make_params(self.scene, rt_type)
+        self.l.orc_set_params(self.h, C.byref(p))
+        cnt = abi.Counters()
+        precalc = rt_type in (abi.RTT_PRECALC_CELL, abi.RTT_PRECALC_SRC)
+        accum = st.u_fest if precalc else st.u_final
+        rc = self.l.orc_run_pass(self.h, C.c_int(rt_type), C.c_int(iterations), abi.dptr(st.u_fest), abi.dptr(accum),
+                                 abi.plane_ptrs(st.scaspe), abi.plane_ptrs(st.scaspe_prev), abi.dptr(st.lum_lost),
+                                 abi.dptr(st.psel_sum), abi.lptr(st.ipsel), C.c_int(nthreads or self.nthreads),
+                                 C.c_int(rank), C.c_int(nranks), C.byref(cnt))
+        if rc != 0:
+            raise RuntimeError(self.l.orc_last_error(self.h).decode())
+        return cnt
+
+    def run_iobs(self, rt_type, st, nthreads=None):
+        p = abi.make_params(self.scene, rt_type)
+        self.l.orc_set_params(self.h, C.byref(p))
+        cnt = abi.Counters()
+        obs = np.ascontiguousarray(self.scene.ccoord_obs, dtype=np.float64)
+        rc = self.l.orc_run_iobs(self.h, C.c_int(rt_type), abi.plane_ptrs(st.scaspe_tot), C.c_int32(obs.shape[0]),
+                                 abi.dptr(obs), abi.dptr(st.i_obs), abi.dptr(st.i_obs_in),
+                                 C.c_int(nthreads or self.nthreads), C.byref(cnt))
+        if rc != 0:
+            raise RuntimeError(self.l.orc_last_error(self.h).decode())
+        return cnt
+
+    def prepare_scatt(self, iterations, st):
+        flag = C.c_int32(0)
+        self.l.orc_prepare_scatt(self.h, C.c_int(iterations), C.c_double(self.scene.conv_en_lim), abi.dptr(st.u_fest),
+                                 abi.dptr(st.u_final), abi.dptr(st.lum_lost_prev), abi.dptr(st.lum_lost),
+                                 abi.plane_ptrs(st.scaspe), abi.plane_ptrs(st.scaspe_prev), abi.plane_ptrs(st.scaspe_tot),
+                                 abi.dptr(st.tot_rad_en), C.byref(flag))
+        self.l.orc_get_lumcell(self.h, abi.dptr(st.lumcell))
+        return bool(flag.value)
+
+    def pix2ang(self, nside, ipix):
+        ipix = np.ascontiguousarray(ipix, dtype=np.int32)
+        th = np.zeros(len(ipix)); ph = np.zeros(len(ipix))
+        self.l.orc_pix2ang_nest(C.c_int(nside), C.c_int(len(ipix)), abi.iptr(ipix), abi.dptr(th), abi.dptr(ph))
+        return th, ph
+
+    def ang2pix(self, nside, th, ph):
+        th = np.ascontiguousarray(th); ph = np.ascontiguousarray(ph)
+        out = np.zeros(len(th), dtype=np.int32)
+        self.l.orc_ang2pix_nest(C.c_int(nside), C.c_int(len(th)), abi.dptr(th), abi.dptr(ph), abi.iptr(out))
+        return out
+
+    def pix2vec(self, nside, ipix):
+        ipix = np.ascontiguousarray(ipix, dtype=np.int32)
+        v = np.zeros((len(ipix), 3))
+        self.l.orc_pix2vec(C.c_int(nside), C.c_int(len(ipix)), abi.iptr(ipix), abi.dptr(v))
+        return v
+
+    def locate(self, xyz, cc_old):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64); cc_old = np.ascontiguousarray(cc_old, dtype=np.int32)
+        out = np.zeros(len(cc_old), dtype=np.int32)
+        self.l.orc_locate_points(self.h, C.c_int32(len(cc_old)), abi.dptr(xyz), abi.iptr(cc_old), abi.iptr(out))
+        return out
+
+    def cindex_roundtrip(self, cell):
+        a = C.c_int32(0); b = C.c_int32(0)
+        self.l.orc_cindex_roundtrip(self.h, C.c_int32(int(cell)), C.byref(a), C.byref(b))
+        return a.value, b.value
