@@ -1,0 +1,906 @@
+// dre_engine.cu — host side of the B200 ray-tracing engine and its C ABI (include/dartray_engine.h).
+//
+// Replaces rt_loop / rt_loop_iobs / rt_mpi of DART-Ray (rt_routines.f90:985-1058, :1470-1603,
+// io_routines.f90:3667-3881).  No CPU fallback: every entry point that computes runs CUDA kernels.
+#include <algorithm>
+#include <dlfcn.h>
+#include "dre_host.h"
+#include "dre_lists.cuh"
+#include "dre_kernels.cuh"
+
+namespace {
+
+// ---- minimal NCCL binding (resolved with dlopen so the library loads without NCCL) --------
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[DRE_NCCL_ID_BYTES]; } ncclUniqueId;
+struct Nccl {
+  void* h = nullptr;
+  int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool load(std::string& err) {
+    if (h) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+    if (!h) { err = std::string("cannot load NCCL: ") + dlerror(); return false; }
+    GetUniqueId = (int (*)(ncclUniqueId*))dlsym(h, "ncclGetUniqueId");
+    CommInitRank = (int (*)(ncclComm_t*, int, ncclUniqueId, int))dlsym(h, "ncclCommInitRank");
+    AllReduce = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))dlsym(h, "ncclAllReduce");
+    CommDestroy = (int (*)(ncclComm_t))dlsym(h, "ncclCommDestroy");
+    GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+    if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy) { err = "NCCL symbols missing"; return false; }
+    return true;
+  }
+};
+Nccl g_nccl;
+const int NCCL_FLOAT64 = 8, NCCL_INT64 = 4, NCCL_SUM = 0;   // ncclDataType_t / ncclRedOp_t values (nccl.h)
+
+inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
+
+}  // namespace
+
+struct dre_engine {
+  int device = 0, rank = 0, nranks = 1;
+  cudaStream_t st = nullptr;
+  ncclComm_t comm = nullptr;
+  std::string err;
+  int sm_count = 148;
+  // static inputs
+  DreDev g;
+  bool have_grid = false, have_opacity = false, have_sources = false, have_params = false;
+  DBuf<int> cchild, src_cell, ik_sca, npix_hp, npix, off; DBuf<unsigned char> lvl; DBuf<long long> cindex;
+  DBuf<double> ccoord, csize, dens, ksca, gsca, lumcell, ccoord_p_src, lum_p_src;
+  DBuf<unsigned short> lamof;
+  DBuf<DreDir> class_dir[DRE_MAXCLASS], dirtab[DRE_MAXK + 1], obs_dir;
+  std::vector<int> h_npix, h_npix_hp, h_off, h_ik, h_cell_src;
+  std::vector<double> h_dir_i_out;
+  int S = 0;
+  // device-resident accumulators
+  DBuf<double> acc, prev, tot, u_fest, lum_lost, lum_lost_prev, psel_sum, psel_av, i_obs, i_obs_in, tmp_d, red_d;
+  DBuf<long long> ipsel;
+  int i_obs_ndir_in = 0;
+  DBuf<unsigned long long> counters;
+  DBuf<int> errflag, srcflag, srcpos, srclist, counter, active;
+  int nsrc_list = 0;
+  // record
+  long long rec_cap = 0; DBuf<dre_isect> rec; DBuf<unsigned long long> rec_n;
+  // wavefront scratch
+  ListStore H[2], W[2], OUT;
+  DBuf<int> u_nc, u_gid, u_nk, u_step, u_mode, u_task_seg;
+  DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, leader, unit_of_ext, ntask, nreco,
+      task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
+  DBuf<DreTask> tasks;
+  // options
+  int opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 8, opt_ctas_per_sm = 1, opt_dir_kmax = 9;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  double last_kernel_ms = 0;
+  long long last_launches = 0;
+
+  size_t rows_elems() const { return (size_t)g.N * g.ROW; }
+};
+
+namespace {
+
+// exclusive scan of n ints into out[0..n] (out[n] = total); recursion over tile sums
+__global__ void k_scan_top(const int* sums, int* scanned) { scanned[0] = 0; scanned[1] = sums[0]; }
+void scan_level(dre_engine* e, const int* in, int* out, int n, int level) {
+  DRE_REQUIRE(level < 3, "scan: input too large");
+  const int nb = cdiv(n, SCAN_TILE);
+  e->scan_tmp[level].ensure((size_t)2 * nb + 8);
+  int* sums = e->scan_tmp[level].p;
+  int* scanned = sums + nb;
+  k_scan_tile<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, sums, n);
+  if (nb == 1) k_scan_top<<<1, 1, 0, e->st>>>(sums, scanned);
+  else scan_level(e, sums, scanned, nb, level + 1);
+  k_scan_add<<<cdiv((size_t)n + 1, 256), 256, 0, e->st>>>(out, scanned, n, nb);
+}
+void scan(dre_engine* e, const int* in, int* out, int n) {
+  if (n <= 0) { k_set_int<<<1, 1, 0, e->st>>>(out, 0); return; }
+  scan_level(e, in, out, n, 0);
+}
+
+int read_int(dre_engine* e, const int* d) {
+  int v = 0; CK(cudaMemcpyAsync(&v, d, sizeof(int), cudaMemcpyDeviceToHost, e->st)); CK(cudaStreamSynchronize(e->st)); return v;
+}
+
+void build_dir_table(dre_engine* e, int k) {
+  if (e->dirtab[k].p) return;
+  const int nside = 1 << k; const size_t np = (size_t)12 * nside * nside;
+  std::vector<DreDir> t(np);
+  for (size_t p = 0; p < np; p++) { double th, ph; hp::pix2ang_nest(nside, (int)p, th, ph); t[p] = hp::make_dir(th, ph); }
+  e->dirtab[k].upload(t.data(), np, e->st);
+  CK(cudaStreamSynchronize(e->st));
+  e->g.dirtab[k] = e->dirtab[k].p;
+  if (k > e->g.dir_kmax) e->g.dir_kmax = k;
+}
+
+}  // namespace
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+#define DRE_TRY(e) try {
+#define DRE_CATCH(e) } catch (const DreError& x) { (e)->err = x.msg; return 1; } catch (const std::exception& x) { (e)->err = x.what(); return 1; } return 0;
+
+extern "C" {
+
+int dre_get_unique_id(void* id128) {
+  std::string err;
+  if (!g_nccl.load(err)) return 1;
+  ncclUniqueId id; memset(&id, 0, sizeof(id));
+  if (g_nccl.GetUniqueId(&id) != 0) return 2;
+  memcpy(id128, &id, DRE_NCCL_ID_BYTES);
+  return 0;
+}
+
+int dre_create(dre_engine** out, int device, int rank, int nranks, const void* nccl_id128) {
+  if (!out) return 1;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    fprintf(stderr, "dre_create: no CUDA device (the engine has no CPU path)\n");
+    return 2;
+  }
+  dre_engine* e = new dre_engine();
+  memset(&e->g, 0, sizeof(e->g));
+  e->g.dir_kmax = -1;
+  e->device = device; e->rank = rank; e->nranks = nranks < 1 ? 1 : nranks;
+  try {
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device));
+    e->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CK(cudaEventCreate(&e->ev[i]));
+    e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->counter.zero(4, e->st); e->active.zero(1, e->st);
+    e->rec_n.zero(1, e->st);
+    if (e->nranks > 1) {
+      DRE_REQUIRE(nccl_id128 != nullptr, "dre_create: nranks > 1 needs an NCCL unique id");
+      std::string err;
+      DRE_REQUIRE(g_nccl.load(err), err.c_str());
+      ncclUniqueId id; memcpy(&id, nccl_id128, DRE_NCCL_ID_BYTES);
+      const int rc = g_nccl.CommInitRank(&e->comm, e->nranks, id, rank);
+      DRE_REQUIRE(rc == 0, "ncclCommInitRank failed");
+    }
+    CK(cudaStreamSynchronize(e->st));
+  } catch (const DreError& x) {
+    fprintf(stderr, "dre_create: %s\n", x.msg.c_str());
+    delete e; return 3;
+  }
+  *out = e;
+  return 0;
+}
+
+void dre_destroy(dre_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  cudaDeviceSynchronize();
+  if (e->comm) g_nccl.CommDestroy(e->comm);
+  for (int i = 0; i < 4; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+  if (e->st) cudaStreamDestroy(e->st);
+  delete e;
+}
+
+const char* dre_last_error(const dre_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2], const int32_t* cchild,
+                 const int32_t* lvl, const int64_t* cindex, const double* ccoord, const double* csize,
+                 const double* csize_arr, const double* carea_arr, const double* cvol_arr) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(N > 1 && max_lvl >= 1, "dre_set_grid: empty grid");
+  DRE_REQUIRE(max_lvl <= DRE_MAXLVL, "dre_set_grid: max_lvl > 8 not supported");
+  DRE_REQUIRE(base[0] >= 2 && base[1] >= 2 && base[0] < 256 && base[1] < 256, "dre_set_grid: base out of range");
+  DreDev& g = e->g;
+  g.N = N; g.max_lvl = max_lvl; g.base[0] = base[0]; g.base[1] = base[1];
+  for (int i = 0; i < 2; i++) {   // set_base smooth_grid_routines.f90:622-649
+    int j = 0; const long long b3 = (long long)base[i] * base[i] * base[i];
+    while (!(b3 < (1ll << j))) j++;
+    g.basediv[i] = 1ll << j; g.basemask[i] = (int)(g.basediv[i] - 1);
+  }
+  std::vector<unsigned char> l8(N);
+  for (int i = 0; i < N; i++) { DRE_REQUIRE(lvl[i] >= 0 && lvl[i] <= max_lvl, "dre_set_grid: lvl out of range"); l8[i] = (unsigned char)lvl[i]; }
+  e->cchild.upload(cchild, N, e->st); e->lvl.upload(l8.data(), N, e->st);
+  e->cindex.upload((const long long*)cindex, N, e->st);
+  e->ccoord.upload(ccoord, 3 * (size_t)N, e->st); e->csize.upload(csize, N, e->st);
+  CK(cudaStreamSynchronize(e->st));
+  g.cchild = e->cchild.p; g.lvl = e->lvl.p; g.cindex = e->cindex.p; g.ccoord = e->ccoord.p; g.csize = e->csize.p;
+  for (int i = 0; i <= max_lvl; i++) { g.csize_arr[i] = csize_arr[i]; g.carea_arr[i] = carea_arr[i]; g.cvol_arr[i] = cvol_arr[i]; }
+  e->have_grid = true; e->have_opacity = false; e->have_sources = false;
+  DRE_CATCH(e)
+}
+
+int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const double* ksca_arr_norm, const double* gsca_arr,
+                    const int32_t* kp_sca_arr, int32_t ndir, const double* dir_i_out) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_grid, "dre_set_opacity: call dre_set_grid first");
+  DRE_REQUIRE(L >= 1 && L <= 32 * DRE_KL, "dre_set_opacity: lnum must be in [1,128]");
+  DRE_REQUIRE(ndir >= 0, "dre_set_opacity: negative tot_ndir_scaspe");
+  DreDev& g = e->g;
+  const int N = g.N;
+  g.L = L; g.KLn = (L + 31) / 32; g.ndir = ndir;
+  e->dens.upload(dens_arr, (size_t)L * N, e->st); e->ksca.upload(ksca_arr_norm, L, e->st); e->gsca.upload(gsca_arr, L, e->st);
+  // classes: set_npix_arr rt_routines.f90:5289-5311
+  e->h_npix.assign(L, 0); e->h_npix_hp.assign(L, 0); e->h_off.assign(L, 0); e->h_ik.assign(L, -1);
+  int kmax = -1;
+  for (int l = 0; l < L; l++) {
+    DRE_REQUIRE(kp_sca_arr[l] >= -1 && kp_sca_arr[l] <= DRE_NSIDE_MIN_K, "dre_set_opacity: kp_sca must be in [-1,2]");
+    e->h_npix_hp[l] = kp_sca_arr[l] < 0 ? 1 : 12 * (1 << (2 * kp_sca_arr[l]));
+    e->h_npix[l] = e->h_npix_hp[l] + ndir;
+    kmax = std::max(kmax, kp_sca_arr[l]);
+  }
+  g.nclass = 0;
+  for (int k = 0; k <= kmax; k++) {
+    bool used = false;
+    for (int l = 0; l < L; l++) if (kp_sca_arr[l] == k) used = true;
+    if (!used) continue;
+    const int ic = g.nclass++;
+    for (int l = 0; l < L; l++) if (kp_sca_arr[l] == k) e->h_ik[l] = ic;
+    const int nhp = 12 * (1 << (2 * k)), np = nhp + ndir;
+    g.class_kp[ic] = k; g.class_nhp[ic] = nhp; g.class_np[ic] = np;
+    std::vector<DreDir> d(np);   // create_scaspe rt_routines.f90:2827-2848
+    for (int j = 0; j < nhp; j++) { double th, ph; hp::pix2ang_nest(1 << k, j, th, ph); d[j] = hp::make_dir(th, ph); }
+    for (int j = 0; j < ndir; j++) d[nhp + j] = hp::make_dir(dir_i_out[j], dir_i_out[ndir + j]);
+    e->class_dir[ic].upload(d.data(), np, e->st);
+    CK(cudaStreamSynchronize(e->st));
+    g.class_dir[ic] = e->class_dir[ic].p;
+  }
+  // accumulator row layout: [0,L) u_final, then one even-padded block per wavelength
+  int off = L + (L & 1);
+  for (int l = 0; l < L; l++) { e->h_off[l] = off; off += e->h_npix[l] + (e->h_npix[l] & 1); }
+  g.ROW = off;
+  DRE_REQUIRE(g.ROW < 65536, "dre_set_opacity: accumulator row too long");
+  std::vector<unsigned short> lam(g.ROW, 0);
+  for (int l = 0; l < L; l++) lam[l] = (unsigned short)l;
+  for (int l = 0; l < L; l++) for (int p = 0; p < e->h_npix[l] + (e->h_npix[l] & 1); p++) lam[e->h_off[l] + p] = (unsigned short)(L + l);
+  e->lamof.upload(lam.data(), g.ROW, e->st);
+  e->ik_sca.upload(e->h_ik.data(), L, e->st); e->npix_hp.upload(e->h_npix_hp.data(), L, e->st);
+  e->npix.upload(e->h_npix.data(), L, e->st); e->off.upload(e->h_off.data(), L, e->st);
+  e->h_dir_i_out.assign(dir_i_out, dir_i_out + 2 * (size_t)ndir);
+  std::vector<DreDir> od(std::max(ndir, 1));
+  for (int j = 0; j < ndir; j++) od[j] = hp::make_dir(dir_i_out[j], dir_i_out[ndir + j]);
+  e->obs_dir.upload(od.data(), od.size(), e->st);
+  CK(cudaStreamSynchronize(e->st));
+  g.dens = e->dens.p; g.ksca = e->ksca.p; g.gsca = e->gsca.p; g.ik_sca = e->ik_sca.p; g.npix_hp = e->npix_hp.p;
+  g.npix = e->npix.p; g.off = e->off.p; g.lamof = e->lamof.p;
+  // device-resident accumulators (zero-initialised)
+  const size_t NL = (size_t)N * L;
+  e->acc.zero(e->rows_elems(), e->st); e->prev.zero(e->rows_elems(), e->st); e->tot.zero(e->rows_elems(), e->st);
+  e->u_fest.zero(NL, e->st); e->lum_lost.zero(L, e->st); e->lum_lost_prev.zero(L, e->st);
+  e->lumcell.zero(NL, e->st); g.lumcell = e->lumcell.p;
+  CK(cudaStreamSynchronize(e->st));
+  e->have_opacity = true; e->have_sources = false;
+  DRE_CATCH(e)
+}
+
+int dre_set_sources(dre_engine* e, const double* lumcell, int32_t S, const double* ccoord_p_src, const double* lum_p_src_arr,
+                    const int32_t* src_cell, const int32_t* cell_src) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_opacity, "dre_set_sources: call dre_set_opacity first");
+  DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L;
+  if (lumcell) e->lumcell.upload(lumcell, NL, e->st); else e->lumcell.zero(NL, e->st);
+  g.lumcell = e->lumcell.p;
+  g.S = S; e->S = S;
+  if (S > 0) {
+    DRE_REQUIRE(ccoord_p_src && lum_p_src_arr && src_cell && cell_src, "dre_set_sources: point-source arrays missing");
+    e->ccoord_p_src.upload(ccoord_p_src, 3 * (size_t)S, e->st); e->lum_p_src.upload(lum_p_src_arr, (size_t)S * g.L, e->st);
+    e->src_cell.upload(src_cell, g.N, e->st);
+    e->h_cell_src.assign(cell_src, cell_src + S);
+  } else {
+    std::vector<int> none(g.N, -1);
+    e->src_cell.upload(none.data(), g.N, e->st);
+    e->ccoord_p_src.zero(3, e->st); e->lum_p_src.zero(g.L, e->st);
+  }
+  CK(cudaStreamSynchronize(e->st));
+  g.ccoord_p_src = e->ccoord_p_src.p; g.lum_p_src = e->lum_p_src.p; g.src_cell = e->src_cell.p;
+  const size_t NS = (size_t)g.N + S;
+  e->psel_sum.zero(NS, e->st); e->ipsel.zero(NS, e->st); e->psel_av.zero(NS, e->st);
+  e->have_sources = true;
+  DRE_CATCH(e)
+}
+
+int dre_set_params(dre_engine* e, const dre_params* p) {
+  DRE_TRY(e)
+  DRE_REQUIRE(p != nullptr, "dre_set_params: null");
+  DRE_REQUIRE(p->bm_par > 0 && p->bm_par_max > 0, "dre_set_params: bm_par / bm_par_max must be positive");
+  e->g.par = *p;
+  e->have_params = true;
+  DRE_CATCH(e)
+}
+
+}  // extern "C"
+
+// =========================================================================================
+// device-resident state: upload / download / zero
+// =========================================================================================
+namespace {
+double* rows_of(dre_engine* e, int which) {
+  switch (which) {
+    case DRE_ARR_SCASPE: return e->acc.p;
+    case DRE_ARR_SCASPE_PREV: return e->prev.p;
+    case DRE_ARR_SCASPE_TOT: return e->tot.p;
+  }
+  return nullptr;
+}
+void planes_io(dre_engine* e, double* rows, double* const* planes, int dir) {
+  const DreDev& g = e->g;
+  for (int l = 0; l < g.L; l++) {
+    const int P = e->h_npix[l];
+    const size_t n = (size_t)g.N * P;
+    e->tmp_d.ensure(n);
+    if (dir == 0) CK(cudaMemcpyAsync(e->tmp_d.p, planes[l], n * 8, cudaMemcpyHostToDevice, e->st));
+    k_plane_rows<<<cdiv(n, 256), 256, 0, e->st>>>(rows, e->tmp_d.p, g.N, P, g.ROW, e->h_off[l], dir);
+    if (dir == 1) CK(cudaMemcpyAsync(planes[l], e->tmp_d.p, n * 8, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+  }
+}
+void u_final_io(dre_engine* e, double* host, int dir) {
+  const DreDev& g = e->g;
+  const size_t n = (size_t)g.N * g.L;
+  e->tmp_d.ensure(n);
+  if (dir == 0) CK(cudaMemcpyAsync(e->tmp_d.p, host, n * 8, cudaMemcpyHostToDevice, e->st));
+  k_u_rows<<<cdiv(n, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, dir);
+  if (dir == 1) CK(cudaMemcpyAsync(host, e->tmp_d.p, n * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+}
+}  // namespace
+
+extern "C" {
+
+int dre_upload(dre_engine* e, int which, const void* planes) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_opacity, "dre_upload: call dre_set_opacity first");
+  DRE_REQUIRE(planes != nullptr, "dre_upload: null pointer");
+  const DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L;
+  switch (which) {
+    case DRE_ARR_U_FEST: e->u_fest.upload((const double*)planes, NL, e->st); break;
+    case DRE_ARR_U_FINAL: u_final_io(e, (double*)planes, 0); break;
+    case DRE_ARR_SCASPE: case DRE_ARR_SCASPE_PREV: case DRE_ARR_SCASPE_TOT:
+      planes_io(e, rows_of(e, which), (double* const*)planes, 0); break;
+    case DRE_ARR_LUM_LOST: e->lum_lost.upload((const double*)planes, g.L, e->st); break;
+    case DRE_ARR_LUMCELL: e->lumcell.upload((const double*)planes, NL, e->st); break;
+    default: DRE_REQUIRE(false, "dre_upload: array cannot be uploaded");
+  }
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_download(dre_engine* e, int which, void* planes) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_opacity, "dre_download: call dre_set_opacity first");
+  DRE_REQUIRE(planes != nullptr, "dre_download: null pointer");
+  const DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L, NS = (size_t)g.N + e->S;
+  switch (which) {
+    case DRE_ARR_U_FEST: CK(cudaMemcpyAsync(planes, e->u_fest.p, NL * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    case DRE_ARR_U_FINAL: u_final_io(e, (double*)planes, 1); break;
+    case DRE_ARR_SCASPE: case DRE_ARR_SCASPE_PREV: case DRE_ARR_SCASPE_TOT:
+      planes_io(e, rows_of(e, which), (double* const*)planes, 1); break;
+    case DRE_ARR_LUM_LOST: CK(cudaMemcpyAsync(planes, e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    case DRE_ARR_LUMCELL: CK(cudaMemcpyAsync(planes, e->lumcell.p, NL * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    case DRE_ARR_PSEL_AV:
+      DRE_REQUIRE(e->have_sources, "dre_download: call dre_set_sources first");
+      k_psel_ratio<<<cdiv(NS, 256), 256, 0, e->st>>>(e->psel_sum.p, e->ipsel.p, (int)NS, e->psel_av.p);
+      CK(cudaMemcpyAsync(planes, e->psel_av.p, NS * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    case DRE_ARR_I_OBS:
+      DRE_REQUIRE(e->i_obs.p, "dre_download: no i_obs pass was run");
+      CK(cudaMemcpyAsync(planes, e->i_obs.p, (size_t)g.ndir * NS * g.L * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    case DRE_ARR_I_OBS_IN:
+      DRE_REQUIRE(e->i_obs_in.p && e->i_obs_ndir_in > 0, "dre_download: no internal-observer pass was run");
+      CK(cudaMemcpyAsync(planes, e->i_obs_in.p, (size_t)e->i_obs_ndir_in * NS * g.L * 8, cudaMemcpyDeviceToHost, e->st)); break;
+    default: DRE_REQUIRE(false, "dre_download: unknown array");
+  }
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_zero(dre_engine* e, int which) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_opacity, "dre_zero: call dre_set_opacity first");
+  const DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L, NS = (size_t)g.N + e->S;
+  const size_t nsca = (size_t)g.N * (g.ROW - g.L);
+  switch (which) {
+    case DRE_ARR_U_FEST: e->u_fest.zero(NL, e->st); break;
+    case DRE_ARR_U_FINAL: e->tmp_d.zero(NL, e->st); k_u_rows<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, 0); break;
+    case DRE_ARR_SCASPE: case DRE_ARR_SCASPE_PREV: case DRE_ARR_SCASPE_TOT:
+      k_zero_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(rows_of(e, which), g.N, g.ROW, g.L); break;
+    case DRE_ARR_LUM_LOST: e->lum_lost.zero(g.L, e->st); break;
+    case DRE_ARR_PSEL_AV: e->psel_sum.zero(NS, e->st); e->ipsel.zero(NS, e->st); break;
+    case DRE_ARR_LUMCELL: e->lumcell.zero(NL, e->st); break;
+    case DRE_ARR_I_OBS: if (e->i_obs.p) e->i_obs.zero((size_t)g.ndir * NS * g.L, e->st); break;
+    case DRE_ARR_I_OBS_IN: if (e->i_obs_in.p) e->i_obs_in.zero((size_t)e->i_obs_ndir_in * NS * g.L, e->st); break;
+    default: DRE_REQUIRE(false, "dre_zero: unknown array");
+  }
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+}  // extern "C"
+
+// =========================================================================================
+// rt_loop on the device: batches of (source, sector) units advanced as one wavefront
+// =========================================================================================
+namespace {
+
+DreAccum make_accum(dre_engine* e, const double* prev_rows) {
+  DreAccum A;
+  A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
+  A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
+  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk;
+  return A;
+}
+
+void check_ready(dre_engine* e) {
+  DRE_REQUIRE(e->have_grid && e->have_opacity && e->have_sources && e->have_params,
+              "engine not configured: dre_set_grid/opacity/sources/params must all be called");
+}
+
+const char* err_text(int code) {
+  switch (code) {
+    case 1: return "ray_tracing: negative path length (rt_routines.f90:1714)";
+    case 2: return "ray_tracing: next cell not found (rt_routines.f90:1849)";
+    case 3: return "find_cc_new2: host cell not found (rt_routines.f90:2037)";
+    case 4: return "angular resolution exceeds the direction tables: raise option dir_kmax";
+    case 5: return "define_next_level: nside fell below 2";
+  }
+  return "unknown device error";
+}
+
+// build the luminous-leaf list for the current rt_type (rt_routines.f90:1016)
+int build_source_list(dre_engine* e) {
+  const DreDev& g = e->g;
+  e->srcflag.ensure(g.N); e->srcpos.ensure((size_t)g.N + 1); e->srclist.ensure(g.N);
+  k_src_flags<<<cdiv(g.N, 256), 256, 0, e->st>>>(g, e->srcflag.p);
+  scan(e, e->srcflag.p, e->srcpos.p, g.N);
+  k_src_compact<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p, e->srcpos.p, g.N, e->srclist.p);
+  e->nsrc_list = read_int(e, e->srcpos.p + g.N);
+  return e->nsrc_list;
+}
+
+int trace_warps(dre_engine* e, size_t* smem) {
+  const DreDev& g = e->g;
+  int w = std::max(1, std::min(e->opt_warps, 32));
+  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w) * e->opt_ctas_per_sm > (size_t)220 * 1024) w--;
+  *smem = dre_trace_smem_bytes(g.ROW, g.L, w);
+  DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
+  return w;
+}
+
+template <int MODE>
+void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
+  size_t smem = 0; int warps = 8;
+  if (MODE == MODE_DEP) {
+    warps = trace_warps(e, &smem);
+    CK(cudaFuncSetAttribute(k_trace<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
+  const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
+  CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
+  CK(cudaEventRecord(e->ev[2], e->st));
+  k_trace<MODE><<<ctas, warps * 32, smem, e->st>>>(e->g, A, u, H, W, e->tasks.p, nT, out, e->counter.p);
+  CK(cudaEventRecord(e->ev[3], e->st));
+  CK(cudaGetLastError());
+  e->last_launches++;
+}
+
+void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
+  const DreDev& g = e->g;
+  const int L = g.L;
+  e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
+  DreUnits u; u.nc = e->u_nc.p; u.gid = e->u_gid.p; u.nk = e->u_nk.p; u.step = e->u_step.p; u.mode = e->u_mode.p;
+  u.task_seg = e->u_task_seg.p; u.U = U;
+  for (int i = 0; i < 2; i++) { e->H[i].ensure(U, L, U); e->W[i].ensure(64, L, U); }
+  int cur = 0;
+  e->H[0].n = U; e->W[0].n = 0;
+  k_seed<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(g, u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
+  e->extcnt.ensure(U); e->ext_seg.ensure((size_t)U + 1); e->reco_cnt.ensure(U);
+  e->keptH.ensure(U); e->keptW.ensure(U); e->newHcnt.ensure(U); e->newWcnt.ensure(U);
+  const int ub = cdiv(U, 256);
+  for (;;) {
+    DreList Hc = e->H[cur].view(), Wc = e->W[cur].view();
+    const int nH = Hc.n, nW = Wc.n;
+    k_plan<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg);
+    if (nH > 0) {
+      e->selH.ensure(nH); e->posH.ensure((size_t)nH + 1);
+      k_select<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p);
+      scan(e, e->selH.p, e->posH.p, nH);
+    }
+    if (nW > 0) {
+      e->selW.ensure(nW); e->posW.ensure((size_t)nW + 1);
+      k_select<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p);
+      scan(e, e->selW.p, e->posW.p, nW);
+    }
+    k_unit_ext<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->extcnt.p);
+    scan(e, e->extcnt.p, e->ext_seg.p, U);
+    const int nExt = read_int(e, e->ext_seg.p + U);
+    int nT = 0;
+    if (nExt > 0) {
+      e->ext.ensure(nExt); e->ipx.ensure(nExt); e->gone.ensure(nExt); e->cand.ensure((size_t)3 * nExt); e->ncand.ensure(nExt);
+      e->leader.ensure(nExt); e->unit_of_ext.ensure(nExt); e->ntask.ensure(nExt); e->nreco.ensure(nExt);
+      e->task_off.ensure((size_t)nExt + 1); e->reco_off.ensure((size_t)nExt + 1);
+      const int xb = cdiv(nExt, 256);
+      if (nH > 0) k_fill_ext<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
+      if (nW > 0) k_fill_ext<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
+      k_unit_of_ext<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->unit_of_ext.p);
+      k_cand<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p);
+      k_resolve<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->cand.p, e->ncand.p, e->gone.p, e->leader.p);
+      k_count<<<xb, 256, 0, e->st>>>(Hc, u, e->ext_seg.p, e->ext.p, nExt, e->unit_of_ext.p, e->ncand.p, e->leader.p, e->ntask.p, e->nreco.p);
+      scan(e, e->ntask.p, e->task_off.p, nExt);
+      scan(e, e->nreco.p, e->reco_off.p, nExt);
+      k_unit_tasks<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->ext_seg.p, e->task_off.p, e->reco_off.p, e->reco_cnt.p);
+      nT = read_int(e, e->task_off.p + nExt);
+      if (nT > 0) {
+        e->tasks.ensure(nT); e->OUT.ensure(nT, L, 1); e->OUT.n = nT;
+        e->fH.ensure(nT); e->fW.ensure(nT); e->posOH.ensure((size_t)nT + 1); e->posOW.ensure((size_t)nT + 1);
+        k_emit_tasks<<<xb, 256, 0, e->st>>>(u, e->ext.p, nExt, e->unit_of_ext.p, e->cand.p, e->ntask.p, e->task_off.p, e->tasks.p);
+        DreList out = e->OUT.view();
+        if (mode == MODE_PRECALC) launch_trace<MODE_PRECALC>(e, A, u, Hc, Wc, nT, out);
+        else launch_trace<MODE_DEP>(e, A, u, Hc, Wc, nT, out);
+        k_out_flags<<<cdiv(nT, 256), 256, 0, e->st>>>(out, nT, e->fH.p, e->fW.p);
+        scan(e, e->fH.p, e->posOH.p, nT);
+        scan(e, e->fW.p, e->posOW.p, nT);
+      }
+    }
+    const int nx = 1 - cur;
+    k_unit_new<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->reco_cnt.p, e->posOH.p, e->posOW.p,
+                                      nExt > 0 ? 1 : 0, nT > 0 ? 1 : 0, e->keptH.p, e->keptW.p, e->newHcnt.p, e->newWcnt.p);
+    scan(e, e->newHcnt.p, e->H[nx].seg.p, U);
+    scan(e, e->newWcnt.p, e->W[nx].seg.p, U);
+    int tot2[2];
+    CK(cudaMemcpyAsync(&tot2[0], e->H[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&tot2[1], e->W[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    if (nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; }
+    const int nH2 = tot2[0], nW2 = tot2[1];
+    // the seg arrays were just written: grow the payload arrays only (seg is sized U+1 already)
+    e->H[nx].ensure(std::max(nH2, 1), L, U); e->W[nx].ensure(std::max(nW2, 1), L, U);
+    e->H[nx].n = nH2; e->W[nx].n = nW2;
+    DreList Hn = e->H[nx].view(), Wn = e->W[nx].view();
+    if (nH > 0) k_build_kept<<<cdiv(nH, 256), 256, 0, e->st>>>(Hn, Hc, e->selH.p, e->posH.p, L);
+    if (nW > 0) k_build_kept<<<cdiv(nW, 256), 256, 0, e->st>>>(Wn, Wc, e->selW.p, e->posW.p, L);
+    if (nExt > 0) k_build_reco<<<cdiv(nExt, 256), 256, 0, e->st>>>(Hn, Wc, u, e->ext.p, nExt, e->unit_of_ext.p, e->ext_seg.p, e->cand.p,
+                                                                 e->nreco.p, e->reco_off.p, e->keptH.p, L);
+    if (nT > 0) k_build_out<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
+                                                             e->keptH.p, e->keptW.p, e->reco_cnt.p, L);
+    cur = nx;
+    CK(cudaMemsetAsync(e->active.p, 0, sizeof(int), e->st));
+    k_next<<<ub, 256, 0, e->st>>>(u, Hn.seg, Wn.seg, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
+    int hv[2];
+    CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+    CK(cudaGetLastError());
+    if (hv[1] != 0) throw DreError{err_text(hv[1])};
+    if (hv[0] == 0) break;
+  }
+}
+
+void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
+  unsigned long long c[16];
+  CK(cudaMemcpyAsync(c, e->counters.p, sizeof(c), cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  if (!out) return;
+  memset(out, 0, sizeof(*out));
+  out->sources = e->nsrc_list; out->rays = c[CNT_RAYS]; out->intersections = c[CNT_ISECT]; out->deposits = c[CNT_DEP];
+  out->beam_tests = c[CNT_BEAM]; out->splits = c[CNT_SPLIT]; out->merges = c[CNT_MERGE]; out->sca_elems = c[CNT_SCA];
+  out->active_lambda = c[CNT_ACT]; out->steps = c[CNT_N]; out->isect_hash = c[CNT_HASH];
+  out->kernel_ms = e->last_kernel_ms; out->pass_ms = pass_ms;
+}
+
+void ensure_dir_tables(dre_engine* e) {
+  const int kmax = std::max(2, std::min(e->opt_dir_kmax, DRE_MAXK));
+  for (int k = 0; k <= kmax; k++) build_dir_table(e, k);
+}
+
+}  // namespace
+
+extern "C" {
+
+int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counters* out) {
+  (void)iterations;
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  int mode;
+  switch (rt_type) {
+    case DRE_RTT_PRECALC_CELL: case DRE_RTT_PRECALC_SRC: mode = MODE_PRECALC; break;
+    case DRE_RTT_DIR_CELL: case DRE_RTT_DIR_SRC: case DRE_RTT_SCATT: mode = MODE_DEP; break;
+    default: DRE_REQUIRE(false, "dre_run_pass: rt_type is not a list pass (use dre_run_iobs for i_obs types)"); mode = 0;
+  }
+  e->g.rt_type = rt_type;
+  ensure_dir_tables(e);
+  e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
+  e->last_kernel_ms = 0; e->last_launches = 0;
+  CK(cudaEventRecord(e->ev[0], e->st));
+  const int nsrc = build_source_list(e);
+  const long long total_units = (long long)nsrc * 48;
+  const long long mine = total_units > e->rank ? (total_units - e->rank + e->nranks - 1) / e->nranks : 0;
+  DreAccum A = make_accum(e, e->prev.p);
+  for (long long u0 = 0; u0 < mine; u0 += e->opt_batch_units) {
+    const int U = (int)std::min<long long>(e->opt_batch_units, mine - u0);
+    run_batch(e, mode, A, (int)u0, U);
+  }
+  CK(cudaEventRecord(e->ev[1], e->st));
+  CK(cudaStreamSynchronize(e->st));
+  float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));
+  fill_counters(e, out, ms);
+  DRE_CATCH(e)
+}
+
+}  // extern "C"
+
+// =========================================================================================
+// drop-in calls with host arrays, rt_loop_iobs, rt_mpi, rt_prepare(rtt_scatt)
+// =========================================================================================
+extern "C" {
+
+int dre_run_pass(dre_engine* e, int rt_type, int iterations, const double* u_fest, double* u_accum, double* const* scaspe,
+                 const double* const* scaspe_prev, double* lum_lost, double* psel_av, dre_counters* out) {
+  const bool precalc = (rt_type == DRE_RTT_PRECALC_CELL || rt_type == DRE_RTT_PRECALC_SRC);
+  int rc;
+  if (precalc) {
+    if (u_accum && (rc = dre_upload(e, DRE_ARR_U_FEST, u_accum))) return rc;
+  } else {
+    if (u_fest && (rc = dre_upload(e, DRE_ARR_U_FEST, u_fest))) return rc;
+    if (u_accum && (rc = dre_upload(e, DRE_ARR_U_FINAL, u_accum))) return rc;
+    if (scaspe && (rc = dre_upload(e, DRE_ARR_SCASPE, scaspe))) return rc;
+    if (scaspe_prev && rt_type == DRE_RTT_SCATT && (rc = dre_upload(e, DRE_ARR_SCASPE_PREV, scaspe_prev))) return rc;
+    if (lum_lost && (rc = dre_upload(e, DRE_ARR_LUM_LOST, lum_lost))) return rc;
+    if ((rc = dre_zero(e, DRE_ARR_PSEL_AV))) return rc;
+  }
+  if ((rc = dre_run_pass_resident(e, rt_type, iterations, out))) return rc;
+  if (precalc) {
+    if (u_accum && (rc = dre_download(e, DRE_ARR_U_FEST, u_accum))) return rc;
+  } else {
+    if (u_accum && (rc = dre_download(e, DRE_ARR_U_FINAL, u_accum))) return rc;
+    if (scaspe && (rc = dre_download(e, DRE_ARR_SCASPE, (void*)scaspe))) return rc;
+    if (lum_lost && (rc = dre_download(e, DRE_ARR_LUM_LOST, lum_lost))) return rc;
+    if (psel_av && (rc = dre_download(e, DRE_ARR_PSEL_AV, psel_av))) return rc;
+  }
+  return 0;
+}
+
+int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, int32_t ndir_in, const double* ccoord_obs,
+                 double* i_obs, double* i_obs_in, dre_counters* out) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  DRE_REQUIRE(rt_type == DRE_RTT_I_OBS_DIR_CELL || rt_type == DRE_RTT_I_OBS_DIR_SRC || rt_type == DRE_RTT_I_OBS,
+              "dre_run_iobs: rt_type is not an i_obs pass");
+  DRE_REQUIRE(ndir_in >= 0 && (ndir_in == 0 || ccoord_obs), "dre_run_iobs: internal observers need ccoord_obs");
+  DreDev& g = e->g;
+  g.rt_type = rt_type;
+  const int L = g.L, ndir = g.ndir;
+  const size_t NS = (size_t)g.N + e->S;
+  if (scaspe_tot && rt_type == DRE_RTT_I_OBS) planes_io(e, e->tot.p, (double* const*)scaspe_tot, 0);
+  // device i_obs arrays: "+=" semantics on the caller's arrays when given, else resident
+  const size_t n_out = (size_t)std::max(ndir, 1) * NS * L, n_in = (size_t)std::max(ndir_in, 1) * NS * L;
+  if (!e->i_obs.p || e->i_obs.cap < n_out) { e->i_obs.release(); e->i_obs.zero(n_out, e->st); }
+  if (!e->i_obs_in.p || e->i_obs_in.cap < n_in || e->i_obs_ndir_in != ndir_in) { e->i_obs_in.release(); e->i_obs_in.zero(n_in, e->st); e->i_obs_ndir_in = ndir_in; }
+  if (i_obs && ndir > 0) CK(cudaMemcpyAsync(e->i_obs.p, i_obs, (size_t)ndir * NS * L * 8, cudaMemcpyHostToDevice, e->st));
+  if (i_obs_in && ndir_in > 0) CK(cudaMemcpyAsync(e->i_obs_in.p, i_obs_in, (size_t)ndir_in * NS * L * 8, cudaMemcpyHostToDevice, e->st));
+  e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
+  e->last_kernel_ms = 0; e->last_launches = 0;
+  CK(cudaEventRecord(e->ev[0], e->st));
+  if (rt_type == DRE_RTT_I_OBS)   // calc_total_luminosity_sca case(rtt_i_obs) rt_routines.f90:760-771
+    k_lumcell_sca<<<cdiv((size_t)g.N * L, 256), 256, 0, e->st>>>(g, e->tot.p, e->lumcell.p, 1);
+  const int nsrc = build_source_list(e);
+  DreIobs q; memset(&q, 0, sizeof(q));
+  q.srclist = e->srclist.p; q.nsrc = nsrc; q.ndir = ndir; q.ndir_in = ndir_in; q.obs_dir = e->obs_dir.p;
+  q.i_obs = e->i_obs.p; q.i_obs_in = e->i_obs_in.p;
+  DBuf<DreDir> d_in_dir; DBuf<double> d_vm; DBuf<int> d_ip;
+  if (ndir_in > 0 && nsrc > 0) {
+    // find_theta_phi_obs_in rt_routines.f90:3164-3217, evaluated with the host libm
+    std::vector<int> hl(nsrc); CK(cudaMemcpy(hl.data(), e->srclist.p, (size_t)nsrc * 4, cudaMemcpyDeviceToHost));
+    std::vector<double> hc((size_t)3 * g.N), hps((size_t)3 * std::max(e->S, 1)); std::vector<int> hsc(g.N);
+    CK(cudaMemcpy(hc.data(), e->ccoord.p, hc.size() * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(hsc.data(), e->src_cell.p, (size_t)g.N * 4, cudaMemcpyDeviceToHost));
+    if (e->S > 0) CK(cudaMemcpy(hps.data(), e->ccoord_p_src.p, (size_t)3 * e->S * 8, cudaMemcpyDeviceToHost));
+    const size_t m = (size_t)nsrc * ndir_in;
+    std::vector<DreDir> dd(m); std::vector<double> vm(m); std::vector<int> ip(m * std::max(g.nclass, 1), 0);
+    const double E8 = (double)1E-8f;
+    for (int si = 0; si < nsrc; si++) {
+      const int nc = hl[si];
+      const double* sc = (rt_type == DRE_RTT_I_OBS_DIR_SRC) ? &hps[3 * (size_t)hsc[nc]] : &hc[3 * (size_t)nc];
+      for (int j = 0; j < ndir_in; j++) {
+        double v[3]; for (int a = 0; a < 3; a++) v[a] = ccoord_obs[3 * (size_t)j + a] - sc[a];
+        double vmod = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]), theta, phi;
+        if (vmod > E8) {
+          double tr = (0 * v[0] + 0 * v[1] + 1 * v[2]) / vmod;
+          if (fabs(tr - 1.0) < E8) tr = 1.0;
+          if (fabs(tr + 1.0) < E8) tr = -1.0;
+          theta = acos(tr);
+          const double vxy = sin(theta);
+          double pr = (vxy > E8) ? v[0] / (vmod * vxy) : 1.;
+          if (fabs(pr - 1.0) < E8) pr = 1.0;
+          if (fabs(pr + 1.0) < E8) pr = -1.0;
+          phi = acos(pr);
+          if (v[1] < 0) phi = 2 * hp::PI_ - phi;
+        } else { theta = 0; phi = 0; vmod = 0; }
+        const size_t o = (size_t)si * ndir_in + j;
+        dd[o] = hp::make_dir(theta, phi); vm[o] = vmod;
+        for (int c = 0; c < g.nclass; c++) ip[o * g.nclass + c] = hp::ang2pix_nest(1 << g.class_kp[c], theta, phi);
+      }
+    }
+    d_in_dir.upload(dd.data(), m, e->st); d_vm.upload(vm.data(), m, e->st); d_ip.upload(ip.data(), ip.size(), e->st);
+    CK(cudaStreamSynchronize(e->st));
+    q.in_dir = d_in_dir.p; q.in_vecmod = d_vm.p; q.in_ip = d_ip.p;
+  }
+  if (nsrc > 0 && ndir + ndir_in > 0) {
+    DreAccum A = make_accum(e, e->tot.p);
+    const long long nt = (long long)nsrc * (ndir + ndir_in);
+    DRE_REQUIRE(nt < (1ll << 31), "dre_run_iobs: too many rays for one launch");
+    const int ctas = (int)std::max<long long>(1, std::min<long long>((long long)e->sm_count * 4, (nt + 7) / 8));
+    CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
+    CK(cudaEventRecord(e->ev[2], e->st));
+    k_iobs<<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    CK(cudaEventRecord(e->ev[3], e->st));
+    CK(cudaGetLastError());
+    e->last_launches++;
+  }
+  CK(cudaEventRecord(e->ev[1], e->st));
+  CK(cudaStreamSynchronize(e->st));
+  if (nsrc > 0 && ndir + ndir_in > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms = ms; }
+  int herr = read_int(e, e->errflag.p);
+  if (herr != 0) throw DreError{err_text(herr)};
+  float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));
+  fill_counters(e, out, ms);
+  if (i_obs && ndir > 0) CK(cudaMemcpyAsync(i_obs, e->i_obs.p, (size_t)ndir * NS * L * 8, cudaMemcpyDeviceToHost, e->st));
+  if (i_obs_in && ndir_in > 0) CK(cudaMemcpyAsync(i_obs_in, e->i_obs_in.p, (size_t)ndir_in * NS * L * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_allreduce(dre_engine* e, int rt_type) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  if (e->nranks <= 1) return 0;
+  DRE_REQUIRE(e->comm != nullptr, "dre_allreduce: no communicator");
+  const DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L, NS = (size_t)g.N + e->S;
+  auto ar = [&](void* p, size_t n, int dt) {
+    const int rc = g_nccl.AllReduce(p, p, n, dt, NCCL_SUM, e->comm, e->st);
+    if (rc != 0) throw DreError{std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error")};
+  };
+  switch (rt_type) {
+    case DRE_RTT_PRECALC_CELL: case DRE_RTT_PRECALC_SRC:       // reduce_u_fest_arr io_routines.f90:3708-3730
+      ar(e->u_fest.p, NL, NCCL_FLOAT64); break;
+    case DRE_RTT_DIR_CELL: case DRE_RTT_DIR_SRC:               // reduce_u_final_arr / reduce_scaspe_arr / reduce_lum_lost
+      ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64); ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
+      ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64); break;
+    case DRE_RTT_SCATT: {
+      // delta trick io_routines.f90:3743-3757 and lum_lost correction :3846-3848
+      k_u_delta<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0);
+      ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64);
+      k_u_delta<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);
+      std::vector<double> ll(g.L), lp(g.L);
+      CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
+      CK(cudaMemcpyAsync(lp.data(), e->lum_lost_prev.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
+      CK(cudaStreamSynchronize(e->st));
+      for (int l = 0; l < g.L; l++) ll[l] = ll[l] - (e->nranks - 1) / (double)e->nranks * lp[l];
+      CK(cudaMemcpyAsync(e->lum_lost.p, ll.data(), g.L * 8, cudaMemcpyHostToDevice, e->st));
+      ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
+      ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64);
+      break;
+    }
+    default: break;   // i_obs passes are not sharded (rt_loop_iobs has no MPI split, rt_routines.f90:1498)
+  }
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double* tot_rad_en, int32_t* cnflag) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  DRE_REQUIRE(tot_rad_en && cnflag, "dre_prepare_scatt: null output");
+  const DreDev& g = e->g;
+  const size_t NL = (size_t)g.N * g.L, nsca = (size_t)g.N * (g.ROW - g.L);
+  k_u_rows<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);          // u_fest <- u_final
+  CK(cudaMemcpyAsync(e->lum_lost_prev.p, e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToDevice, e->st));
+  if (iterations == 1)   // create_scaspe_tot rt_routines.f90:3012-3040: scaspe_tot_arr = scaspe_arr
+    CK(cudaMemcpyAsync(e->tot.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));
+  CK(cudaMemcpyAsync(e->prev.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));  // scaspe_prev <- scaspe
+  e->red_d.ensure((size_t)2 * g.L);
+  if (iterations == 1) {
+    k_totrad<<<g.L, 256, 0, e->st>>>(g, e->acc.p, e->red_d.p);
+    CK(cudaMemcpyAsync(tot_rad_en, e->red_d.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
+  }
+  k_lumcell_sca<<<cdiv(NL, 256), 256, 0, e->st>>>(g, e->acc.p, e->lumcell.p, 0);
+  k_colsum<<<g.L, 256, 0, e->st>>>(e->lumcell.p, g.N, g.L, e->red_d.p + g.L);
+  std::vector<double> tl(g.L);
+  CK(cudaMemcpyAsync(tl.data(), e->red_d.p + g.L, g.L * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  double sum_tot = 0; for (int l = 0; l < g.L; l++) sum_tot += tot_rad_en[l];
+  int flag = 1;
+  if (sum_tot > 0) for (int l = 0; l < g.L; l++) if (!(tl[l] / tot_rad_en[l] < conv_en_lim)) flag = 0;
+  *cnflag = flag;
+  if (iterations > 1) k_add_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->tot.p, e->acc.p, g.N, g.ROW, g.L);
+  k_zero_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->acc.p, g.N, g.ROW, g.L);
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_build_source_list(dre_engine* e, int rt_type, int32_t* n_sources, int32_t* list_out) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  e->g.rt_type = rt_type;
+  const int n = build_source_list(e);
+  if (n_sources) *n_sources = n;
+  if (list_out && n > 0) CK(cudaMemcpy(list_out, e->srclist.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  DRE_CATCH(e)
+}
+
+int dre_locate_points(dre_engine* e, int32_t npts, const double* xyz, const int32_t* cc_old, int32_t* cell_out) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_grid && e->have_params, "dre_locate_points: grid/params not set");
+  if (npts <= 0) return 0;
+  DBuf<double> dx; DBuf<int> dc, dout;
+  dx.upload(xyz, (size_t)3 * npts, e->st); dc.upload(cc_old, npts, e->st); dout.ensure(npts);
+  k_locate<<<cdiv(npts, 128), 128, 0, e->st>>>(e->g, npts, dx.p, dc.p, dout.p);
+  CK(cudaMemcpyAsync(cell_out, dout.p, (size_t)npts * 4, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_pix2vec(dre_engine* e, int32_t nside, int32_t npix, const int32_t* ipix, double* theta, double* phi, double* vec) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  int k = 0; while ((1 << k) < nside) k++;
+  DRE_REQUIRE((1 << k) == nside && k <= DRE_MAXK, "dre_pix2vec: nside must be a power of two <= 8192");
+  DRE_REQUIRE(k <= 10, "dre_pix2vec: direction tables are limited to nside <= 1024");
+  for (int i = 0; i < npix; i++) DRE_REQUIRE(ipix[i] >= 0 && ipix[i] < 12 * nside * nside, "dre_pix2vec: ipix out of range");
+  build_dir_table(e, k);
+  if (npix <= 0) return 0;
+  DBuf<int> dp; DBuf<double> dv;
+  dp.upload(ipix, npix, e->st); dv.ensure((size_t)3 * npix);
+  k_pix2vec<<<cdiv(npix, 256), 256, 0, e->st>>>(e->dirtab[k].p, npix, dp.p, dv.p);
+  CK(cudaMemcpyAsync(vec, dv.p, (size_t)3 * npix * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  if (theta && phi) for (int i = 0; i < npix; i++) hp::pix2ang_nest(nside, ipix[i], theta[i], phi[i]);
+  DRE_CATCH(e)
+}
+
+int dre_set_record(dre_engine* e, int64_t max_records) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  e->rec_cap = max_records < 0 ? 0 : max_records;
+  if (e->rec_cap > 0) e->rec.ensure((size_t)e->rec_cap, 1.0);
+  DRE_CATCH(e)
+}
+int dre_get_records(dre_engine* e, dre_isect* out, int64_t cap, int64_t* n) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  unsigned long long m = 0;
+  CK(cudaMemcpy(&m, e->rec_n.p, 8, cudaMemcpyDeviceToHost));
+  if (n) *n = (int64_t)m;
+  const int64_t k = std::min<int64_t>(std::min<int64_t>(cap, (int64_t)m), e->rec_cap);
+  if (out && k > 0) CK(cudaMemcpy(out, e->rec.p, (size_t)k * sizeof(dre_isect), cudaMemcpyDeviceToHost));
+  DRE_CATCH(e)
+}
+int dre_set_option(dre_engine* e, const char* name, double value) {
+  DRE_TRY(e)
+  const std::string s(name ? name : "");
+  if (s == "use_bulk") e->opt_use_bulk = value != 0;
+  else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
+  else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
+  else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
+  else if (s == "dir_kmax") e->opt_dir_kmax = std::max(2, std::min(10, (int)value));
+  else DRE_REQUIRE(false, "dre_set_option: unknown option");
+  DRE_CATCH(e)
+}
+int64_t dre_last_launches(const dre_engine* e) { return e ? e->last_launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,315 @@
+// dre_kernels.cuh — persistent ray-march kernels and the separate small kernels
+// (cell list, point locator, pix2vec, layout transposes, scattering-iteration bookkeeping).
+#pragma once
+#include "dre_trace.cuh"
+
+__device__ __forceinline__ void dre_src_coord(const DreDev& g, int nc, double src[3]) {   // calc_src_ccoord :1922-1939
+  const int rt = g.rt_type;
+  if (rt == DRE_RTT_PRECALC_SRC || rt == DRE_RTT_DIR_SRC || rt == DRE_RTT_I_OBS_DIR_SRC) {
+    const int s = g.src_cell[nc];
+    for (int a = 0; a < 3; a++) src[a] = g.ccoord_p_src[3 * (size_t)s + a];
+  } else for (int a = 0; a < 3; a++) src[a] = g.ccoord[3 * (size_t)nc + a];
+}
+__device__ __forceinline__ double dre_src_lum(const DreDev& g, int nc, int l) {            // src_lum_value :1897-1919
+  const int rt = g.rt_type;
+  if (rt == DRE_RTT_PRECALC_SRC || rt == DRE_RTT_DIR_SRC || rt == DRE_RTT_I_OBS_DIR_SRC)
+    return (g.S > 0 && g.src_cell[nc] != -1) ? g.lum_p_src[(size_t)g.src_cell[nc] * g.L + l] : 0.0;
+  return g.lumcell[(size_t)nc * g.L + l];
+}
+
+__device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need) {
+  ws.pending = 0;
+  if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
+  const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
+  unsigned short* lam = (unsigned short*)smem;
+  for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
+  const size_t per = (size_t)(2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0)) * 8;   // keeps 16-B alignment
+  double* base = (double*)(smem + lam_bytes + per * warp);
+  ws.lamof = lam; ws.stage = base; ws.F = base + g.ROW; ws.en2 = base + 2 * g.ROW;
+  __syncthreads();
+}
+static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps) {
+  const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
+  const size_t per = (size_t)(2 * ROW + 2 * L + (L & 1 ? 2 : 0)) * 8;
+  return lam_bytes + per * warps;
+}
+
+__device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpStats& st, int lane) {
+  if (lane != 0) return;
+  atomicAdd(&A.counters[CNT_RAYS], st.rays); atomicAdd(&A.counters[CNT_ISECT], st.isect);
+  atomicAdd(&A.counters[CNT_DEP], st.dep); atomicAdd(&A.counters[CNT_BEAM], st.beam);
+  atomicAdd(&A.counters[CNT_SPLIT], st.split); atomicAdd(&A.counters[CNT_MERGE], st.merge);
+  atomicAdd(&A.counters[CNT_SCA], st.sca); atomicAdd(&A.counters[CNT_ACT], st.act);
+  atomicAdd(&A.counters[CNT_HASH], st.hash);
+}
+
+// ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
+template <int MODE>
+__global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
+                        DreList out, int* __restrict__ counter) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpSmem ws;
+  dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP);
+  WarpStats st; memset(&st, 0, sizeof(st));
+  double lost[DRE_KL];
+#pragma unroll
+  for (int k = 0; k < DRE_KL; k++) lost[k] = 0;
+  const int L = g.L;
+  for (;;) {
+    int t = 0;
+    if (lane == 0) t = atomicAdd(counter, 1);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= nt) break;
+    const DreTask tk = tasks[t];
+    const int un = tk.unit;
+    RayIn r;
+    r.nc = u.nc[un]; r.nk = u.nk[un]; r.gid = u.gid[un]; r.step = u.step[un]; r.ray_ord = t - u.task_seg[un];
+    r.vec_mod = 0;
+    dre_src_coord(g, r.nc, r.src);
+    const DreList& S = (tk.kind == 2) ? W : H;
+    const unsigned m = S.meta[tk.e0];
+    int dk, dip;
+    if (tk.kind == 0) { dk = r.nk; dip = 4 * (S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - (r.nk - 1)))) + tk.sub; r.type = RT_HIGH; }
+    else if (tk.kind == 1) { dk = META_DIRK(m); dip = S.dir_ipix[tk.e0]; r.type = RT_RECO; }
+    else { dk = r.nk; dip = S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - r.nk)); r.type = RT_LOW; }
+    r.dir = g.dirtab[dk][dip];
+    r.fdir = (r.type == RT_RECO && r.nk <= 8) ? g.dirtab[r.nk][1] : r.dir;   // Q2: ipix = 1 for ray_type_reco
+    r.cc_old = S.cc_old[tk.e0]; r.isel_ray = META_ISEL(m);
+    r.prev_ray = S.prev[tk.e0];
+    if (tk.kind == 2) r.prev_ray = (((S.prev[tk.e0] + S.prev[tk.e1]) + S.prev[tk.e2]) + S.prev[tk.e3]) / 4;   // ray_list.f90:266
+    double I[DRE_KL];
+#pragma unroll
+    for (int k = 0; k < DRE_KL; k++) {
+      const int l = lane + 32 * k;
+      I[k] = 0;
+      if (k < g.KLn && l < L) {
+        if (g.rt_type == DRE_RTT_SCATT && r.cc_old == r.nc) {       // assign_src_lum :3043-3071
+          const int ik = g.ik_sca[l];
+          const int ip = (ik >= 0) ? (dip >> (2 * (dk - g.class_kp[ik]))) : 0;
+          I[k] = A.prev[(size_t)r.nc * g.ROW + g.off[l] + ip] * g.npix_hp[l];
+        } else if (tk.kind == 2) {
+          double s = S.lum[(size_t)tk.e0 * L + l];
+          s = s + S.lum[(size_t)tk.e1 * L + l]; s = s + S.lum[(size_t)tk.e2 * L + l]; s = s + S.lum[(size_t)tk.e3 * L + l];
+          I[k] = s / 4;                                              // ray_list.f90:261-264
+        } else I[k] = S.lum[(size_t)tk.e0 * L + l];
+      }
+    }
+    RayOut o;
+    st.psel = 0; st.npsel = 0;
+    trace_ray<MODE>(g, A, ws, lane, r, I, lost, st, o);
+    if (MODE == MODE_DEP && lane == 0 && st.npsel > 0) {
+      const int sid = (g.rt_type == DRE_RTT_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
+      atomicAdd(&A.psel_sum[sid], st.psel);
+      atomicAdd((unsigned long long*)&A.ipsel[sid], (unsigned long long)st.npsel);
+    }
+    if (lane == 0) {
+      const int ty = (o.kind == OUT_HIGH) ? RT_HIGH : (o.kind == OUT_LOW ? RT_LOW : RT_GONE);
+      out.unit[t] = un; out.dir_ipix[t] = dip; out.meta[t] = dre_meta(dk, r.nk, o.isel_old, ty);
+      out.cc_old[t] = o.cc; out.dplane[t] = o.dplane; out.prev[t] = o.prev;
+    }
+    if (o.kind != OUT_NONE) {
+#pragma unroll
+      for (int k = 0; k < DRE_KL; k++) {
+        const int l = lane + 32 * k;
+        if (k < g.KLn && l < L) out.lum[(size_t)t * L + l] = I[k];
+      }
+    }
+  }
+  if (MODE == MODE_DEP) {
+    if (lane == 0) bulk_wait_all();
+#pragma unroll
+    for (int k = 0; k < DRE_KL; k++) {
+      const int l = lane + 32 * k;
+      if (k < g.KLn && l < L && lost[k] != 0) atomicAdd(&A.lum_lost[l], lost[k]);
+    }
+  }
+  dre_flush_stats(A, st, lane);
+}
+
+// ---- rt_loop_iobs rt_routines.f90:1470-1603: one attenuation-only ray per (source, direction)
+struct DreIobs {
+  const int* srclist; int nsrc;        // luminous leaf cells
+  int ndir, ndir_in;
+  const DreDir* obs_dir;               // [ndir] external directions dir_i_out
+  const DreDir* in_dir;                // [nsrc][ndir_in] find_theta_phi_obs_in :3164-3217 (host libm)
+  const double* in_vecmod;             // [nsrc][ndir_in]
+  const int* in_ip;                    // [nsrc][ndir_in][nclass] ang2pix_nest of the observer direction
+  double* i_obs;                       // [ndir][N+S][L]
+  double* i_obs_in;                    // [ndir_in][N+S][L]
+};
+__global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counter) {
+  const int lane = threadIdx.x & 31;
+  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr;
+  WarpStats st; memset(&st, 0, sizeof(st));
+  double lost[DRE_KL] = {0, 0, 0, 0};
+  const int L = g.L, nun = q.ndir + q.ndir_in;
+  const long long nt = (long long)q.nsrc * nun;
+  for (;;) {
+    int t = 0;
+    if (lane == 0) t = atomicAdd(counter, 1);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= nt) break;
+    const int si = t / nun, j = t % nun;
+    RayIn r;
+    r.nc = q.srclist[si]; r.nk = DRE_NSIDE_MIN_K; r.gid = t; r.step = 0; r.ray_ord = 0;
+    dre_src_coord(g, r.nc, r.src);
+    r.cc_old = r.nc; r.isel_ray = 0; r.prev_ray = 0; r.vec_mod = 0;
+    const bool inner = (j >= q.ndir);
+    const int jj = inner ? j - q.ndir : j;
+    if (!inner) { r.dir = q.obs_dir[jj]; r.type = RT_IOBS; }
+    else { r.dir = q.in_dir[(size_t)si * q.ndir_in + jj]; r.vec_mod = q.in_vecmod[(size_t)si * q.ndir_in + jj]; r.type = RT_IOBS_IN; }
+    r.fdir = r.dir;
+    double I[DRE_KL];
+#pragma unroll
+    for (int k = 0; k < DRE_KL; k++) {
+      const int l = lane + 32 * k;
+      I[k] = 0;
+      if (k < g.KLn && l < L) {
+        if (g.rt_type == DRE_RTT_I_OBS) {
+          const double* row = A.prev + (size_t)r.nc * g.ROW + g.off[l];
+          if (!inner) I[k] = row[g.npix_hp[l] + jj] * g.npix_hp[l];                       // :1541
+          else {
+            const int ik = g.ik_sca[l];
+            const int ip = (ik >= 0) ? q.in_ip[((size_t)si * q.ndir_in + jj) * g.nclass + ik] : 0;
+            I[k] = row[ip] * g.npix_hp[l];
+          }
+        } else I[k] = dre_src_lum(g, r.nc, l);
+      }
+    }
+    RayOut o;
+    trace_ray<MODE_IOBS>(g, A, ws, lane, r, I, lost, st, o);
+    const int sid = (g.rt_type == DRE_RTT_I_OBS_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
+    double* dst = (inner ? q.i_obs_in : q.i_obs) + ((size_t)jj * (g.N + g.S) + sid) * L;
+    if (o.iobs_valid) {
+#pragma unroll
+      for (int k = 0; k < DRE_KL; k++) {
+        const int l = lane + 32 * k;
+        if (k < g.KLn && l < L) dst[l] += I[k];
+      }
+    }
+  }
+  dre_flush_stats(A, st, lane);
+}
+
+// ---- cell-list kernel: leaf && sum(lum) /= 0 gate of rt_loop rt_routines.f90:1016 -------
+__global__ void k_src_flags(DreDev g, int* __restrict__ flag) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.N) return;
+  double s = 0;
+  for (int l = 0; l < g.L; l++) s += dre_src_lum(g, i, l);
+  flag[i] = (g.cchild[i] == -1 && s != 0) ? 1 : 0;
+}
+__global__ void k_src_compact(const int* __restrict__ flag, const int* __restrict__ pos, int N, int* __restrict__ list) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N && flag[i]) list[pos[i]] = i;
+}
+
+// seeds of a batch of units: create_high_ray_list ray_list.f90:71-106 (nside 2 pixel = sector)
+__global__ void k_seed(DreDev g, DreUnits u, DreList H, DreList W, const int* __restrict__ srclist, int unit0, int stride,
+                       int rank_off) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > u.U) return;
+  H.seg[i] = i; W.seg[i] = 0;
+  if (i == u.U) return;
+  const int gid = rank_off + (unit0 + i) * stride;     // global unit id = source_ordinal*48 + sector
+  const int nc = srclist[gid / 48], sector = gid % 48;
+  u.nc[i] = nc; u.gid[i] = gid; u.nk[i] = DRE_NSIDE_MIN_K; u.step[i] = 0; u.mode[i] = 1;
+  H.unit[i] = i; H.dir_ipix[i] = sector; H.meta[i] = dre_meta(1, 1, 0, RT_HIGH); H.cc_old[i] = nc;
+  H.dplane[i] = 0; H.prev[i] = 0;
+  for (int l = 0; l < g.L; l++) H.lum[(size_t)i * g.L + l] = dre_src_lum(g, nc, l);
+}
+
+// ---- bounding-box / locator kernel: find_cc_new2 for arbitrary points ----------------------
+__global__ void k_locate(DreDev g, int n, const double* __restrict__ xyz, const int* __restrict__ cc_old, int* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double src[3] = {0, 0, 0};
+  const double d[3] = {xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2]};
+  int cc_new = -1, clvl = 0; unsigned long long c[3];
+  const int rc = dre_locate(g, src, d, 1.0, cc_old[i], cc_new, clvl, c);
+  out[i] = (rc == 0) ? cc_new : -1;
+}
+// pix2vec = pix2ang_nest + calc_cproj from the direction table
+__global__ void k_pix2vec(const DreDir* __restrict__ tab, int n, const int* __restrict__ ipix, double* __restrict__ vec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const DreDir d = tab[ipix[i]];
+  vec[3 * (size_t)i] = d.st * d.cp; vec[3 * (size_t)i + 1] = d.st * d.sp; vec[3 * (size_t)i + 2] = d.ct;
+}
+
+// ---- layout transposes between the Fortran arrays and the accumulator rows -----------------
+// dir 0: rows[c][off+p] = plane[c][p] ; dir 1: plane[c][p] = rows[c][off+p]
+__global__ void k_plane_rows(double* __restrict__ rows, double* __restrict__ plane, int N, int P, int ROW, int off, int dir) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)N * P) return;
+  const size_t c = i / P; const int p = (int)(i % P);
+  if (dir == 0) rows[c * ROW + off + p] = plane[i]; else plane[i] = rows[c * ROW + off + p];
+}
+__global__ void k_zero_sca(double* __restrict__ rows, int N, int ROW, int L) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = ROW - L;
+  if (i >= (size_t)N * w) return;
+  rows[(i / w) * ROW + L + (i % w)] = 0;
+}
+__global__ void k_add_sca(double* __restrict__ dst, const double* __restrict__ src, int N, int ROW, int L) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = ROW - L;
+  if (i >= (size_t)N * w) return;
+  const size_t j = (i / w) * ROW + L + (i % w);
+  dst[j] += src[j];
+}
+// lumcell(l,c) = sum_{p<npix_hp} scaspe(l)(p,c) for leaves (calc_total_luminosity_sca rt_routines.f90:722-740);
+// all = 1 sums the observer slots too (case rtt_i_obs :760-771)
+__global__ void k_lumcell_sca(DreDev g, const double* __restrict__ rows, double* __restrict__ lumcell, int all) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)g.N * g.L) return;
+  const int c = (int)(i / g.L), l = (int)(i % g.L);
+  double s = 0;
+  if (g.cchild[c] == -1) {
+    const double* r = rows + (size_t)c * g.ROW + g.off[l];
+    const int n = all ? g.npix[l] : g.npix_hp[l];
+    for (int p = 0; p < n; p++) s += r[p];
+  }
+  lumcell[i] = s;
+}
+// out[l] = sum_c a[c][l*stride...] in a fixed order: one block per wavelength, strided partials,
+// tree reduction (deterministic for a fixed block size)
+__global__ void k_colsum(const double* __restrict__ a, int N, int L, double* __restrict__ out) {
+  __shared__ double sh[256];
+  const int l = blockIdx.x;
+  double s = 0;
+  for (int c = threadIdx.x; c < N; c += blockDim.x) s += a[(size_t)c * L + l];
+  sh[threadIdx.x] = s; __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) out[l] = sh[0];
+}
+// tot_rad_en(l) = sum over ALL cells of the HEALPix part of scaspe (rt_routines.f90:690-698)
+__global__ void k_totrad(DreDev g, const double* __restrict__ rows, double* __restrict__ out) {
+  __shared__ double sh[256];
+  const int l = blockIdx.x;
+  const int off = g.off[l], n = g.npix_hp[l];
+  double s = 0;
+  for (int c = threadIdx.x; c < g.N; c += blockDim.x) { const double* r = rows + (size_t)c * g.ROW + off; for (int p = 0; p < n; p++) s += r[p]; }
+  sh[threadIdx.x] = s; __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) out[l] = sh[0];
+}
+// u part of the rows <-> (N,L) array.  dir 0: rows <- u ; 1: u <- rows
+__global__ void k_u_rows(double* __restrict__ rows, double* __restrict__ u, int N, int L, int ROW, int dir) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)N * L) return;
+  const size_t j = (i / L) * ROW + (i % L);
+  if (dir == 0) rows[j] = u[i]; else u[i] = rows[j];
+}
+// rt_mpi delta trick for the scattering u_final (io_routines.f90:3743-3757): rows.u = max(rows.u - u_fest, 0) / + u_fest
+__global__ void k_u_delta(double* __restrict__ rows, const double* __restrict__ u_fest, int N, int L, int ROW, int dir) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)N * L) return;
+  const size_t j = (i / L) * ROW + (i % L);
+  if (dir == 0) { const double v = rows[j] - u_fest[i]; rows[j] = v < 0 ? 0 : v; } else rows[j] = rows[j] + u_fest[i];
+}
+__global__ void k_psel_ratio(const double* __restrict__ s, const long long* __restrict__ n, int m, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < m) out[i] = n[i] > 0 ? s[i] / (double)n[i] : 0.0;
+}

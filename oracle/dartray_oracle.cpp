@@ -1131,6 +1131,8 @@ int orc_prepare_scatt(orc_ctx* o, int iterations, double conv_en_lim, double* u_
   const int L = c.L, N = c.N;
   memcpy(u_fest, u_final, sizeof(double) * (size_t)L * N);
   if (lum_lost_prev && lum_lost) memcpy(lum_lost_prev, lum_lost, sizeof(double) * L);
+  if (iterations == 1)  // create_scaspe_tot rt_routines.f90:3012-3040: scaspe_tot_arr = scaspe_arr
+    for (int l = 0; l < L; l++) memcpy(scaspe_tot[l], scaspe[l], sizeof(double) * (size_t)c.npix_arr[l] * N);
   for (int l = 0; l < L; l++) memcpy(scaspe_prev[l], scaspe[l], sizeof(double) * (size_t)c.npix_arr[l] * N);
   if (iterations == 1) {
     for (int i = 0; i < L; i++) {
