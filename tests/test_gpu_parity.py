@@ -1,0 +1,124 @@
+"""GPU parity: the CUDA engine (through the C ABI) against the CPU oracle on the same inputs.
+Bit-exact: intersection lists (cell, isel, psel bits), counters.  fp64 fields: <= 1e-5 relative
+(north star tolerance; the engine's atomics only change the summation order)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+
+
+def _engine(scene):
+    from dartray_b200 import engine
+    return engine.Engine(scene)
+
+
+def _oracle(scene, nthreads=8):
+    from oracle import oracle as O
+    return O.Oracle(scene, nthreads=nthreads), O.State(scene)
+
+
+def _sorted_records(r):
+    return np.sort(r, order=["unit", "step", "ray", "k"])
+
+
+def assert_fields_close(a, b, name, rtol=RTOL):
+    a = np.asarray(a); b = np.asarray(b)
+    scale = np.abs(b).max()
+    if scale == 0:
+        assert np.abs(a).max() == 0, name
+        return
+    # relative to each element, with an absolute floor far below any physically meaningful value
+    err = np.abs(a - b) / np.maximum(np.abs(b), 1e-12 * scale)
+    assert err.max() <= rtol, f"{name}: max rel err {err.max():.3e}"
+
+
+def assert_counters_equal(c1, c2, keys=("sources", "rays", "intersections", "deposits", "beam_tests", "splits", "merges",
+                                        "sca_elems", "active_lambda", "steps", "isect_hash")):
+    d1, d2 = c1.as_dict(), c2.as_dict()
+    for k in keys:
+        assert d1[k] == d2[k], f"counter {k}: engine {d1[k]} oracle {d2[k]}"
+
+
+def run_sequence(scene, record=0, iterations=2):
+    """precalc_src -> dir_src -> i_obs_dir_src -> scatt x iterations -> i_obs on both sides, comparing after each pass."""
+    from dartray_b200 import abi
+    eng = _engine(scene)
+    orc, st = _oracle(scene)
+    from oracle import oracle as O
+    gst = O.State(scene)
+    has_src = scene.nsrc > 0
+    has_cell = bool(np.any(scene.lumcell))
+    passes = []
+    if has_cell:
+        passes.append(abi.RTT_PRECALC_CELL)
+    if has_src:
+        passes.append(abi.RTT_PRECALC_SRC)
+    if has_cell:
+        passes.append(abi.RTT_DIR_CELL)
+    if has_src:
+        passes.append(abi.RTT_DIR_SRC)
+    for rt in passes:
+        if record:
+            eng.set_record(record); orc.set_record(record)
+        c_o = orc.run_pass(rt, 0, st)
+        c_g = eng.rt_loop(rt, 0)
+        assert_counters_equal(c_g, c_o)
+        if record:
+            ro, rg = _sorted_records(orc.records()), _sorted_records(eng.records())
+            assert len(ro) == len(rg) == c_o.intersections
+            assert np.array_equal(ro, rg), f"intersection list differs in pass {rt}"
+        eng.download_state(gst)
+        assert_fields_close(gst.u_fest, st.u_fest, f"u_fest after pass {rt}")
+        assert_fields_close(gst.u_final, st.u_final, f"u_final after pass {rt}")
+        for l in range(scene.lnum):
+            assert_fields_close(gst.scaspe[l], st.scaspe[l], f"scaspe[{l}] after pass {rt}")
+        assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost after pass {rt}")
+    # direct-light i_obs
+    for rt in ([abi.RTT_I_OBS_DIR_CELL] if has_cell else []) + ([abi.RTT_I_OBS_DIR_SRC] if has_src else []):
+        c_o = orc.run_iobs(rt, st)
+        c_g = eng.rt_loop_iobs(rt, gst)
+        assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
+        assert_fields_close(gst.i_obs, st.i_obs, f"i_obs after pass {rt}")
+    # scattering iterations
+    tot_g = np.zeros(scene.lnum)
+    for it in range(1, iterations + 1):
+        f_o = orc.prepare_scatt(it, st)
+        f_g = eng.rt_prepare_scatt(it, tot_g)
+        assert f_o == f_g
+        assert_fields_close(tot_g, st.tot_rad_en, "tot_rad_en")
+        if f_o:
+            break
+        orc.set_sources(st.lumcell)
+        if record:
+            eng.set_record(record); orc.set_record(record)
+        c_o = orc.run_pass(abi.RTT_SCATT, it, st)
+        c_g = eng.rt_loop(abi.RTT_SCATT, it)
+        assert_counters_equal(c_g, c_o)
+        if record:
+            ro, rg = _sorted_records(orc.records()), _sorted_records(eng.records())
+            assert np.array_equal(ro, rg), f"intersection list differs in scattering iteration {it}"
+        eng.download_state(gst)
+        assert_fields_close(gst.u_final, st.u_final, f"u_final after scatt {it}")
+        for l in range(scene.lnum):
+            assert_fields_close(gst.scaspe[l], st.scaspe[l], f"scaspe[{l}] after scatt {it}")
+            assert_fields_close(gst.scaspe_tot[l], st.scaspe_tot[l], f"scaspe_tot[{l}] after scatt {it}")
+        assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost after scatt {it}")
+        assert_fields_close(gst.lumcell, st.lumcell, f"lumcell after scatt {it}")
+    # scattered-light i_obs from scaspe_tot
+    it += 1
+    orc.prepare_scatt(it, st); eng.rt_prepare_scatt(it, tot_g)
+    c_o = orc.run_iobs(abi.RTT_I_OBS, st)
+    c_g = eng.rt_loop_iobs(abi.RTT_I_OBS, gst)
+    assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
+    assert_fields_close(gst.i_obs, st.i_obs, "i_obs after rtt_i_obs")
+    eng.close()
+
+
+def test_trusti_small_full_sequence(small_trusti):
+    run_sequence(small_trusti, record=6_000_000, iterations=2)
+
+
+def test_trusti_tiny_thick(tiny_trusti):
+    run_sequence(tiny_trusti, record=4_000_000, iterations=3)
