@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py — ray-cell intersections/s of the DART-Ray ray-tracing hot path on B200.
+
+One "step" = one full radiation-field solve of the workload: precalc pass, direct-light pass and
+all scattering iterations up to convergence (the rt_loop calls of dartray_main,
+dartray_hub.f90:12-67), on synthetic inputs shaped like the reference's example
+(`--workload trustI`: TRUSTI_GRIDS/input_trustI_tau0.01_LD.in, 21 801 cells, 32 wavelengths).
+
+  value   whole-job intersections/s, accumulators resident in HBM (device timed, max over ranks)
+  e2e     the same solve through dre_run_pass with HOST (pinned) arrays: every pass uploads
+          u_fest/u_final/scaspe/scaspe_prev/lum_lost and downloads the results
+  roofline  algorithmic bytes of the deposit passes / device time of the ray-march kernel launches
+  cpu_baseline  the CPU oracle (C++ restatement of the reference path, OpenMP over sources like
+          rt_routines.f90:994) on all host cores, on a bounded sample of scattering iteration 1
+
+`--impl reference` times that CPU path alone (the Fortran reference cannot be built in this image).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def load_scene(name):
+    from dartray_b200 import scenes
+    if name == "trustI":
+        return scenes.trusti_scene(), "TRUST-I slab tau=0.01 (input_trustI_tau0.01_LD.in): 21801 cells, 32 wavelengths, 1 point source"
+    if name == "trustI_small":
+        return scenes.trusti_scene(lnum=4, max_lvl=3), "TRUST-I slab reduced (5801 cells, 4 wavelengths)"
+    fn = getattr(scenes, name + "_scene", None)
+    if fn is None:
+        raise SystemExit(f"unknown workload {name}")
+    sc = fn()
+    return sc, f"{name}: {sc.grid.ncell} cells, {sc.lnum} wavelengths"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.stop = threading.Event()
+        self.th = None
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i] == "Active" for r in self.rows if len(r) > 2 + i)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def algorithmic_bytes(c):
+    """geometry 24 B ccoord + 4 B lvl per intersection + 4 B per cchild load; deposit
+    8*La dens + 16*La u_final RMW + 16*sum P(lambda) scaspe RMW; beam test 8*La dens + 8*La u_fest."""
+    beam_act = c.active_lambda - c.active_lambda_dep
+    return 28 * c.intersections + 4 * c.descent_loads + 24 * c.active_lambda_dep + 16 * c.sca_elems + 16 * beam_act
+
+
+def solve_resident(eng, scene, abi, max_iterations=30):
+    """precalc -> direct -> scattering iterations on device-resident state; returns the pass counters."""
+    for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST,
+              abi.ARR_PSEL_AV):
+        eng.zero(a)
+    eng.set_sources(scene.lumcell)
+    has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
+    cs = []
+    if has_cell:
+        cs.append(("precalc_cell", eng.rt_loop(abi.RTT_PRECALC_CELL)))
+    if has_src:
+        cs.append(("precalc_src", eng.rt_loop(abi.RTT_PRECALC_SRC)))
+    eng.rt_mpi(abi.RTT_PRECALC_SRC)
+    if has_cell:
+        cs.append(("dir_cell", eng.rt_loop(abi.RTT_DIR_CELL)))
+    if has_src:
+        cs.append(("dir_src", eng.rt_loop(abi.RTT_DIR_SRC)))
+    eng.rt_mpi(abi.RTT_DIR_SRC)
+    tot = np.zeros(scene.lnum)
+    for it in range(1, max_iterations + 1):
+        if eng.rt_prepare_scatt(it, tot):
+            break
+        cs.append((f"scatt{it}", eng.rt_loop(abi.RTT_SCATT, it)))
+        eng.rt_mpi(abi.RTT_SCATT)
+    return cs
+
+
+def pinned(shape):
+    import torch
+    return torch.zeros(shape, dtype=torch.float64).pin_memory().numpy()
+
+
+class HostState:
+    """The Fortran host's arrays (u_fest_arr, u_final_arr, scaspe_arr, ...) in pinned memory."""
+
+    def __init__(self, scene):
+        N, L = scene.grid.ncell, scene.lnum
+        self.u_fest, self.u_final = pinned((N, L)), pinned((N, L))
+        self.scaspe = [pinned((N, int(p))) for p in scene.npix]
+        self.scaspe_prev = [pinned((N, int(p))) for p in scene.npix]
+        self.scaspe_tot = [pinned((N, int(p))) for p in scene.npix]
+        self.lum_lost, self.lum_lost_prev = pinned((L,)), pinned((L,))
+        self.lumcell = pinned((N, L))
+        self.psel_av = pinned((N + scene.nsrc,))
+
+    def nbytes_up(self, precalc, scatt):
+        n = self.u_fest.nbytes
+        if not precalc:
+            n += self.u_final.nbytes + sum(p.nbytes for p in self.scaspe) + self.lum_lost.nbytes
+            if scatt:
+                n += sum(p.nbytes for p in self.scaspe_prev)
+        return n
+
+    def nbytes_down(self, precalc):
+        if precalc:
+            return self.u_fest.nbytes
+        return self.u_final.nbytes + sum(p.nbytes for p in self.scaspe) + self.lum_lost.nbytes + self.psel_av.nbytes
+
+
+def solve_host(eng, scene, abi, hs, max_iterations=30):
+    """The same solve through the drop-in call dre_run_pass with host arrays; rt_prepare(rtt_scatt)
+    (dartray_hub.f90:432-457) is done on the host arrays like the Fortran host does."""
+    for a in (hs.u_fest, hs.u_final, hs.lum_lost, hs.lum_lost_prev, hs.lumcell, *hs.scaspe, *hs.scaspe_prev, *hs.scaspe_tot):
+        a[...] = 0
+    eng.set_sources(scene.lumcell)
+    has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
+    up = down = 0
+    isect = 0
+    seq = ([abi.RTT_PRECALC_CELL] if has_cell else []) + ([abi.RTT_PRECALC_SRC] if has_src else []) + \
+          ([abi.RTT_DIR_CELL] if has_cell else []) + ([abi.RTT_DIR_SRC] if has_src else [])
+    for rt in seq:
+        pre = rt in (abi.RTT_PRECALC_CELL, abi.RTT_PRECALC_SRC)
+        c = eng.rt_loop_host(rt, 0, hs)
+        isect += c.intersections
+        up += hs.nbytes_up(pre, False); down += hs.nbytes_down(pre)
+    leaf = scene.grid.cchild == -1
+    tot_rad_en = np.zeros(scene.lnum)
+    nhp = scene.npix_hp
+    for it in range(1, max_iterations + 1):
+        hs.u_fest[...] = hs.u_final
+        hs.lum_lost_prev[...] = hs.lum_lost
+        for l in range(scene.lnum):
+            if it == 1:
+                hs.scaspe_tot[l][...] = hs.scaspe[l]
+                tot_rad_en[l] = hs.scaspe[l][:, :nhp[l]].sum()
+            hs.scaspe_prev[l][...] = hs.scaspe[l]
+            hs.lumcell[:, l] = np.where(leaf, hs.scaspe[l][:, :nhp[l]].sum(axis=1), 0.0)
+        tl = hs.lumcell.sum(axis=0)
+        conv = bool(np.all(tl / tot_rad_en < scene.conv_en_lim)) if tot_rad_en.sum() > 0 else True
+        for l in range(scene.lnum):
+            if it > 1:
+                hs.scaspe_tot[l] += hs.scaspe[l]
+            hs.scaspe[l][...] = 0
+        if conv:
+            break
+        eng.set_sources(hs.lumcell)
+        up += hs.lumcell.nbytes
+        c = eng.rt_loop_host(abi.RTT_SCATT, it, hs)
+        isect += c.intersections
+        up += hs.nbytes_up(False, True); down += hs.nbytes_down(False)
+    return isect, up, down
+
+
+def cpu_sample(scene, abi, st, target_s=15.0, nthreads=None):
+    """Oracle on all host cores: scattering iteration 1 restricted to units with gid % K == 0."""
+    from oracle import oracle as O
+    nthreads = nthreads or os.cpu_count() or 1
+    orc = O.Oracle(scene, nthreads=nthreads)
+    orc.set_sources(st.lumcell)
+
+    def run(K):
+        s2 = O.State(scene)
+        s2.u_fest[...] = st.u_fest; s2.u_final[...] = st.u_final
+        for l in range(scene.lnum):
+            s2.scaspe_prev[l][...] = st.scaspe_prev[l]
+        t0 = time.perf_counter()
+        c = orc.run_pass(abi.RTT_SCATT, 1, s2, rank=0, nranks=K)
+        return c, time.perf_counter() - t0
+
+    K = 64
+    c, dt = run(K)
+    full_est = dt * K
+    K2 = max(1, int(round(full_est / target_s)))
+    if K2 < K:
+        c, dt = run(K2)
+        K = K2
+    return c, dt, K, nthreads
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="trustI")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--option", action="append", default=[], help="engine option name=value")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    from dartray_b200 import abi
+
+    scene, desc = load_scene(args.workload)
+    metric, unit = "ray-cell intersections/s (direct+scatter solve)", "intersections/s"
+    config = {"workload": desc, "solve": "precalc + direct + scattering iterations to conv_en_lim=%g" % scene.conv_en_lim,
+              "l2_policy": "working set (accumulator rows %.0f MB) exceeds the 126 MB L2" %
+                           (scene.grid.ncell * (scene.lnum + int(scene.npix.sum())) * 8 / 1e6)}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        from oracle import oracle as O
+        ncores = os.cpu_count() or 1
+        orc = O.Oracle(scene, nthreads=ncores)
+        st = O.State(scene)
+        t0 = time.perf_counter()
+        orc.run_pass(abi.RTT_PRECALC_SRC if scene.nsrc else abi.RTT_PRECALC_CELL, 0, st)
+        orc.run_pass(abi.RTT_DIR_SRC if scene.nsrc else abi.RTT_DIR_CELL, 0, st)
+        orc.prepare_scatt(1, st)
+        setup_s = time.perf_counter() - t0
+        vals = []
+        K = None
+        for i in range(args.warmup + args.steps):
+            c, dt, K, nth = cpu_sample(scene, abi, st, target_s=12.0 if K is None else 12.0, nthreads=ncores)
+            if i >= args.warmup:
+                vals.append((c.intersections, dt))
+        n = sum(v[0] for v in vals); t = sum(v[1] for v in vals)
+        v = n / t
+        sample = f"scattering iteration 1, units with id % {K} == 0 ({vals[-1][0]} intersections per step); untimed setup {setup_s:.1f} s"
+        print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": 1e3 * t / max(1, len(vals)), "higher_is_better": True,
+                          "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": v, "unit": unit, "cores": nth, "kind": "port", "sample": sample},
+                          "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    from dartray_b200 import engine
+    torch.cuda.set_device(local_rank)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        obj = [engine.Engine.get_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        nccl_id = obj[0]
+    eng = engine.Engine(scene, device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id)
+    for o in args.option:
+        k, v = o.split("=")
+        eng.set_option(k, float(v))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def maxr(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sumr(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        solve_resident(eng, scene, abi)
+    barrier()
+    l0 = eng.launch_count()
+    step_ms, last = [], None
+    with ClockSampler(local_rank) as clk:
+        for _ in range(args.steps):
+            barrier()
+            eng.mark(0)
+            last = solve_resident(eng, scene, abi)
+            eng.mark(1)
+            step_ms.append(maxr(eng.elapsed_ms(0, 1)))
+            barrier()
+    launches = eng.launch_count() - l0
+    clocks = clk.summary()
+    isect = sumr(float(sum(c.intersections for _, c in last)))
+    deposits = sumr(float(sum(c.deposits for _, c in last)))
+    ms = float(np.mean(step_ms))
+    value = isect / (ms * 1e-3)
+    dep = [c for n, c in last if n.startswith("dir") or n.startswith("scatt")]
+    abytes = sum(algorithmic_bytes(c) for c in dep)
+    kms = sum(c.kernel_ms for c in dep)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ach = abytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+    roof = {"bound": "hbm", "kernel": "k_trace<MODE_DEP>", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
+            "algorithmic_bytes_per_step": abytes, "kernel_ms_per_step": kms,
+            "launches_per_step": int(sum(c.trace_launches for c in dep))}
+    line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(launches),
+            "s_per_wavelength": ms * 1e-3 / scene.lnum, "intersections_per_step": isect, "deposits_per_step": deposits,
+            "passes": {n: {"ms": round(c.pass_ms, 3), "kernel_ms": round(c.kernel_ms, 3), "intersections": c.intersections,
+                           "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
+            "roofline": roof}
+
+    if not args.no_e2e:
+        hs = HostState(scene)
+        solve_host(eng, scene, abi, hs)  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = 1
+        for _ in range(n_e2e):
+            isect_h, up, down = solve_host(eng, scene, abi, hs)
+        barrier()
+        dt = maxr(time.perf_counter() - t0) / n_e2e
+        line["e2e"] = {"value": sumr(float(isect_h)) / dt, "unit": unit, "h2d_bytes_per_step": int(up), "d2h_bytes_per_step": int(down),
+                       "ms_per_step": dt * 1e3, "timing": "host wall clock around dre_run_pass calls (uploads and downloads inside)"}
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import oracle as O
+        st = O.State(scene)
+        # state before scattering iteration 1, produced by the engine (setup only, untimed)
+        for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST):
+            eng.zero(a)
+        eng.set_sources(scene.lumcell)
+        eng.rt_loop(abi.RTT_PRECALC_SRC if scene.nsrc else abi.RTT_PRECALC_CELL)
+        eng.rt_loop(abi.RTT_DIR_SRC if scene.nsrc else abi.RTT_DIR_CELL)
+        eng.rt_prepare_scatt(1, np.zeros(scene.lnum))
+        eng.download_state(st)
+        c, dt, K, nth = cpu_sample(scene, abi, st)
+        line["cpu_baseline"] = {"value": c.intersections / dt, "unit": unit, "cores": nth, "kind": "port",
+                                "sample": f"scattering iteration 1, units with id % {K} == 0: {c.intersections} intersections in {dt:.1f} s"}
+    if rank == 0:
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

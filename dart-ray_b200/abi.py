@@ -29,7 +29,8 @@ class Counters(C.Structure):
         ("sources", C.c_int64), ("rays", C.c_int64), ("intersections", C.c_int64), ("deposits", C.c_int64),
         ("beam_tests", C.c_int64), ("splits", C.c_int64), ("merges", C.c_int64), ("sca_elems", C.c_int64),
         ("active_lambda", C.c_int64), ("steps", C.c_int64), ("kernel_ms", C.c_double), ("pass_ms", C.c_double),
-        ("isect_hash", C.c_uint64),
+        ("isect_hash", C.c_uint64), ("active_lambda_dep", C.c_int64), ("descent_loads", C.c_int64),
+        ("launches", C.c_int64), ("trace_launches", C.c_int64),
     ]
 
     def as_dict(self):

@@ -202,4 +202,4 @@ struct DreAccum {
   int* err;             // first reference STOP condition hit
   int use_bulk;         // 1: TMA bulk reduce of the whole row; 0: per-lane red.global.add.f64
 };
-enum { CNT_RAYS = 0, CNT_ISECT, CNT_DEP, CNT_BEAM, CNT_SPLIT, CNT_MERGE, CNT_SCA, CNT_ACT, CNT_HASH, CNT_N };
+enum { CNT_RAYS = 0, CNT_ISECT, CNT_DEP, CNT_BEAM, CNT_SPLIT, CNT_MERGE, CNT_SCA, CNT_ACT, CNT_HASH, CNT_N, CNT_ACTDEP, CNT_DESC };

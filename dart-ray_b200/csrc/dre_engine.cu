@@ -76,7 +76,8 @@ struct dre_engine {
   int opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 8, opt_ctas_per_sm = 1, opt_dir_kmax = 9;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
-  long long last_launches = 0;
+  long long last_launches = 0, n_launch = 0, launch_mark = 0;
+  cudaEvent_t marks[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   size_t rows_elems() const { return (size_t)g.N * g.ROW; }
 };
@@ -91,13 +92,13 @@ void scan_level(dre_engine* e, const int* in, int* out, int n, int level) {
   e->scan_tmp[level].ensure((size_t)2 * nb + 8);
   int* sums = e->scan_tmp[level].p;
   int* scanned = sums + nb;
-  k_scan_tile<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, sums, n);
-  if (nb == 1) k_scan_top<<<1, 1, 0, e->st>>>(sums, scanned);
+  (e->n_launch++, k_scan_tile)<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, sums, n);
+  if (nb == 1) (e->n_launch++, k_scan_top)<<<1, 1, 0, e->st>>>(sums, scanned);
   else scan_level(e, sums, scanned, nb, level + 1);
-  k_scan_add<<<cdiv((size_t)n + 1, 256), 256, 0, e->st>>>(out, scanned, n, nb);
+  (e->n_launch++, k_scan_add)<<<cdiv((size_t)n + 1, 256), 256, 0, e->st>>>(out, scanned, n, nb);
 }
 void scan(dre_engine* e, const int* in, int* out, int n) {
-  if (n <= 0) { k_set_int<<<1, 1, 0, e->st>>>(out, 0); return; }
+  if (n <= 0) { (e->n_launch++, k_set_int)<<<1, 1, 0, e->st>>>(out, 0); return; }
   scan_level(e, in, out, n, 0);
 }
 
@@ -178,6 +179,7 @@ void dre_destroy(dre_engine* e) {
   cudaDeviceSynchronize();
   if (e->comm) g_nccl.CommDestroy(e->comm);
   for (int i = 0; i < 4; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+  for (int i = 0; i < 8; i++) if (e->marks[i]) cudaEventDestroy(e->marks[i]);
   if (e->st) cudaStreamDestroy(e->st);
   delete e;
 }
@@ -333,7 +335,7 @@ void planes_io(dre_engine* e, double* rows, double* const* planes, int dir) {
     const size_t n = (size_t)g.N * P;
     e->tmp_d.ensure(n);
     if (dir == 0) CK(cudaMemcpyAsync(e->tmp_d.p, planes[l], n * 8, cudaMemcpyHostToDevice, e->st));
-    k_plane_rows<<<cdiv(n, 256), 256, 0, e->st>>>(rows, e->tmp_d.p, g.N, P, g.ROW, e->h_off[l], dir);
+    (e->n_launch++, k_plane_rows)<<<cdiv(n, 256), 256, 0, e->st>>>(rows, e->tmp_d.p, g.N, P, g.ROW, e->h_off[l], dir);
     if (dir == 1) CK(cudaMemcpyAsync(planes[l], e->tmp_d.p, n * 8, cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
   }
@@ -343,7 +345,7 @@ void u_final_io(dre_engine* e, double* host, int dir) {
   const size_t n = (size_t)g.N * g.L;
   e->tmp_d.ensure(n);
   if (dir == 0) CK(cudaMemcpyAsync(e->tmp_d.p, host, n * 8, cudaMemcpyHostToDevice, e->st));
-  k_u_rows<<<cdiv(n, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, dir);
+  (e->n_launch++, k_u_rows)<<<cdiv(n, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, dir);
   if (dir == 1) CK(cudaMemcpyAsync(host, e->tmp_d.p, n * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
 }
@@ -387,7 +389,7 @@ int dre_download(dre_engine* e, int which, void* planes) {
     case DRE_ARR_LUMCELL: CK(cudaMemcpyAsync(planes, e->lumcell.p, NL * 8, cudaMemcpyDeviceToHost, e->st)); break;
     case DRE_ARR_PSEL_AV:
       DRE_REQUIRE(e->have_sources, "dre_download: call dre_set_sources first");
-      k_psel_ratio<<<cdiv(NS, 256), 256, 0, e->st>>>(e->psel_sum.p, e->ipsel.p, (int)NS, e->psel_av.p);
+      (e->n_launch++, k_psel_ratio)<<<cdiv(NS, 256), 256, 0, e->st>>>(e->psel_sum.p, e->ipsel.p, (int)NS, e->psel_av.p);
       CK(cudaMemcpyAsync(planes, e->psel_av.p, NS * 8, cudaMemcpyDeviceToHost, e->st)); break;
     case DRE_ARR_I_OBS:
       DRE_REQUIRE(e->i_obs.p, "dre_download: no i_obs pass was run");
@@ -410,9 +412,9 @@ int dre_zero(dre_engine* e, int which) {
   const size_t nsca = (size_t)g.N * (g.ROW - g.L);
   switch (which) {
     case DRE_ARR_U_FEST: e->u_fest.zero(NL, e->st); break;
-    case DRE_ARR_U_FINAL: e->tmp_d.zero(NL, e->st); k_u_rows<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, 0); break;
+    case DRE_ARR_U_FINAL: e->tmp_d.zero(NL, e->st); (e->n_launch++, k_u_rows)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->tmp_d.p, g.N, g.L, g.ROW, 0); break;
     case DRE_ARR_SCASPE: case DRE_ARR_SCASPE_PREV: case DRE_ARR_SCASPE_TOT:
-      k_zero_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(rows_of(e, which), g.N, g.ROW, g.L); break;
+      (e->n_launch++, k_zero_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(rows_of(e, which), g.N, g.ROW, g.L); break;
     case DRE_ARR_LUM_LOST: e->lum_lost.zero(g.L, e->st); break;
     case DRE_ARR_PSEL_AV: e->psel_sum.zero(NS, e->st); e->ipsel.zero(NS, e->st); break;
     case DRE_ARR_LUMCELL: e->lumcell.zero(NL, e->st); break;
@@ -459,9 +461,9 @@ const char* err_text(int code) {
 int build_source_list(dre_engine* e) {
   const DreDev& g = e->g;
   e->srcflag.ensure(g.N); e->srcpos.ensure((size_t)g.N + 1); e->srclist.ensure(g.N);
-  k_src_flags<<<cdiv(g.N, 256), 256, 0, e->st>>>(g, e->srcflag.p);
+  (e->n_launch++, k_src_flags)<<<cdiv(g.N, 256), 256, 0, e->st>>>(g, e->srcflag.p);
   scan(e, e->srcflag.p, e->srcpos.p, g.N);
-  k_src_compact<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p, e->srcpos.p, g.N, e->srclist.p);
+  (e->n_launch++, k_src_compact)<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p, e->srcpos.p, g.N, e->srclist.p);
   e->nsrc_list = read_int(e, e->srcpos.p + g.N);
   return e->nsrc_list;
 }
@@ -486,6 +488,7 @@ void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const Dre
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
+  e->n_launch++;
   k_trace<MODE><<<ctas, warps * 32, smem, e->st>>>(e->g, A, u, H, W, e->tasks.p, nT, out, e->counter.p);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
@@ -501,25 +504,25 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
   for (int i = 0; i < 2; i++) { e->H[i].ensure(U, L, U); e->W[i].ensure(64, L, U); }
   int cur = 0;
   e->H[0].n = U; e->W[0].n = 0;
-  k_seed<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(g, u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
+  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(g, u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
   e->extcnt.ensure(U); e->ext_seg.ensure((size_t)U + 1); e->reco_cnt.ensure(U);
   e->keptH.ensure(U); e->keptW.ensure(U); e->newHcnt.ensure(U); e->newWcnt.ensure(U);
   const int ub = cdiv(U, 256);
   for (;;) {
     DreList Hc = e->H[cur].view(), Wc = e->W[cur].view();
     const int nH = Hc.n, nW = Wc.n;
-    k_plan<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg);
+    (e->n_launch++, k_plan)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg);
     if (nH > 0) {
       e->selH.ensure(nH); e->posH.ensure((size_t)nH + 1);
-      k_select<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p);
+      (e->n_launch++, k_select)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p);
       scan(e, e->selH.p, e->posH.p, nH);
     }
     if (nW > 0) {
       e->selW.ensure(nW); e->posW.ensure((size_t)nW + 1);
-      k_select<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p);
+      (e->n_launch++, k_select)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p);
       scan(e, e->selW.p, e->posW.p, nW);
     }
-    k_unit_ext<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->extcnt.p);
+    (e->n_launch++, k_unit_ext)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->extcnt.p);
     scan(e, e->extcnt.p, e->ext_seg.p, U);
     const int nExt = read_int(e, e->ext_seg.p + U);
     int nT = 0;
@@ -528,30 +531,30 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
       e->leader.ensure(nExt); e->unit_of_ext.ensure(nExt); e->ntask.ensure(nExt); e->nreco.ensure(nExt);
       e->task_off.ensure((size_t)nExt + 1); e->reco_off.ensure((size_t)nExt + 1);
       const int xb = cdiv(nExt, 256);
-      if (nH > 0) k_fill_ext<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
-      if (nW > 0) k_fill_ext<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
-      k_unit_of_ext<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->unit_of_ext.p);
-      k_cand<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p);
-      k_resolve<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->cand.p, e->ncand.p, e->gone.p, e->leader.p);
-      k_count<<<xb, 256, 0, e->st>>>(Hc, u, e->ext_seg.p, e->ext.p, nExt, e->unit_of_ext.p, e->ncand.p, e->leader.p, e->ntask.p, e->nreco.p);
+      if (nH > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
+      if (nW > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
+      (e->n_launch++, k_unit_of_ext)<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->unit_of_ext.p);
+      (e->n_launch++, k_cand)<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p);
+      (e->n_launch++, k_resolve)<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->cand.p, e->ncand.p, e->gone.p, e->leader.p);
+      (e->n_launch++, k_count)<<<xb, 256, 0, e->st>>>(Hc, u, e->ext_seg.p, e->ext.p, nExt, e->unit_of_ext.p, e->ncand.p, e->leader.p, e->ntask.p, e->nreco.p);
       scan(e, e->ntask.p, e->task_off.p, nExt);
       scan(e, e->nreco.p, e->reco_off.p, nExt);
-      k_unit_tasks<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->ext_seg.p, e->task_off.p, e->reco_off.p, e->reco_cnt.p);
+      (e->n_launch++, k_unit_tasks)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->ext_seg.p, e->task_off.p, e->reco_off.p, e->reco_cnt.p);
       nT = read_int(e, e->task_off.p + nExt);
       if (nT > 0) {
         e->tasks.ensure(nT); e->OUT.ensure(nT, L, 1); e->OUT.n = nT;
         e->fH.ensure(nT); e->fW.ensure(nT); e->posOH.ensure((size_t)nT + 1); e->posOW.ensure((size_t)nT + 1);
-        k_emit_tasks<<<xb, 256, 0, e->st>>>(u, e->ext.p, nExt, e->unit_of_ext.p, e->cand.p, e->ntask.p, e->task_off.p, e->tasks.p);
+        (e->n_launch++, k_emit_tasks)<<<xb, 256, 0, e->st>>>(u, e->ext.p, nExt, e->unit_of_ext.p, e->cand.p, e->ntask.p, e->task_off.p, e->tasks.p);
         DreList out = e->OUT.view();
         if (mode == MODE_PRECALC) launch_trace<MODE_PRECALC>(e, A, u, Hc, Wc, nT, out);
         else launch_trace<MODE_DEP>(e, A, u, Hc, Wc, nT, out);
-        k_out_flags<<<cdiv(nT, 256), 256, 0, e->st>>>(out, nT, e->fH.p, e->fW.p);
+        (e->n_launch++, k_out_flags)<<<cdiv(nT, 256), 256, 0, e->st>>>(out, nT, e->fH.p, e->fW.p);
         scan(e, e->fH.p, e->posOH.p, nT);
         scan(e, e->fW.p, e->posOW.p, nT);
       }
     }
     const int nx = 1 - cur;
-    k_unit_new<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->reco_cnt.p, e->posOH.p, e->posOW.p,
+    (e->n_launch++, k_unit_new)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->reco_cnt.p, e->posOH.p, e->posOW.p,
                                       nExt > 0 ? 1 : 0, nT > 0 ? 1 : 0, e->keptH.p, e->keptW.p, e->newHcnt.p, e->newWcnt.p);
     scan(e, e->newHcnt.p, e->H[nx].seg.p, U);
     scan(e, e->newWcnt.p, e->W[nx].seg.p, U);
@@ -565,15 +568,15 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
     e->H[nx].ensure(std::max(nH2, 1), L, U); e->W[nx].ensure(std::max(nW2, 1), L, U);
     e->H[nx].n = nH2; e->W[nx].n = nW2;
     DreList Hn = e->H[nx].view(), Wn = e->W[nx].view();
-    if (nH > 0) k_build_kept<<<cdiv(nH, 256), 256, 0, e->st>>>(Hn, Hc, e->selH.p, e->posH.p, L);
-    if (nW > 0) k_build_kept<<<cdiv(nW, 256), 256, 0, e->st>>>(Wn, Wc, e->selW.p, e->posW.p, L);
-    if (nExt > 0) k_build_reco<<<cdiv(nExt, 256), 256, 0, e->st>>>(Hn, Wc, u, e->ext.p, nExt, e->unit_of_ext.p, e->ext_seg.p, e->cand.p,
+    if (nH > 0) (e->n_launch++, k_build_kept)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hn, Hc, e->selH.p, e->posH.p, L);
+    if (nW > 0) (e->n_launch++, k_build_kept)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wn, Wc, e->selW.p, e->posW.p, L);
+    if (nExt > 0) (e->n_launch++, k_build_reco)<<<cdiv(nExt, 256), 256, 0, e->st>>>(Hn, Wc, u, e->ext.p, nExt, e->unit_of_ext.p, e->ext_seg.p, e->cand.p,
                                                                  e->nreco.p, e->reco_off.p, e->keptH.p, L);
-    if (nT > 0) k_build_out<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
+    if (nT > 0) (e->n_launch++, k_build_out)<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
                                                              e->keptH.p, e->keptW.p, e->reco_cnt.p, L);
     cur = nx;
     CK(cudaMemsetAsync(e->active.p, 0, sizeof(int), e->st));
-    k_next<<<ub, 256, 0, e->st>>>(u, Hn.seg, Wn.seg, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
+    (e->n_launch++, k_next)<<<ub, 256, 0, e->st>>>(u, Hn.seg, Wn.seg, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
     int hv[2];
     CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
@@ -594,6 +597,8 @@ void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
   out->beam_tests = c[CNT_BEAM]; out->splits = c[CNT_SPLIT]; out->merges = c[CNT_MERGE]; out->sca_elems = c[CNT_SCA];
   out->active_lambda = c[CNT_ACT]; out->steps = c[CNT_N]; out->isect_hash = c[CNT_HASH];
   out->kernel_ms = e->last_kernel_ms; out->pass_ms = pass_ms;
+  out->active_lambda_dep = c[CNT_ACTDEP]; out->descent_loads = c[CNT_DESC];
+  out->launches = e->n_launch - e->launch_mark; out->trace_launches = e->last_launches;
 }
 
 void ensure_dir_tables(dre_engine* e) {
@@ -619,7 +624,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   e->g.rt_type = rt_type;
   ensure_dir_tables(e);
   e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
-  e->last_kernel_ms = 0; e->last_launches = 0;
+  e->last_kernel_ms = 0; e->last_launches = 0; e->launch_mark = e->n_launch;
   CK(cudaEventRecord(e->ev[0], e->st));
   const int nsrc = build_source_list(e);
   const long long total_units = (long long)nsrc * 48;
@@ -689,10 +694,10 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
   if (i_obs && ndir > 0) CK(cudaMemcpyAsync(e->i_obs.p, i_obs, (size_t)ndir * NS * L * 8, cudaMemcpyHostToDevice, e->st));
   if (i_obs_in && ndir_in > 0) CK(cudaMemcpyAsync(e->i_obs_in.p, i_obs_in, (size_t)ndir_in * NS * L * 8, cudaMemcpyHostToDevice, e->st));
   e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
-  e->last_kernel_ms = 0; e->last_launches = 0;
+  e->last_kernel_ms = 0; e->last_launches = 0; e->launch_mark = e->n_launch;
   CK(cudaEventRecord(e->ev[0], e->st));
   if (rt_type == DRE_RTT_I_OBS)   // calc_total_luminosity_sca case(rtt_i_obs) rt_routines.f90:760-771
-    k_lumcell_sca<<<cdiv((size_t)g.N * L, 256), 256, 0, e->st>>>(g, e->tot.p, e->lumcell.p, 1);
+    (e->n_launch++, k_lumcell_sca)<<<cdiv((size_t)g.N * L, 256), 256, 0, e->st>>>(g, e->tot.p, e->lumcell.p, 1);
   const int nsrc = build_source_list(e);
   DreIobs q; memset(&q, 0, sizeof(q));
   q.srclist = e->srclist.p; q.nsrc = nsrc; q.ndir = ndir; q.ndir_in = ndir_in; q.obs_dir = e->obs_dir.p;
@@ -742,7 +747,7 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
     const int ctas = (int)std::max<long long>(1, std::min<long long>((long long)e->sm_count * 4, (nt + 7) / 8));
     CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
     CK(cudaEventRecord(e->ev[2], e->st));
-    k_iobs<<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    (e->n_launch++, k_iobs)<<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
     CK(cudaEventRecord(e->ev[3], e->st));
     CK(cudaGetLastError());
     e->last_launches++;
@@ -780,9 +785,9 @@ int dre_allreduce(dre_engine* e, int rt_type) {
       ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64); break;
     case DRE_RTT_SCATT: {
       // delta trick io_routines.f90:3743-3757 and lum_lost correction :3846-3848
-      k_u_delta<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0);
+      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0);
       ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64);
-      k_u_delta<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);
+      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);
       std::vector<double> ll(g.L), lp(g.L);
       CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
       CK(cudaMemcpyAsync(lp.data(), e->lum_lost_prev.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
@@ -806,18 +811,18 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   DRE_REQUIRE(tot_rad_en && cnflag, "dre_prepare_scatt: null output");
   const DreDev& g = e->g;
   const size_t NL = (size_t)g.N * g.L, nsca = (size_t)g.N * (g.ROW - g.L);
-  k_u_rows<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);          // u_fest <- u_final
+  (e->n_launch++, k_u_rows)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);          // u_fest <- u_final
   CK(cudaMemcpyAsync(e->lum_lost_prev.p, e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToDevice, e->st));
   if (iterations == 1)   // create_scaspe_tot rt_routines.f90:3012-3040: scaspe_tot_arr = scaspe_arr
     CK(cudaMemcpyAsync(e->tot.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));
   CK(cudaMemcpyAsync(e->prev.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));  // scaspe_prev <- scaspe
   e->red_d.ensure((size_t)2 * g.L);
   if (iterations == 1) {
-    k_totrad<<<g.L, 256, 0, e->st>>>(g, e->acc.p, e->red_d.p);
+    (e->n_launch++, k_totrad)<<<g.L, 256, 0, e->st>>>(g, e->acc.p, e->red_d.p);
     CK(cudaMemcpyAsync(tot_rad_en, e->red_d.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
   }
-  k_lumcell_sca<<<cdiv(NL, 256), 256, 0, e->st>>>(g, e->acc.p, e->lumcell.p, 0);
-  k_colsum<<<g.L, 256, 0, e->st>>>(e->lumcell.p, g.N, g.L, e->red_d.p + g.L);
+  (e->n_launch++, k_lumcell_sca)<<<cdiv(NL, 256), 256, 0, e->st>>>(g, e->acc.p, e->lumcell.p, 0);
+  (e->n_launch++, k_colsum)<<<g.L, 256, 0, e->st>>>(e->lumcell.p, g.N, g.L, e->red_d.p + g.L);
   std::vector<double> tl(g.L);
   CK(cudaMemcpyAsync(tl.data(), e->red_d.p + g.L, g.L * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
@@ -825,8 +830,8 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   int flag = 1;
   if (sum_tot > 0) for (int l = 0; l < g.L; l++) if (!(tl[l] / tot_rad_en[l] < conv_en_lim)) flag = 0;
   *cnflag = flag;
-  if (iterations > 1) k_add_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->tot.p, e->acc.p, g.N, g.ROW, g.L);
-  k_zero_sca<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->acc.p, g.N, g.ROW, g.L);
+  if (iterations > 1) (e->n_launch++, k_add_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->tot.p, e->acc.p, g.N, g.ROW, g.L);
+  (e->n_launch++, k_zero_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->acc.p, g.N, g.ROW, g.L);
   CK(cudaStreamSynchronize(e->st));
   DRE_CATCH(e)
 }
@@ -849,7 +854,7 @@ int dre_locate_points(dre_engine* e, int32_t npts, const double* xyz, const int3
   if (npts <= 0) return 0;
   DBuf<double> dx; DBuf<int> dc, dout;
   dx.upload(xyz, (size_t)3 * npts, e->st); dc.upload(cc_old, npts, e->st); dout.ensure(npts);
-  k_locate<<<cdiv(npts, 128), 128, 0, e->st>>>(e->g, npts, dx.p, dc.p, dout.p);
+  (e->n_launch++, k_locate)<<<cdiv(npts, 128), 128, 0, e->st>>>(e->g, npts, dx.p, dc.p, dout.p);
   CK(cudaMemcpyAsync(cell_out, dout.p, (size_t)npts * 4, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
   DRE_CATCH(e)
@@ -866,7 +871,7 @@ int dre_pix2vec(dre_engine* e, int32_t nside, int32_t npix, const int32_t* ipix,
   if (npix <= 0) return 0;
   DBuf<int> dp; DBuf<double> dv;
   dp.upload(ipix, npix, e->st); dv.ensure((size_t)3 * npix);
-  k_pix2vec<<<cdiv(npix, 256), 256, 0, e->st>>>(e->dirtab[k].p, npix, dp.p, dv.p);
+  (e->n_launch++, k_pix2vec)<<<cdiv(npix, 256), 256, 0, e->st>>>(e->dirtab[k].p, npix, dp.p, dv.p);
   CK(cudaMemcpyAsync(vec, dv.p, (size_t)3 * npix * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
   if (theta && phi) for (int i = 0; i < npix; i++) hp::pix2ang_nest(nside, ipix[i], theta[i], phi[i]);
@@ -901,6 +906,23 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else DRE_REQUIRE(false, "dre_set_option: unknown option");
   DRE_CATCH(e)
 }
-int64_t dre_last_launches(const dre_engine* e) { return e ? e->last_launches : 0; }
+int dre_mark(dre_engine* e, int slot) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(slot >= 0 && slot < 8, "dre_mark: slot out of range");
+  if (!e->marks[slot]) CK(cudaEventCreate(&e->marks[slot]));
+  CK(cudaEventRecord(e->marks[slot], e->st));
+  DRE_CATCH(e)
+}
+int dre_elapsed_ms(dre_engine* e, int a, int b, double* ms) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(a >= 0 && a < 8 && b >= 0 && b < 8 && e->marks[a] && e->marks[b] && ms, "dre_elapsed_ms: bad slots");
+  CK(cudaEventSynchronize(e->marks[b]));
+  float f = 0; CK(cudaEventElapsedTime(&f, e->marks[a], e->marks[b]));
+  *ms = f;
+  DRE_CATCH(e)
+}
+int64_t dre_launch_count(const dre_engine* e) { return e ? e->n_launch : 0; }
 
 }  // extern "C"

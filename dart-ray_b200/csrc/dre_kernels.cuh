@@ -41,6 +41,7 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
   atomicAdd(&A.counters[CNT_SPLIT], st.split); atomicAdd(&A.counters[CNT_MERGE], st.merge);
   atomicAdd(&A.counters[CNT_SCA], st.sca); atomicAdd(&A.counters[CNT_ACT], st.act);
   atomicAdd(&A.counters[CNT_HASH], st.hash);
+  atomicAdd(&A.counters[CNT_ACTDEP], st.actdep); atomicAdd(&A.counters[CNT_DESC], st.desc);
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------

@@ -22,7 +22,7 @@ SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
     "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_build_source_list",
-    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option",
+    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
 
@@ -121,6 +121,19 @@ class Engine:
 
     def set_option(self, name, value):
         self._ck(self.l.dre_set_option(self.h, name.encode(), C.c_double(value)))
+
+    def mark(self, slot):
+        self._ck(self.l.dre_mark(self.h, C.c_int(slot)))
+
+    def elapsed_ms(self, a, b):
+        ms = C.c_double(0)
+        self._ck(self.l.dre_elapsed_ms(self.h, C.c_int(a), C.c_int(b), C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        self.l.dre_launch_count.restype = C.c_int64
+        self.l.dre_launch_count.argtypes = [C.c_void_p]
+        return int(self.l.dre_launch_count(self.h))
 
     def set_record(self, n):
         self._ck(self.l.dre_set_record(self.h, C.c_int64(n)))

@@ -76,6 +76,10 @@ typedef struct dre_counters {
   double  kernel_ms;      /* device time of the ray-march kernel(s), CUDA events */
   double  pass_ms;        /* device time of the whole pass */
   uint64_t isect_hash;    /* order-independent hash of (unit, cell, isel, psel bits) */
+  int64_t active_lambda_dep; /* sum over deposits only of active wavelengths */
+  int64_t descent_loads;  /* cchild loads of ccindd_to_cc (sum of descent depths) */
+  int64_t launches;       /* CUDA kernels launched by the pass */
+  int64_t trace_launches; /* of which ray-march kernels */
 } dre_counters;
 
 /* One recorded intersection (debug/parity mode, dre_set_record). */
@@ -159,6 +163,10 @@ int dre_pix2vec(dre_engine*, int32_t nside, int32_t npix, const int32_t* ipix,
 int dre_set_record(dre_engine*, int64_t max_records);   /* 0 disables */
 int dre_get_records(dre_engine*, dre_isect* out, int64_t cap, int64_t* n);
 int dre_set_option(dre_engine*, const char* name, double value);
+/* timing hooks: CUDA events on the engine's stream (print_time io_routines.f90:4268 is wall clock) */
+int dre_mark(dre_engine*, int slot /*0..7*/);
+int dre_elapsed_ms(dre_engine*, int slot_a, int slot_b, double* ms /*out; synchronises*/);
+int64_t dre_launch_count(const dre_engine*);  /* kernels launched since dre_create */
 
 #ifdef __cplusplus
 }

@@ -469,7 +469,7 @@ void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, i
       if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
         for (int k = 0; k < La; k++)
           atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
-        t.cnt.deposits++; t.cnt.active_lambda += La;
+        t.cnt.deposits++; t.cnt.active_lambda += La; t.cnt.active_lambda_dep += La;
       } else { ray_status = RAS_GO_LOW; return; }
       break;
     case DRE_RTT_DIR_SRC:
@@ -493,7 +493,7 @@ void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, i
       } else if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
         for (int k = 0; k < La; k++)
           atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
-        t.cnt.deposits++; t.cnt.active_lambda += La;
+        t.cnt.deposits++; t.cnt.active_lambda += La; t.cnt.active_lambda_dep += La;
         std::vector<double> en_sca(La, 0.0);
         if (cc != nc) {
           for (int k = 0; k < La; k++) {
@@ -655,6 +655,7 @@ bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vecto
     }
     if (left) break;
     if (!ccindd_to_cc(c, t.ccindd, cc, clvl)) { ok = false; break; }  // 'Here you should never get'
+    t.cnt.descent_loads += clvl;
   }
   t.ray_ord++;
   return ok;
@@ -851,6 +852,7 @@ void cnt_add(dre_counters& a, const dre_counters& b) {
   a.sources += b.sources; a.rays += b.rays; a.intersections += b.intersections; a.deposits += b.deposits;
   a.beam_tests += b.beam_tests; a.splits += b.splits; a.merges += b.merges; a.sca_elems += b.sca_elems;
   a.active_lambda += b.active_lambda; a.steps += b.steps; a.isect_hash += b.isect_hash;
+  a.active_lambda_dep += b.active_lambda_dep; a.descent_loads += b.descent_loads;
 }
 
 }  // namespace

@@ -39,7 +39,7 @@ def test_struct_layouts_match_header():
     from dartray_b200 import abi
     # dre_params: 4 int32 + 4 double + 4 int32 + 6 double ; dre_counters: 10 int64 + 2 double + uint64
     assert C.sizeof(abi.Params) == 4 * 4 + 4 * 8 + 4 * 4 + 6 * 8
-    assert C.sizeof(abi.Counters) == 13 * 8
+    assert C.sizeof(abi.Counters) == 17 * 8
     assert abi.ISECT_DTYPE.itemsize == 32
 
 
