@@ -157,6 +157,8 @@ class Oracle:
     def locate(self, xyz, cc_old):
         xyz = np.ascontiguousarray(xyz, dtype=np.float64); cc_old = np.ascontiguousarray(cc_old, dtype=np.int32)
         out = np.zeros(len(cc_old), dtype=np.int32)
+        p = abi.make_params(self.scene, abi.RTT_DIR_CELL)
+        self.l.orc_set_params(self.h, C.byref(p))
         self.l.orc_locate_points(self.h, C.c_int32(len(cc_old)), abi.dptr(xyz), abi.iptr(cc_old), abi.iptr(out))
         return out
 
