@@ -200,6 +200,7 @@ struct DreAccum {
   unsigned long long* counters; // [16]
   dre_isect* rec; long long rec_cap; unsigned long long* rec_n;
   int* err;             // first reference STOP condition hit
+  int want_hash;        // accumulate the intersection checksum (parity runs)
   int use_bulk;         // 1: TMA bulk reduce of the whole row; 0: per-lane red.global.add.f64
 };
 enum { CNT_RAYS = 0, CNT_ISECT, CNT_DEP, CNT_BEAM, CNT_SPLIT, CNT_MERGE, CNT_SCA, CNT_ACT, CNT_HASH, CNT_N, CNT_ACTDEP, CNT_DESC };

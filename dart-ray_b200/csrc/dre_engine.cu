@@ -73,7 +73,7 @@ struct dre_engine {
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
   // options
-  int opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 8, opt_ctas_per_sm = 1, opt_dir_kmax = 9;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 12, opt_ctas_per_sm = 1, opt_dir_kmax = 9;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
@@ -437,7 +437,7 @@ DreAccum make_accum(dre_engine* e, const double* prev_rows) {
   DreAccum A;
   A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
   A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
-  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk;
+  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash;
   return A;
 }
 
@@ -477,22 +477,31 @@ int trace_warps(dre_engine* e, size_t* smem) {
   return w;
 }
 
-template <int MODE>
-void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
+template <int MODE, int KL>
+void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
   size_t smem = 0; int warps = 8;
   if (MODE == MODE_DEP) {
     warps = trace_warps(e, &smem);
-    CK(cudaFuncSetAttribute(k_trace<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(k_trace<MODE, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE><<<ctas, warps * 32, smem, e->st>>>(e->g, A, u, H, W, e->tasks.p, nT, out, e->counter.p);
+  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(e->g, A, u, H, W, e->tasks.p, nT, out, e->counter.p);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
   e->last_launches++;
+}
+
+template <int MODE>
+void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
+  switch (e->g.KLn) {
+    case 1: launch_trace_kl<MODE, 1>(e, A, u, H, W, nT, out); break;
+    case 2: launch_trace_kl<MODE, 2>(e, A, u, H, W, nT, out); break;
+    default: launch_trace_kl<MODE, 4>(e, A, u, H, W, nT, out); break;
+  }
 }
 
 void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
@@ -747,7 +756,10 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
     const int ctas = (int)std::max<long long>(1, std::min<long long>((long long)e->sm_count * 4, (nt + 7) / 8));
     CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
     CK(cudaEventRecord(e->ev[2], e->st));
-    (e->n_launch++, k_iobs)<<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    e->n_launch++;
+    if (g.KLn == 1) k_iobs<1><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    else if (g.KLn == 2) k_iobs<2><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    else k_iobs<4><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
     CK(cudaEventRecord(e->ev[3], e->st));
     CK(cudaGetLastError());
     e->last_launches++;
@@ -899,6 +911,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   DRE_TRY(e)
   const std::string s(name ? name : "");
   if (s == "use_bulk") e->opt_use_bulk = value != 0;
+  else if (s == "hash") e->opt_hash = value != 0;
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));

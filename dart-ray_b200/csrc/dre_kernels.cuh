@@ -45,7 +45,7 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
-template <int MODE>
+template <int MODE, int KL>
 __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
                         DreList out, int* __restrict__ counter) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -53,9 +53,9 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
   WarpSmem ws;
   dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP);
   WarpStats st; memset(&st, 0, sizeof(st));
-  double lost[DRE_KL];
+  double lost[KL];
 #pragma unroll
-  for (int k = 0; k < DRE_KL; k++) lost[k] = 0;
+  for (int k = 0; k < KL; k++) lost[k] = 0;
   const int L = g.L;
   for (;;) {
     int t = 0;
@@ -79,9 +79,9 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
     r.cc_old = S.cc_old[tk.e0]; r.isel_ray = META_ISEL(m);
     r.prev_ray = S.prev[tk.e0];
     if (tk.kind == 2) r.prev_ray = (((S.prev[tk.e0] + S.prev[tk.e1]) + S.prev[tk.e2]) + S.prev[tk.e3]) / 4;   // ray_list.f90:266
-    double I[DRE_KL];
+    double I[KL];
 #pragma unroll
-    for (int k = 0; k < DRE_KL; k++) {
+    for (int k = 0; k < KL; k++) {
       const int l = lane + 32 * k;
       I[k] = 0;
       if (k < g.KLn && l < L) {
@@ -98,7 +98,7 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
     }
     RayOut o;
     st.psel = 0; st.npsel = 0;
-    trace_ray<MODE>(g, A, ws, lane, r, I, lost, st, o);
+    trace_ray<MODE, KL>(g, A, ws, lane, r, I, lost, st, o);
     if (MODE == MODE_DEP && lane == 0 && st.npsel > 0) {
       const int sid = (g.rt_type == DRE_RTT_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
       atomicAdd(&A.psel_sum[sid], st.psel);
@@ -111,7 +111,7 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
     }
     if (o.kind != OUT_NONE) {
 #pragma unroll
-      for (int k = 0; k < DRE_KL; k++) {
+      for (int k = 0; k < KL; k++) {
         const int l = lane + 32 * k;
         if (k < g.KLn && l < L) out.lum[(size_t)t * L + l] = I[k];
       }
@@ -120,7 +120,7 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
   if (MODE == MODE_DEP) {
     if (lane == 0) bulk_wait_all();
 #pragma unroll
-    for (int k = 0; k < DRE_KL; k++) {
+    for (int k = 0; k < KL; k++) {
       const int l = lane + 32 * k;
       if (k < g.KLn && l < L && lost[k] != 0) atomicAdd(&A.lum_lost[l], lost[k]);
     }
@@ -139,11 +139,14 @@ struct DreIobs {
   double* i_obs;                       // [ndir][N+S][L]
   double* i_obs_in;                    // [ndir_in][N+S][L]
 };
+template <int KL>
 __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counter) {
   const int lane = threadIdx.x & 31;
   WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr;
   WarpStats st; memset(&st, 0, sizeof(st));
-  double lost[DRE_KL] = {0, 0, 0, 0};
+  double lost[KL];
+#pragma unroll
+  for (int k = 0; k < KL; k++) lost[k] = 0;
   const int L = g.L, nun = q.ndir + q.ndir_in;
   const long long nt = (long long)q.nsrc * nun;
   for (;;) {
@@ -161,9 +164,9 @@ __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counte
     if (!inner) { r.dir = q.obs_dir[jj]; r.type = RT_IOBS; }
     else { r.dir = q.in_dir[(size_t)si * q.ndir_in + jj]; r.vec_mod = q.in_vecmod[(size_t)si * q.ndir_in + jj]; r.type = RT_IOBS_IN; }
     r.fdir = r.dir;
-    double I[DRE_KL];
+    double I[KL];
 #pragma unroll
-    for (int k = 0; k < DRE_KL; k++) {
+    for (int k = 0; k < KL; k++) {
       const int l = lane + 32 * k;
       I[k] = 0;
       if (k < g.KLn && l < L) {
@@ -179,12 +182,12 @@ __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counte
       }
     }
     RayOut o;
-    trace_ray<MODE_IOBS>(g, A, ws, lane, r, I, lost, st, o);
+    trace_ray<MODE_IOBS, KL>(g, A, ws, lane, r, I, lost, st, o);
     const int sid = (g.rt_type == DRE_RTT_I_OBS_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
     double* dst = (inner ? q.i_obs_in : q.i_obs) + ((size_t)jj * (g.N + g.S) + sid) * L;
     if (o.iobs_valid) {
 #pragma unroll
-      for (int k = 0; k < DRE_KL; k++) {
+      for (int k = 0; k < KL; k++) {
         const int l = lane + 32 * k;
         if (k < g.KLn && l < L) dst[l] += I[k];
       }

@@ -11,7 +11,9 @@ RTOL = 1e-5
 
 def _engine(scene):
     from dartray_b200 import engine
-    return engine.Engine(scene)
+    eng = engine.Engine(scene)
+    eng.set_option("hash", 1)   # intersection checksum (off by default: parity facility)
+    return eng
 
 
 def _oracle(scene, nthreads=8):
