@@ -61,6 +61,8 @@ struct DreDev {
   // direction tables per log2(nside)
   const DreDir* dirtab[DRE_MAXK + 1];
   int dir_kmax;             // largest k with a table
+  // phase-function rows per direction (calc_ffn_arr for every pixel of nside 2^k), accumulator-row layout
+  const double* ftab[DRE_MAXK + 1];
   // sources
   int S;
   const double* lumcell;    // [N][L]

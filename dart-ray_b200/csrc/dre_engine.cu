@@ -54,6 +54,7 @@ struct dre_engine {
   DBuf<double> ccoord, csize, dens, ksca, gsca, lumcell, ccoord_p_src, lum_p_src;
   DBuf<unsigned short> lamof;
   DBuf<DreDir> class_dir[DRE_MAXCLASS], dirtab[DRE_MAXK + 1], obs_dir;
+  DBuf<double> ftab[DRE_MAXK + 1];
   std::vector<int> h_npix, h_npix_hp, h_off, h_ik, h_cell_src;
   std::vector<double> h_dir_i_out;
   int S = 0;
@@ -73,7 +74,7 @@ struct dre_engine {
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 12, opt_ctas_per_sm = 1, opt_dir_kmax = 9;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 12, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 5;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
@@ -154,7 +155,7 @@ int dre_create(dre_engine** out, int device, int rank, int nranks, const void* n
     e->sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CK(cudaEventCreate(&e->ev[i]));
-    e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->counter.zero(4, e->st); e->active.zero(1, e->st);
+    e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->counter.zero(4, e->st); e->active.zero(2, e->st);
     e->rec_n.zero(1, e->st);
     if (e->nranks > 1) {
       DRE_REQUIRE(nccl_id128 != nullptr, "dre_create: nranks > 1 needs an NCCL unique id");
@@ -223,6 +224,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   DreDev& g = e->g;
   const int N = g.N;
   g.L = L; g.KLn = (L + 31) / 32; g.ndir = ndir;
+  for (int k = 0; k <= DRE_MAXK; k++) { e->ftab[k].release(); g.ftab[k] = nullptr; }
   e->dens.upload(dens_arr, (size_t)L * N, e->st); e->ksca.upload(ksca_arr_norm, L, e->st); e->gsca.upload(gsca_arr, L, e->st);
   // classes: set_npix_arr rt_routines.f90:5289-5311
   e->h_npix.assign(L, 0); e->h_npix_hp.assign(L, 0); e->h_off.assign(L, 0); e->h_ik.assign(L, -1);
@@ -477,6 +479,21 @@ int trace_warps(dre_engine* e, size_t* smem) {
   return w;
 }
 
+// phase-function rows for every pixel of nside 2^k (used by the deposit passes up to ftab_kmax)
+void ensure_ftab(dre_engine* e, unsigned nkmask) {
+  DreDev& g = e->g;
+  for (int k = DRE_NSIDE_MIN_K; k <= std::min(e->opt_ftab_kmax, 8); k++) {
+    if (!((nkmask >> k) & 1u) || g.ftab[k]) continue;
+    build_dir_table(e, k);
+    const size_t npix = (size_t)12 << (2 * k);
+    e->ftab[k].ensure(npix * g.ROW, 1.0);
+    e->n_launch++;
+    k_build_ftab<<<cdiv(npix * 32, 256), 256, 0, e->st>>>(g, k, e->ftab[k].p);
+    CK(cudaGetLastError());
+    g.ftab[k] = e->ftab[k].p;
+  }
+}
+
 template <int MODE, int KL>
 void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
   size_t smem = 0; int warps = 8;
@@ -506,6 +523,7 @@ void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const Dre
 
 void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
   const DreDev& g = e->g;
+  unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
   const int L = g.L;
   e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
   DreUnits u; u.nc = e->u_nc.p; u.gid = e->u_gid.p; u.nk = e->u_nk.p; u.step = e->u_step.p; u.mode = e->u_mode.p;
@@ -555,6 +573,7 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
         e->fH.ensure(nT); e->fW.ensure(nT); e->posOH.ensure((size_t)nT + 1); e->posOW.ensure((size_t)nT + 1);
         (e->n_launch++, k_emit_tasks)<<<xb, 256, 0, e->st>>>(u, e->ext.p, nExt, e->unit_of_ext.p, e->cand.p, e->ntask.p, e->task_off.p, e->tasks.p);
         DreList out = e->OUT.view();
+        if (mode == MODE_DEP) ensure_ftab(e, nkmask);
         if (mode == MODE_PRECALC) launch_trace<MODE_PRECALC>(e, A, u, Hc, Wc, nT, out);
         else launch_trace<MODE_DEP>(e, A, u, Hc, Wc, nT, out);
         (e->n_launch++, k_out_flags)<<<cdiv(nT, 256), 256, 0, e->st>>>(out, nT, e->fH.p, e->fW.p);
@@ -584,15 +603,17 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
     if (nT > 0) (e->n_launch++, k_build_out)<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
                                                              e->keptH.p, e->keptW.p, e->reco_cnt.p, L);
     cur = nx;
-    CK(cudaMemsetAsync(e->active.p, 0, sizeof(int), e->st));
+    CK(cudaMemsetAsync(e->active.p, 0, 2 * sizeof(int), e->st));
     (e->n_launch++, k_next)<<<ub, 256, 0, e->st>>>(u, Hn.seg, Wn.seg, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
-    int hv[2];
+    int hv[2], hmask = 0;
     CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&hmask, e->active.p + 1, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
     CK(cudaGetLastError());
     if (hv[1] != 0) throw DreError{err_text(hv[1])};
     if (hv[0] == 0) break;
+    nkmask = (unsigned)hmask;
   }
 }
 
@@ -912,6 +933,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   const std::string s(name ? name : "");
   if (s == "use_bulk") e->opt_use_bulk = value != 0;
   else if (s == "hash") e->opt_hash = value != 0;
+  else if (s == "ftab_kmax") e->opt_ftab_kmax = std::max(0, std::min(8, (int)value));
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));

@@ -19,18 +19,22 @@ __device__ __forceinline__ double dre_src_lum(const DreDev& g, int nc, int l) { 
 
 __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need) {
   ws.pending = 0;
+  ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
   if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
-  const size_t per = (size_t)(2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0)) * 8;   // keeps 16-B alignment
+  const size_t per = (size_t)(2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 2) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
   ws.lamof = lam; ws.stage = base; ws.F = base + g.ROW; ws.en2 = base + 2 * g.ROW;
+  ws.mbar = (unsigned long long*)(base + 2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
+  ws.fphase = 0; ws.fwait = 0;
+  if (lane == 0) mbar_init(ws.mbar);
   __syncthreads();
 }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(2 * ROW + 2 * L + (L & 1 ? 2 : 0)) * 8;
+  const size_t per = (size_t)(2 * ROW + 2 * L + (L & 1 ? 2 : 0) + 2) * 8;
   return lam_bytes + per * warps;
 }
 
@@ -76,6 +80,8 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
     else { dk = r.nk; dip = S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - r.nk)); r.type = RT_LOW; }
     r.dir = g.dirtab[dk][dip];
     r.fdir = (r.type == RT_RECO && r.nk <= 8) ? g.dirtab[r.nk][1] : r.dir;   // Q2: ipix = 1 for ray_type_reco
+    r.fpix = -1;
+    if (MODE == MODE_DEP && g.ftab[r.nk] != nullptr) r.fpix = (r.type == RT_RECO) ? 1 : dip;
     r.cc_old = S.cc_old[tk.e0]; r.isel_ray = META_ISEL(m);
     r.prev_ray = S.prev[tk.e0];
     if (tk.kind == 2) r.prev_ray = (((S.prev[tk.e0] + S.prev[tk.e1]) + S.prev[tk.e2]) + S.prev[tk.e3]) / 4;   // ray_list.f90:266
@@ -118,6 +124,7 @@ __global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, 
     }
   }
   if (MODE == MODE_DEP) {
+    if (ws.fwait) { mbar_wait(ws.mbar, ws.fphase); ws.fwait = 0; }
     if (lane == 0) bulk_wait_all();
 #pragma unroll
     for (int k = 0; k < KL; k++) {
@@ -142,7 +149,7 @@ struct DreIobs {
 template <int KL>
 __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counter) {
   const int lane = threadIdx.x & 31;
-  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr;
+  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
 #pragma unroll
@@ -163,7 +170,7 @@ __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counte
     const int jj = inner ? j - q.ndir : j;
     if (!inner) { r.dir = q.obs_dir[jj]; r.type = RT_IOBS; }
     else { r.dir = q.in_dir[(size_t)si * q.ndir_in + jj]; r.vec_mod = q.in_vecmod[(size_t)si * q.ndir_in + jj]; r.type = RT_IOBS_IN; }
-    r.fdir = r.dir;
+    r.fdir = r.dir; r.fpix = -1;
     double I[KL];
 #pragma unroll
     for (int k = 0; k < KL; k++) {
@@ -194,6 +201,19 @@ __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counte
     }
   }
   dre_flush_stats(A, st, lane);
+}
+
+// ---- phase-function table: one warp per pixel of nside 2^k writes calc_ffn_arr for all wavelengths
+__global__ void k_build_ftab(DreDev g, int k, double* __restrict__ rows) {
+  const int lane = threadIdx.x & 31;
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long npix = 12ll << (2 * k);
+  if (w >= npix) return;
+  WarpSmem ws; ws.pending = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
+  ws.F = rows + (size_t)w * g.ROW;
+  unsigned act[DRE_KL];
+  for (int q = 0; q < DRE_KL; q++) { const int rem = g.L - 32 * q; act[q] = rem >= 32 ? 0xffffffffu : (rem > 0 ? ((1u << rem) - 1u) : 0u); }
+  dre_phase<DRE_KL>(g, ws, lane, g.dirtab[k][w], act);
 }
 
 // ---- cell-list kernel: leaf && sum(lum) /= 0 gate of rt_loop rt_routines.f90:1016 -------

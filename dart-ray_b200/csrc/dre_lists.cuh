@@ -263,6 +263,7 @@ __global__ void k_build_out(DreList dstH, DreList dstW, DreList out, int nt, Dre
 // define_next_level rt_routines.f90:2745-2770 ; *active counts units that still have rays
 __global__ void k_next(DreUnits u, const int* __restrict__ segH, const int* __restrict__ segW, int* __restrict__ active,
                        int* __restrict__ err, int kmax, unsigned long long* __restrict__ steps) {
+  // active[0] = units that still have rays, active[1] = bit mask of their log2(nside)
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= u.U) return;
   if (u.mode[i] == 0) return;
@@ -273,4 +274,5 @@ __global__ void k_next(DreUnits u, const int* __restrict__ segH, const int* __re
   if (u.nk[i] > kmax) { atomicCAS(err, 0, 4); return; }
   if (u.nk[i] < 1) { atomicCAS(err, 0, 5); return; }
   atomicAdd(active, 1);
+  atomicOr(active + 1, 1 << u.nk[i]);
 }
