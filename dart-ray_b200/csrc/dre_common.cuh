@@ -202,6 +202,7 @@ struct DreAccum {
   unsigned long long* counters; // [16]
   dre_isect* rec; long long rec_cap; unsigned long long* rec_n;
   int* err;             // first reference STOP condition hit
+  int stage_split;      // the deposit row is staged and reduced in this many chunks (smem vs occupancy)
   int want_hash;        // accumulate the intersection checksum (parity runs)
   int use_bulk;         // 1: TMA bulk reduce of the whole row; 0: per-lane red.global.add.f64
 };

@@ -74,7 +74,7 @@ struct dre_engine {
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 12, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 5;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 5;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
@@ -439,7 +439,7 @@ DreAccum make_accum(dre_engine* e, const double* prev_rows) {
   DreAccum A;
   A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
   A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
-  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash;
+  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash; A.stage_split = e->opt_stage_split;
   return A;
 }
 
@@ -473,8 +473,9 @@ int build_source_list(dre_engine* e) {
 int trace_warps(dre_engine* e, size_t* smem) {
   const DreDev& g = e->g;
   int w = std::max(1, std::min(e->opt_warps, 32));
-  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w) * e->opt_ctas_per_sm > (size_t)220 * 1024) w--;
-  *smem = dre_trace_smem_bytes(g.ROW, g.L, w);
+  w = std::min(w, 16);
+  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) * e->opt_ctas_per_sm > (size_t)224 * 1024) w--;
+  *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split);
   DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
   return w;
 }
@@ -933,6 +934,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   const std::string s(name ? name : "");
   if (s == "use_bulk") e->opt_use_bulk = value != 0;
   else if (s == "hash") e->opt_hash = value != 0;
+  else if (s == "stage_split") e->opt_stage_split = std::max(1, std::min(8, (int)value));
   else if (s == "ftab_kmax") e->opt_ftab_kmax = std::max(0, std::min(8, (int)value));
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));

@@ -17,24 +17,28 @@ __device__ __forceinline__ double dre_src_lum(const DreDev& g, int nc, int l) { 
   return g.lumcell[(size_t)nc * g.L + l];
 }
 
-__device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need) {
-  ws.pending = 0;
+__host__ __device__ inline int dre_stage_len(int ROW, int split) {
+  int n = (ROW + split - 1) / split; n += n & 1; return n < 2 ? 2 : n;
+}
+__device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split) {
+  ws.pending = 0; ws.stage_len = 0;
   ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
   if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
-  const size_t per = (size_t)(2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 2) * 8;   // keeps 16-B alignment
+  const int sl = dre_stage_len(g.ROW, split);
+  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 2) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
-  ws.lamof = lam; ws.stage = base; ws.F = base + g.ROW; ws.en2 = base + 2 * g.ROW;
-  ws.mbar = (unsigned long long*)(base + 2 * g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
+  ws.lamof = lam; ws.stage = base; ws.F = base + sl; ws.en2 = base + sl + g.ROW; ws.stage_len = sl;
+  ws.mbar = (unsigned long long*)(base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
   ws.fphase = 0; ws.fwait = 0;
   if (lane == 0) mbar_init(ws.mbar);
   __syncthreads();
 }
-static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps) {
+static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(2 * ROW + 2 * L + (L & 1 ? 2 : 0) + 2) * 8;
+  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 2) * 8;
   return lam_bytes + per * warps;
 }
 
@@ -50,12 +54,12 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL>
-__global__ void k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
+__global__ void __launch_bounds__(512, 1) k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
                         DreList out, int* __restrict__ counter) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpSmem ws;
-  dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP);
+  dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split);
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
 #pragma unroll
