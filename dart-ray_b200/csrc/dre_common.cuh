@@ -9,6 +9,9 @@
 #include "../../include/dartray_engine.h"
 #include "../../include/dartray_hash.h"
 
+#ifndef DRE_RARE
+#define DRE_RARE __forceinline__   // measured: __noinline__ on the rare paths costs 25% (call ABI spills), see profiles/
+#endif
 #define DRE_MAXLVL 8        // tree levels packed 8 bits each into one 64-bit word per axis
 #define DRE_MAXK 13         // log2 of the largest HEALPix nside (8192, healpix_routines.f90:9)
 #define DRE_KL 4            // wavelengths per lane: lnum <= 32*DRE_KL
@@ -37,6 +40,7 @@ struct DreDev {
   int N, max_lvl, base[2];
   long long basediv[2];
   int basemask[2];
+  int baseshift[2];         // log2(basediv)
   const int* cchild;        // [N]
   const unsigned char* lvl; // [N]
   const long long* cindex;  // [N]
@@ -74,6 +78,9 @@ struct DreDev {
   int rt_type;
 };
 
+// The static inputs of the current pass live in constant memory (one engine per device at a time).
+__constant__ DreDev c_g;
+
 __device__ __forceinline__ int dre_base(const DreDev& g, int lev) { return g.base[lev > 1 ? 1 : 0]; }
 
 // ---- packed tree coordinates: digit of level j (1-based) lives in bits [8(j-1), 8j) -----
@@ -85,19 +92,20 @@ __device__ __forceinline__ unsigned long long cx_set(unsigned long long c, int j
 
 __device__ __forceinline__ long long dre_ipow64(long long b, int e) { long long r = 1; for (int i = 0; i < e; i++) r *= b; return r; }
 
-// cindex_to_ccindd smooth_grid_routines.f90:793-813
-__device__ __forceinline__ void dre_decode(const DreDev& g, int nc, int clvl, unsigned long long c[3]) {
-  c[0] = c[1] = c[2] = 0;
-  const long long ci = g.cindex[nc];
+// cindex_to_ccindd smooth_grid_routines.f90:793-813 (basediv are powers of two: divisions become shifts)
+__device__ DRE_RARE void dre_decode(const DreDev& g, int nc, int clvl, unsigned long long c[3]) {
+  unsigned long long c0 = 0, c1 = 0, c2 = 0;
+  const unsigned long long ci = (unsigned long long)g.cindex[nc];
   for (int i = 1; i <= clvl; i++) {
-    int ib; long long j;
-    if (i > 1) { ib = 1; j = ((ci / (g.basediv[0] * dre_ipow64(g.basediv[1], i - 2))) & g.basemask[1]) - 1; }
-    else { ib = 0; j = (ci & g.basemask[0]) - 1; }
+    int ib, j;
+    if (i > 1) { ib = 1; j = (int)((ci >> (g.baseshift[0] + g.baseshift[1] * (i - 2))) & (unsigned)g.basemask[1]) - 1; }
+    else { ib = 0; j = (int)(ci & (unsigned)g.basemask[0]) - 1; }
     const int b = g.base[ib];
-    c[0] = cx_set(c[0], i, (int)(j % b));
-    c[1] = cx_set(c[1], i, (int)((j / b) % b));
-    c[2] = cx_set(c[2], i, (int)((j / ((long long)b * b)) % b));
+    c0 = cx_set(c0, i, j % b);
+    c1 = cx_set(c1, i, (j / b) % b);
+    c2 = cx_set(c2, i, (j / (b * b)) % b);
   }
+  c[0] = c0; c[1] = c1; c[2] = c2;
 }
 
 // ccindd_to_cc smooth_grid_routines.f90:820-852 ; returns false if no leaf was found
@@ -122,7 +130,7 @@ __device__ __forceinline__ int dre_outcube(const double r[3], double cellsize) {
 }
 
 // find_cc_new2 rt_routines.f90:1962-2066.  Returns 0 ok, 1 outside the model, 2 reference STOP.
-__device__ __forceinline__ int dre_locate(const DreDev& g, const double src[3], const double d[3], double prev,
+__device__ DRE_RARE int dre_locate(const DreDev& g, const double src[3], const double d[3], double prev,
                                           int cc_old, int& cc_new, int& clvl, unsigned long long c[3]) {
   double p[3], rel[3], q[3];
   for (int i = 0; i < 3; i++) p[i] = src[i] + prev * d[i];

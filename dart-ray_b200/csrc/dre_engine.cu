@@ -103,6 +103,11 @@ void scan(dre_engine* e, const int* in, int* out, int n) {
   scan_level(e, in, out, n, 0);
 }
 
+// publish the static inputs to the constant bank the kernels read
+void sync_g(dre_engine* e) {
+  CK(cudaMemcpyToSymbolAsync(c_g, &e->g, sizeof(DreDev), 0, cudaMemcpyHostToDevice, e->st));
+}
+
 int read_int(dre_engine* e, const int* d) {
   int v = 0; CK(cudaMemcpyAsync(&v, d, sizeof(int), cudaMemcpyDeviceToHost, e->st)); CK(cudaStreamSynchronize(e->st)); return v;
 }
@@ -200,7 +205,7 @@ int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2
   for (int i = 0; i < 2; i++) {   // set_base smooth_grid_routines.f90:622-649
     int j = 0; const long long b3 = (long long)base[i] * base[i] * base[i];
     while (!(b3 < (1ll << j))) j++;
-    g.basediv[i] = 1ll << j; g.basemask[i] = (int)(g.basediv[i] - 1);
+    g.basediv[i] = 1ll << j; g.basemask[i] = (int)(g.basediv[i] - 1); g.baseshift[i] = j;
   }
   std::vector<unsigned char> l8(N);
   for (int i = 0; i < N; i++) { DRE_REQUIRE(lvl[i] >= 0 && lvl[i] <= max_lvl, "dre_set_grid: lvl out of range"); l8[i] = (unsigned char)lvl[i]; }
@@ -463,7 +468,8 @@ const char* err_text(int code) {
 int build_source_list(dre_engine* e) {
   const DreDev& g = e->g;
   e->srcflag.ensure(g.N); e->srcpos.ensure((size_t)g.N + 1); e->srclist.ensure(g.N);
-  (e->n_launch++, k_src_flags)<<<cdiv(g.N, 256), 256, 0, e->st>>>(g, e->srcflag.p);
+  sync_g(e);
+  (e->n_launch++, k_src_flags)<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p);
   scan(e, e->srcflag.p, e->srcpos.p, g.N);
   (e->n_launch++, k_src_compact)<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p, e->srcpos.p, g.N, e->srclist.p);
   e->nsrc_list = read_int(e, e->srcpos.p + g.N);
@@ -488,10 +494,12 @@ void ensure_ftab(dre_engine* e, unsigned nkmask) {
     build_dir_table(e, k);
     const size_t npix = (size_t)12 << (2 * k);
     e->ftab[k].ensure(npix * g.ROW, 1.0);
+    sync_g(e);
     e->n_launch++;
-    k_build_ftab<<<cdiv(npix * 32, 256), 256, 0, e->st>>>(g, k, e->ftab[k].p);
+    k_build_ftab<<<cdiv(npix * 32, 256), 256, 0, e->st>>>(k, e->ftab[k].p);
     CK(cudaGetLastError());
     g.ftab[k] = e->ftab[k].p;
+    sync_g(e);
   }
 }
 
@@ -507,7 +515,7 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(e->g, A, u, H, W, e->tasks.p, nT, out, e->counter.p);
+  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, u, H, W, e->tasks.p, nT, out, e->counter.p);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
   e->last_launches++;
@@ -532,7 +540,7 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
   for (int i = 0; i < 2; i++) { e->H[i].ensure(U, L, U); e->W[i].ensure(64, L, U); }
   int cur = 0;
   e->H[0].n = U; e->W[0].n = 0;
-  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(g, u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
+  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
   e->extcnt.ensure(U); e->ext_seg.ensure((size_t)U + 1); e->reco_cnt.ensure(U);
   e->keptH.ensure(U); e->keptW.ensure(U); e->newHcnt.ensure(U); e->newWcnt.ensure(U);
   const int ub = cdiv(U, 256);
@@ -717,6 +725,7 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
   g.rt_type = rt_type;
   const int L = g.L, ndir = g.ndir;
   const size_t NS = (size_t)g.N + e->S;
+  sync_g(e);
   if (scaspe_tot && rt_type == DRE_RTT_I_OBS) planes_io(e, e->tot.p, (double* const*)scaspe_tot, 0);
   // device i_obs arrays: "+=" semantics on the caller's arrays when given, else resident
   const size_t n_out = (size_t)std::max(ndir, 1) * NS * L, n_in = (size_t)std::max(ndir_in, 1) * NS * L;
@@ -728,7 +737,7 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
   e->last_kernel_ms = 0; e->last_launches = 0; e->launch_mark = e->n_launch;
   CK(cudaEventRecord(e->ev[0], e->st));
   if (rt_type == DRE_RTT_I_OBS)   // calc_total_luminosity_sca case(rtt_i_obs) rt_routines.f90:760-771
-    (e->n_launch++, k_lumcell_sca)<<<cdiv((size_t)g.N * L, 256), 256, 0, e->st>>>(g, e->tot.p, e->lumcell.p, 1);
+    (e->n_launch++, k_lumcell_sca)<<<cdiv((size_t)g.N * L, 256), 256, 0, e->st>>>(e->tot.p, e->lumcell.p, 1);
   const int nsrc = build_source_list(e);
   DreIobs q; memset(&q, 0, sizeof(q));
   q.srclist = e->srclist.p; q.nsrc = nsrc; q.ndir = ndir; q.ndir_in = ndir_in; q.obs_dir = e->obs_dir.p;
@@ -779,9 +788,9 @@ int dre_run_iobs(dre_engine* e, int rt_type, const double* const* scaspe_tot, in
     CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
     CK(cudaEventRecord(e->ev[2], e->st));
     e->n_launch++;
-    if (g.KLn == 1) k_iobs<1><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
-    else if (g.KLn == 2) k_iobs<2><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
-    else k_iobs<4><<<ctas, 256, 0, e->st>>>(g, A, q, e->counter.p);
+    if (g.KLn == 1) k_iobs<1><<<ctas, 256, 0, e->st>>>(A, q, e->counter.p);
+    else if (g.KLn == 2) k_iobs<2><<<ctas, 256, 0, e->st>>>(A, q, e->counter.p);
+    else k_iobs<4><<<ctas, 256, 0, e->st>>>(A, q, e->counter.p);
     CK(cudaEventRecord(e->ev[3], e->st));
     CK(cudaGetLastError());
     e->last_launches++;
@@ -845,6 +854,7 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   DRE_REQUIRE(tot_rad_en && cnflag, "dre_prepare_scatt: null output");
   const DreDev& g = e->g;
   const size_t NL = (size_t)g.N * g.L, nsca = (size_t)g.N * (g.ROW - g.L);
+  sync_g(e);
   (e->n_launch++, k_u_rows)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);          // u_fest <- u_final
   CK(cudaMemcpyAsync(e->lum_lost_prev.p, e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToDevice, e->st));
   if (iterations == 1)   // create_scaspe_tot rt_routines.f90:3012-3040: scaspe_tot_arr = scaspe_arr
@@ -852,10 +862,10 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   CK(cudaMemcpyAsync(e->prev.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));  // scaspe_prev <- scaspe
   e->red_d.ensure((size_t)2 * g.L);
   if (iterations == 1) {
-    (e->n_launch++, k_totrad)<<<g.L, 256, 0, e->st>>>(g, e->acc.p, e->red_d.p);
+    (e->n_launch++, k_totrad)<<<g.L, 256, 0, e->st>>>(e->acc.p, e->red_d.p);
     CK(cudaMemcpyAsync(tot_rad_en, e->red_d.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
   }
-  (e->n_launch++, k_lumcell_sca)<<<cdiv(NL, 256), 256, 0, e->st>>>(g, e->acc.p, e->lumcell.p, 0);
+  (e->n_launch++, k_lumcell_sca)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->lumcell.p, 0);
   (e->n_launch++, k_colsum)<<<g.L, 256, 0, e->st>>>(e->lumcell.p, g.N, g.L, e->red_d.p + g.L);
   std::vector<double> tl(g.L);
   CK(cudaMemcpyAsync(tl.data(), e->red_d.p + g.L, g.L * 8, cudaMemcpyDeviceToHost, e->st));
@@ -887,8 +897,9 @@ int dre_locate_points(dre_engine* e, int32_t npts, const double* xyz, const int3
   DRE_REQUIRE(e->have_grid && e->have_params, "dre_locate_points: grid/params not set");
   if (npts <= 0) return 0;
   DBuf<double> dx; DBuf<int> dc, dout;
+  sync_g(e);
   dx.upload(xyz, (size_t)3 * npts, e->st); dc.upload(cc_old, npts, e->st); dout.ensure(npts);
-  (e->n_launch++, k_locate)<<<cdiv(npts, 128), 128, 0, e->st>>>(e->g, npts, dx.p, dc.p, dout.p);
+  (e->n_launch++, k_locate)<<<cdiv(npts, 128), 128, 0, e->st>>>(npts, dx.p, dc.p, dout.p);
   CK(cudaMemcpyAsync(cell_out, dout.p, (size_t)npts * 4, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
   DRE_CATCH(e)

@@ -22,23 +22,24 @@ __host__ __device__ inline int dre_stage_len(int ROW, int split) {
 }
 __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split) {
   ws.pending = 0; ws.stage_len = 0;
-  ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
+  ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
   const int sl = dre_stage_len(g.ROW, split);
-  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 2) * 8;   // keeps 16-B alignment
+  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
   ws.lamof = lam; ws.stage = base; ws.F = base + sl; ws.en2 = base + sl + g.ROW; ws.stage_len = sl;
   ws.mbar = (unsigned long long*)(base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
+  ws.runs = (int*)(ws.mbar + 2);
   ws.fphase = 0; ws.fwait = 0;
   if (lane == 0) mbar_init(ws.mbar);
   __syncthreads();
 }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 2) * 8;
+  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6) * 8;
   return lam_bytes + per * warps;
 }
 
@@ -54,9 +55,10 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL>
-__global__ void __launch_bounds__(512, 1) k_trace(DreDev g, DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
+__global__ void __launch_bounds__(512, 1) k_trace(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
                         DreList out, int* __restrict__ counter) {
   extern __shared__ __align__(128) unsigned char smem[];
+  const DreDev& g = c_g;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpSmem ws;
   dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split);
@@ -151,9 +153,10 @@ struct DreIobs {
   double* i_obs_in;                    // [ndir_in][N+S][L]
 };
 template <int KL>
-__global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counter) {
+__global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
+  const DreDev& g = c_g;
   const int lane = threadIdx.x & 31;
-  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
+  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
 #pragma unroll
@@ -208,12 +211,13 @@ __global__ void k_iobs(DreDev g, DreAccum A, DreIobs q, int* __restrict__ counte
 }
 
 // ---- phase-function table: one warp per pixel of nside 2^k writes calc_ffn_arr for all wavelengths
-__global__ void k_build_ftab(DreDev g, int k, double* __restrict__ rows) {
+__global__ void k_build_ftab(int k, double* __restrict__ rows) {
+  const DreDev& g = c_g;
   const int lane = threadIdx.x & 31;
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long npix = 12ll << (2 * k);
   if (w >= npix) return;
-  WarpSmem ws; ws.pending = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0;
+  WarpSmem ws; ws.pending = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   ws.F = rows + (size_t)w * g.ROW;
   unsigned act[DRE_KL];
   for (int q = 0; q < DRE_KL; q++) { const int rem = g.L - 32 * q; act[q] = rem >= 32 ? 0xffffffffu : (rem > 0 ? ((1u << rem) - 1u) : 0u); }
@@ -221,7 +225,8 @@ __global__ void k_build_ftab(DreDev g, int k, double* __restrict__ rows) {
 }
 
 // ---- cell-list kernel: leaf && sum(lum) /= 0 gate of rt_loop rt_routines.f90:1016 -------
-__global__ void k_src_flags(DreDev g, int* __restrict__ flag) {
+__global__ void k_src_flags(int* __restrict__ flag) {
+  const DreDev& g = c_g;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.N) return;
   double s = 0;
@@ -234,8 +239,9 @@ __global__ void k_src_compact(const int* __restrict__ flag, const int* __restric
 }
 
 // seeds of a batch of units: create_high_ray_list ray_list.f90:71-106 (nside 2 pixel = sector)
-__global__ void k_seed(DreDev g, DreUnits u, DreList H, DreList W, const int* __restrict__ srclist, int unit0, int stride,
+__global__ void k_seed(DreUnits u, DreList H, DreList W, const int* __restrict__ srclist, int unit0, int stride,
                        int rank_off) {
+  const DreDev& g = c_g;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i > u.U) return;
   H.seg[i] = i; W.seg[i] = 0;
@@ -249,7 +255,8 @@ __global__ void k_seed(DreDev g, DreUnits u, DreList H, DreList W, const int* __
 }
 
 // ---- bounding-box / locator kernel: find_cc_new2 for arbitrary points ----------------------
-__global__ void k_locate(DreDev g, int n, const double* __restrict__ xyz, const int* __restrict__ cc_old, int* __restrict__ out) {
+__global__ void k_locate(int n, const double* __restrict__ xyz, const int* __restrict__ cc_old, int* __restrict__ out) {
+  const DreDev& g = c_g;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double src[3] = {0, 0, 0};
@@ -289,7 +296,8 @@ __global__ void k_add_sca(double* __restrict__ dst, const double* __restrict__ s
 }
 // lumcell(l,c) = sum_{p<npix_hp} scaspe(l)(p,c) for leaves (calc_total_luminosity_sca rt_routines.f90:722-740);
 // all = 1 sums the observer slots too (case rtt_i_obs :760-771)
-__global__ void k_lumcell_sca(DreDev g, const double* __restrict__ rows, double* __restrict__ lumcell, int all) {
+__global__ void k_lumcell_sca(const double* __restrict__ rows, double* __restrict__ lumcell, int all) {
+  const DreDev& g = c_g;
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (size_t)g.N * g.L) return;
   const int c = (int)(i / g.L), l = (int)(i % g.L);
@@ -313,7 +321,8 @@ __global__ void k_colsum(const double* __restrict__ a, int N, int L, double* __r
   if (threadIdx.x == 0) out[l] = sh[0];
 }
 // tot_rad_en(l) = sum over ALL cells of the HEALPix part of scaspe (rt_routines.f90:690-698)
-__global__ void k_totrad(DreDev g, const double* __restrict__ rows, double* __restrict__ out) {
+__global__ void k_totrad(const double* __restrict__ rows, double* __restrict__ out) {
+  const DreDev& g = c_g;
   __shared__ double sh[256];
   const int l = blockIdx.x;
   const int off = g.off[l], n = g.npix_hp[l];

@@ -16,7 +16,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdartray_engine.so")
+LIB_PATH = os.environ.get("DARTRAY_ENGINE_LIB", os.path.join(_HERE, "libdartray_engine.so"))  # override: A/B builds
 
 SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
