@@ -411,3 +411,145 @@ def trusti_scene(tau_z=0.01, base=(10, 2), max_lvl=4, lnum=None, kp_sca_max=1, n
                  src_cell=src_cell, cell_src=cell_src, bm_par=10, bm_par_sca=5, bm_par_max=200, rad_lim=0.1,
                  accuracy=0.1, conv_en_lim=0.01, wall_on=(0, 0, 1),
                  wall_coord=(0.0, 0.0, 0.0, 0.0, 0.0 * ms - ms / 2.0, 0.3 * ms - ms / 2.0))
+
+
+# --------------------------------------------------------------------------------------
+# C2: MAGTAR ellipsoidal dust shell with a central point source
+# --------------------------------------------------------------------------------------
+def magtar_grid(tau_z=0.48, base=(10, 3), max_lvl=3, min_lvl=1, max_dtau=0.048, modelsize=10.0,
+                ax=1.09, by=2.18, cz=2.18, width=0.10) -> Grid:
+    """MAGTAR_GRIDS/input_grid_shell.in: av_rho_dust_shell user_routines_magtar.f90:159-210 (9^3 sub-samples
+    of the cell, ellipsoidal radius within `width` of 1) and the 'shell' criterion
+    create_adap_grid_magtar.f90:80-106."""
+    ax, by, cz, width = (float(np.float32(v)) for v in (ax, by, cz, width))  # real32 module variables (:17-23)
+    nstep = 10
+    frac = (np.arange(nstep - 1) + 0.5) / (nstep - 1)
+
+    def calc_dens(x, y, z, cs):
+        xp = (x - cs / 2.0) + frac * cs
+        yp = (y - cs / 2.0) + frac * cs
+        zp = (z - cs / 2.0) + frac * cs
+        rad = np.sqrt((xp[:, None, None] / ax) ** 2 + (yp[None, :, None] / by) ** 2 + (zp[None, None, :] / cz) ** 2)
+        n_in = int((np.abs(rad - 1.0) < width).sum())
+        s = cs / (nstep - 1)
+        return n_in * tau_z * (s * s * s) / cs ** 3, 0.0
+
+    def crit(x, y, z, cs, nlevel, dens, dens_stars):
+        return (dens * cs > max_dtau) or (nlevel < min_lvl)
+
+    tag = f"magtar_t{tau_z}_b{base[0]}_{base[1]}_l{max_lvl}_m{min_lvl}_d{max_dtau}"
+    return _grid_cached(tag, lambda: build_grid(modelsize, base, max_lvl, calc_dens, crit))
+
+
+def magtar_scene(tau_z=0.48, base=(10, 3), max_lvl=3, lnum=None, kp_sca_max=1, max_dtau=0.048, name="magtar") -> Scene:
+    """C2: MAGTAR_GRIDS/input_shell.in — point source at the origin (T_eff 3660 K Planck), 7 directions, no wall."""
+    g = magtar_grid(tau_z, base, max_lvl, max_dtau=max_dtau)
+    t = _load_table("magtar")
+    sel = np.arange(len(t["lambda_um"]))
+    if lnum is not None:
+        sel = np.unique(np.linspace(0, len(sel) - 1, lnum).round().astype(int))
+    L = len(sel)
+    kscale = np.asarray(t["kext_scale"])[sel]
+    gsca = np.asarray(t["gsca"])[sel]
+    theta = np.array([float("%.6g" % v) for v in np.arange(7) * (math.pi / 6)])
+    dir_i_out = np.ascontiguousarray(np.stack([theta, np.zeros(7)]))
+    pos, src_cell, cell_src = prepare_p_src(g, [[0.0, 0.0, 0.0]])
+    return Scene(name=name, grid=g, lambda_um=np.asarray(t["lambda_um"])[sel],
+                 dens_arr=np.ascontiguousarray(g.dens[:, None] * kscale[None, :]),
+                 ksca_norm=np.asarray(t["ksca_norm"])[sel], gsca=gsca, kp_sca=set_kp_sca(gsca, kp_sca_max),
+                 dir_i_out=dir_i_out, lumcell=np.zeros((g.ncell, L)), ccoord_p_src=pos,
+                 lum_p_src=np.ascontiguousarray(np.asarray(t["lum_p_src"])[sel][None, :]),
+                 src_cell=src_cell, cell_src=cell_src, bm_par=10, bm_par_sca=5, bm_par_max=200, rad_lim=0.1,
+                 accuracy=0.1, conv_en_lim=0.01)
+
+
+# --------------------------------------------------------------------------------------
+# C3: galaxy-shaped grid (disk + bulge), every luminous leaf cell emits
+# --------------------------------------------------------------------------------------
+def _zavg_exp(z, cs, zs):
+    """mean of exp(-|z'|/zs) over z' in [z-cs/2, z+cs/2] (analytic vertical cell average)."""
+    a, b = z - cs / 2.0, z + cs / 2.0
+    if a >= 0 or b <= 0:
+        lo, hi = (a, b) if a >= 0 else (-b, -a)
+        return zs * (math.exp(-lo / zs) - math.exp(-hi / zs)) / cs
+    return zs * ((1.0 - math.exp(a / zs)) + (1.0 - math.exp(-b / zs))) / cs
+
+
+def galaxy_grid(base=(3, 3), max_lvl=4, min_lvl=2, max_dtau=0.01, max_dlum=0.5e-6, modelsize=28000.0,
+                z_subd_lim=50.0, r_subd_lim=4000.0, tau_scale=1.0):
+    """Galaxy-shaped stand-in for GALAXY_GRIDS/input_grid_galaxy_example1.in: geometry
+    parameters from the input file (old/young stellar disks h=3200 pc, z=140/50 pc; dust disks
+    tau_B=3.17/0.61, h=5200/3200 pc, z=140/50 pc; bulge r_eff=400 pc; truncation R<14000, |z|<4000),
+    double-exponential profiles, 'standard' subdivision criterion create_adap_grid_galaxy.f90:270-296.
+    Returns (grid, w_old, w_young): dens = B-band extinction coefficient [1/pc]; w_* = per-cell stellar
+    weights (fraction of the component's total luminosity per unit volume)."""
+    rtrun, max_z = 14000.0, 4000.0
+    hs, zs_old, zs_young = 3200.0, 140.0, 50.0
+    hd1, zd1, tau1 = 5200.0, 140.0, 3.17 * tau_scale
+    hd2, zd2, tau2 = 3200.0, 50.0, 0.61 * tau_scale
+    reff, bd = 400.0, 1.0
+    norm_disk = lambda h, z: 4.0 * math.pi * h * h * z      # volume integral of exp(-R/h-|z|/z)
+    norm_bulge = 8.0 * math.pi * (reff / 7.67 ** 4) ** 3 * 0.6 * math.factorial(11) / 4.0   # int exp(-7.67 (m/reff)^(1/4)) dV, q = 0.6
+
+    def comps(x, y, z, cs):
+        R = math.sqrt(x * x + y * y)
+        if R - cs > rtrun or abs(z) - cs / 2.0 > max_z:
+            return 0.0, 0.0, 0.0
+        dust = tau1 / (2.0 * zd1) * math.exp(-R / hd1) * _zavg_exp(z, cs, zd1) + \
+            tau2 / (2.0 * zd2) * math.exp(-R / hd2) * _zavg_exp(z, cs, zd2)
+        m = math.sqrt(R * R + (z / 0.6) ** 2)
+        old = math.exp(-R / hs) * _zavg_exp(z, cs, zs_old) / norm_disk(hs, zs_old) + \
+            bd * math.exp(-7.67 * (max(m, 0.25 * cs) / reff) ** 0.25) / norm_bulge
+        young = math.exp(-R / hs) * _zavg_exp(z, cs, zs_young) / norm_disk(hs, zs_young)
+        return dust, old / (1.0 + bd), young
+
+    def calc_dens(x, y, z, cs):
+        d, o, yv = comps(x, y, z, cs)
+        return d, o + yv
+
+    def crit(x, y, z, cs, nlevel, dens, dens_stars):
+        return (dens * cs > max_dtau) or (0.5 * dens_stars * cs ** 3 > max_dlum) or (nlevel < min_lvl) or \
+            (abs(z) < z_subd_lim and math.sqrt(x * x + y * y) < r_subd_lim)
+
+    tag = f"galaxy_b{base[0]}_{base[1]}_l{max_lvl}_m{min_lvl}_t{max_dtau}_d{max_dlum}_s{tau_scale}"
+    g = _grid_cached(tag, lambda: build_grid(modelsize, base, max_lvl, calc_dens, crit))
+    w_old = np.zeros(g.ncell); w_young = np.zeros(g.ncell)
+    for i in np.nonzero(g.cchild == -1)[0]:
+        _, o, yv = comps(g.ccoord[i, 0], g.ccoord[i, 1], g.ccoord[i, 2], g.csize[i])
+        w_old[i], w_young[i] = o, yv
+    return g, w_old, w_young
+
+
+def galaxy_scene(max_lvl=4, min_lvl=2, lnum=None, kp_sca_max=1, max_dtau=0.01, max_dlum=0.5e-6, tau_scale=1.0,
+                 name="galaxy") -> Scene:
+    """C3: GALAXY_GRIDS/input_galaxy_example1.in — no point sources, every leaf with stellar emissivity
+    emits (rtt_precalc_cell / rtt_dir_cell), 8 directions theta = 0..pi/2, z wall [0.3, 0.7]."""
+    g, w_old, w_young = galaxy_grid(max_lvl=max_lvl, min_lvl=min_lvl, max_dtau=max_dtau, max_dlum=max_dlum, tau_scale=tau_scale)
+    t = _load_table("galaxy")
+    sel = np.arange(len(t["lambda_um"]))
+    if lnum is not None:
+        sel = np.unique(np.linspace(0, len(sel) - 1, lnum).round().astype(int))
+    L = len(sel)
+    kscale = np.asarray(t["kext_scale"])[sel]
+    gsca = np.asarray(t["gsca"])[sel]
+    sed_old = np.asarray(t["sed_old"], dtype=np.float64); sed_young = np.asarray(t["sed_young"], dtype=np.float64)
+    # the pt11 SED files stop at 2.2 um: continue with a Rayleigh-Jeans-like fall-off (synthetic)
+    lam = np.asarray(t["lambda_um"])
+    for sed in (sed_old, sed_young):
+        last = int(np.nonzero(sed)[0][-1])
+        for j in range(last + 1, len(sed)):
+            sed[j] = sed[last] * (lam[last] / lam[j]) ** 2
+    vol = g.csize ** 3
+    lumcell = (w_old * vol)[:, None] * sed_old[sel][None, :] + (w_young * vol)[:, None] * sed_young[sel][None, :]
+    lumcell[g.cchild != -1] = 0.0
+    theta = np.array([0.0, 0.224399481500898, 0.448798963001796, 0.673198444502694, 0.897597926003592,
+                      1.12199740750449, 1.34639688900539, 1.57079637050629])
+    dir_i_out = np.ascontiguousarray(np.stack([theta, np.zeros(8)]))
+    ms = g.modelsize
+    return Scene(name=name, grid=g, lambda_um=lam[sel], dens_arr=np.ascontiguousarray(g.dens[:, None] * kscale[None, :]),
+                 ksca_norm=np.asarray(t["ksca_norm"])[sel], gsca=gsca, kp_sca=set_kp_sca(gsca, kp_sca_max),
+                 dir_i_out=dir_i_out, lumcell=np.ascontiguousarray(lumcell), ccoord_p_src=np.zeros((0, 3)),
+                 lum_p_src=np.zeros((0, L)), src_cell=np.full(g.ncell, -1, dtype=np.int32),
+                 cell_src=np.zeros(0, dtype=np.int32), bm_par=5, bm_par_sca=5, bm_par_max=200, rad_lim=0.1,
+                 accuracy=0.3, conv_en_lim=0.01, wall_on=(0, 0, 1),
+                 wall_coord=(0.0, 0.0, 0.0, 0.0, 0.3 * ms - ms / 2.0, 0.7 * ms - ms / 2.0))

@@ -124,3 +124,19 @@ def test_trusti_small_full_sequence(small_trusti):
 
 def test_trusti_tiny_thick(tiny_trusti):
     run_sequence(tiny_trusti, record=4_000_000, iterations=3)
+
+
+def test_magtar_small_full_sequence(small_magtar):
+    """C2: point source on a cell corner (fix_ccoord_p_src), isotropic + kp 0 + kp 1 wavelengths, no wall."""
+    run_sequence(small_magtar, record=12_000_000, iterations=2)
+
+
+def test_galaxy_tiny_full_sequence(tiny_galaxy):
+    """C3: emitting cells (rtt_precalc_cell / rtt_dir_cell / rtt_i_obs_dir_cell, quirk Q3), z wall."""
+    run_sequence(tiny_galaxy, record=2_000_000, iterations=2)
+
+
+def test_galaxy_small_counters(small_galaxy):
+    """C3 at 3 levels: 2909 sources x 48 sectors; counters + order-independent intersection checksum
+    (1.1e8 intersections: the record list is not kept)."""
+    run_sequence(small_galaxy, record=0, iterations=1)
