@@ -34,6 +34,18 @@ enum { MODE_PRECALC = 0, MODE_DEP = 1, MODE_IOBS = 2 };
 // (rt_routines.f90:1945-1953) is reproduced bit for bit.
 struct __align__(32) DreDir { double st, ct, sp, cp; };
 
+// Per-cell traversal record (64 B, one L2 line half): centre + the six face neighbours.
+// nbr[2*axis + (inc>0)] is the result of the reference's neighbour step restricted to the levels
+// <= lvl(cell) -- `increment` (smooth_grid_routines.f90:751-769) followed by the tree descent
+// `ccindd_to_cc` (:820-852), which for those levels depends on the integer tree coordinates only:
+//   DRE_NBR_OUT               the ray leaves the model (carry out of level 1, rt_routines.f90:1790)
+//   bit 31 clear              leaf reached at level (e >> 27) & 15 <= lvl(cell), id = e & 0x7ffffff
+//   bit 31 set                the same-level neighbour is subdivided; e & 0x7fffffff = its first child:
+//                             the descent continues with digits taken from the exit point (:1807-1838)
+// Built on the device by k_build_nbr at dre_set_grid.
+#define DRE_NBR_OUT 0xffffffffu
+struct __align__(64) DreCell { double c[3]; unsigned nbr[6]; int lvl; int pad; double csize; };   // csize = csize(cell), not csize_arr(lvl)
+
 // Static inputs in HBM (SoA).  Passed to kernels by value (lives in the constant bank).
 struct DreDev {
   // grid: smooth_grid_routines.f90:41-70
@@ -46,6 +58,7 @@ struct DreDev {
   const long long* cindex;  // [N]
   const double* ccoord;     // [N][3]
   const double* csize;      // [N]
+  const DreCell* cell;      // [N] traversal records
   double csize_arr[DRE_MAXLVL + 1], carea_arr[DRE_MAXLVL + 1], cvol_arr[DRE_MAXLVL + 1];
   // opacity / scattering classes
   int L, KLn;               // wavelengths, ceil(L/32)
@@ -131,30 +144,32 @@ __device__ __forceinline__ int dre_outcube(const double r[3], double cellsize) {
 
 // find_cc_new2 rt_routines.f90:1962-2066.  Returns 0 ok, 1 outside the model, 2 reference STOP.
 __device__ DRE_RARE int dre_locate(const DreDev& g, const double src[3], const double d[3], double prev,
-                                          int cc_old, int& cc_new, int& clvl, unsigned long long c[3]) {
+                                          int cc_old, int& cc_new, int& clvl) {
   double p[3], rel[3], q[3];
   for (int i = 0; i < 3; i++) p[i] = src[i] + prev * d[i];
   for (int i = 0; i < 3; i++) if (fabs(p[i]) > g.par.modelsize / 2.) return 1;
-  for (int i = 0; i < 3; i++) rel[i] = p[i] - g.ccoord[3 * (size_t)cc_old + i];
-  if (dre_outcube(rel, g.csize[cc_old]) == 0) {
-    clvl = g.lvl[cc_old]; cc_new = cc_old;
-    dre_decode(g, cc_new, clvl, c);
-    return 0;
-  }
+  const DreCell* co = &g.cell[cc_old];
+  for (int i = 0; i < 3; i++) rel[i] = p[i] - co->c[i];
+  const int lold = co->lvl;
+  if (dre_outcube(rel, co->csize) == 0) { clvl = lold; cc_new = cc_old; return 0; }   // csize(cc_old), :1991
   for (int i = 0; i < 3; i++) q[i] = p[i] + g.par.modelsize / 2.;
-  c[0] = c[1] = c[2] = 0;
+  int l = 1; bool found = false;
   for (int i = 1; i <= g.max_lvl; i++) {
     const int b = dre_base(g, i);
     const double cs = g.csize_arr[i];
+    int v[3];
     for (int a = 0; a < 3; a++) {
-      int v = (int)(q[a] / cs);
-      if (v == b) v = b - 1;
-      c[a] = cx_set(c[a], i, v);
-      q[a] = q[a] - v * cs;
+      v[a] = (int)(q[a] / cs);
+      if (v[a] == b) v[a] = b - 1;
+      q[a] = q[a] - v[a] * cs;
     }
+    l += (v[2] * b + v[1]) * b + v[0];
+    const int ch = __ldg(&g.cchild[l]);
+    if (ch == -1) { cc_new = l; clvl = i; found = true; break; }
+    l = ch;
   }
-  if (!dre_descend(g, c, cc_new, clvl)) return 2;
-  for (int i = 0; i < 3; i++) rel[i] = p[i] - g.ccoord[3 * (size_t)cc_new + i];
+  if (!found) return 2;
+  for (int i = 0; i < 3; i++) rel[i] = p[i] - g.cell[cc_new].c[i];
   return dre_outcube(rel, g.csize_arr[clvl]) == 0 ? 0 : 2;
 }
 

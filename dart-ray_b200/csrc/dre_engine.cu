@@ -51,6 +51,7 @@ struct dre_engine {
   DreDev g;
   bool have_grid = false, have_opacity = false, have_sources = false, have_params = false;
   DBuf<int> cchild, src_cell, ik_sca, npix_hp, npix, off; DBuf<unsigned char> lvl; DBuf<long long> cindex;
+  DBuf<DreCell> cells;
   DBuf<double> ccoord, csize, dens, ksca, gsca, lumcell, ccoord_p_src, lum_p_src;
   DBuf<unsigned short> lamof;
   DBuf<DreDir> class_dir[DRE_MAXCLASS], dirtab[DRE_MAXK + 1], obs_dir;
@@ -215,6 +216,13 @@ int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2
   CK(cudaStreamSynchronize(e->st));
   g.cchild = e->cchild.p; g.lvl = e->lvl.p; g.cindex = e->cindex.p; g.ccoord = e->ccoord.p; g.csize = e->csize.p;
   for (int i = 0; i <= max_lvl; i++) { g.csize_arr[i] = csize_arr[i]; g.carea_arr[i] = carea_arr[i]; g.cvol_arr[i] = cvol_arr[i]; }
+  DRE_REQUIRE(N < (1 << 27), "dre_set_grid: more than 2^27 cells");
+  e->cells.ensure(N);
+  sync_g(e);
+  (e->n_launch++, k_build_nbr)<<<cdiv((size_t)N * 6, 256), 256, 0, e->st>>>(e->cells.p);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(e->st));
+  g.cell = e->cells.p;
   e->have_grid = true; e->have_opacity = false; e->have_sources = false;
   DRE_CATCH(e)
 }

@@ -254,6 +254,49 @@ __global__ void k_seed(DreUnits u, DreList H, DreList W, const int* __restrict__
   for (int l = 0; l < g.L; l++) H.lum[(size_t)i * g.L + l] = dre_src_lum(g, nc, l);
 }
 
+// ---- traversal records: centre, level, size and the six tabulated neighbour steps of every cell.
+// One thread per (cell, face): cindex_to_ccindd (smooth_grid_routines.f90:793-813), `increment`
+// (:751-769) along the face axis, then ccindd_to_cc (:820-852) restricted to the levels <= lvl(cell).
+__global__ void k_build_nbr(DreCell* __restrict__ cells) {
+  const DreDev& g = c_g;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= g.N * 6) return;
+  const int cc = t / 6, face = t % 6, axis = face >> 1;
+  const int clvl = g.lvl[cc];
+  if (face == 0) {
+    DreCell* o = &cells[cc];
+    for (int a = 0; a < 3; a++) o->c[a] = g.ccoord[3 * (size_t)cc + a];
+    o->lvl = clvl; o->pad = 0; o->csize = g.csize[cc];
+  }
+  unsigned e = DRE_NBR_OUT;
+  if (clvl >= 1) {
+    unsigned long long c[3];
+    dre_decode(g, cc, clvl, c);
+    int k = (face & 1) ? 1 : -1;
+    unsigned long long ca = c[axis];
+    for (int j = clvl; j >= 1; j--) {
+      const int b = dre_base(g, j);
+      int v = cx_get(ca, j) + k;
+      if (v >= b) v = 0; else if (v < 0) v = b - 1; else k = 0;
+      ca = cx_set(ca, j, v);
+      if (k == 0) break;
+    }
+    c[axis] = ca;
+    if (k == 0) {
+      int l = 1;
+      for (int i = 1; i <= clvl; i++) {
+        const int b = dre_base(g, i);
+        l += (cx_get(c[2], i) * b + cx_get(c[1], i)) * b + cx_get(c[0], i);
+        const int ch = g.cchild[l];
+        if (ch == -1) { e = (unsigned)l | ((unsigned)i << 27); break; }
+        if (i == clvl) { e = 0x80000000u | (unsigned)ch; break; }
+        l = ch;
+      }
+    }
+  }
+  cells[cc].nbr[face] = e;
+}
+
 // ---- bounding-box / locator kernel: find_cc_new2 for arbitrary points ----------------------
 __global__ void k_locate(int n, const double* __restrict__ xyz, const int* __restrict__ cc_old, int* __restrict__ out) {
   const DreDev& g = c_g;
@@ -261,8 +304,8 @@ __global__ void k_locate(int n, const double* __restrict__ xyz, const int* __res
   if (i >= n) return;
   const double src[3] = {0, 0, 0};
   const double d[3] = {xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2]};
-  int cc_new = -1, clvl = 0; unsigned long long c[3];
-  const int rc = dre_locate(g, src, d, 1.0, cc_old[i], cc_new, clvl, c);
+  int cc_new = -1, clvl = 0;
+  const int rc = dre_locate(g, src, d, 1.0, cc_old[i], cc_new, clvl);
   out[i] = (rc == 0) ? cc_new : -1;
 }
 // pix2vec = pix2ang_nest + calc_cproj from the direction table
