@@ -71,7 +71,7 @@ struct dre_engine {
   // wavefront scratch
   ListStore H[2], W[2], OUT;
   DBuf<int> u_nc, u_gid, u_nk, u_step, u_mode, u_task_seg;
-  DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, leader, unit_of_ext, ntask, nreco,
+  DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, leader, unit_of_ext, ntask, nreco,
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
   // options
@@ -571,15 +571,15 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
     const int nExt = read_int(e, e->ext_seg.p + U);
     int nT = 0;
     if (nExt > 0) {
-      e->ext.ensure(nExt); e->ipx.ensure(nExt); e->gone.ensure(nExt); e->cand.ensure((size_t)3 * nExt); e->ncand.ensure(nExt);
+      e->ext.ensure(nExt); e->ipx.ensure(nExt); e->gone.ensure(nExt); e->cand.ensure((size_t)3 * nExt); e->ncand.ensure(nExt); e->nxt.ensure(nExt); e->hasprev.ensure(nExt);
       e->leader.ensure(nExt); e->unit_of_ext.ensure(nExt); e->ntask.ensure(nExt); e->nreco.ensure(nExt);
       e->task_off.ensure((size_t)nExt + 1); e->reco_off.ensure((size_t)nExt + 1);
       const int xb = cdiv(nExt, 256);
-      if (nH > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
-      if (nW > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p);
+      if (nH > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p, e->hasprev.p);
+      if (nW > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p, e->hasprev.p);
       (e->n_launch++, k_unit_of_ext)<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->unit_of_ext.p);
-      (e->n_launch++, k_cand)<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p);
-      (e->n_launch++, k_resolve)<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->cand.p, e->ncand.p, e->gone.p, e->leader.p);
+      (e->n_launch++, k_cand)<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p, e->nxt.p, e->hasprev.p);
+      (e->n_launch++, k_resolve)<<<xb, 256, 0, e->st>>>(u, e->unit_of_ext.p, nExt, e->cand.p, e->ncand.p, e->nxt.p, e->hasprev.p, e->gone.p, e->leader.p);
       (e->n_launch++, k_count)<<<xb, 256, 0, e->st>>>(Hc, u, e->ext_seg.p, e->ext.p, nExt, e->unit_of_ext.p, e->ncand.p, e->leader.p, e->ntask.p, e->nreco.p);
       scan(e, e->ntask.p, e->task_off.p, nExt);
       scan(e, e->nreco.p, e->reco_off.p, nExt);
@@ -671,6 +671,8 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   e->g.rt_type = rt_type;
   ensure_dir_tables(e);
   e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
+  // psel_av_arr(i0, iterations, :) is a fresh slice in every pass (rt_routines.f90:1446, io_routines.f90:3874)
+  { const size_t NS = (size_t)e->g.N + e->S; e->psel_sum.zero(NS, e->st); e->ipsel.zero(NS, e->st); }
   e->last_kernel_ms = 0; e->last_launches = 0; e->launch_mark = e->n_launch;
   CK(cudaEventRecord(e->ev[0], e->st));
   const int nsrc = build_source_list(e);

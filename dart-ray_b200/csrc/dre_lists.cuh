@@ -81,13 +81,13 @@ __global__ void k_unit_ext(DreUnits u, const int* __restrict__ segH, const int* 
 // pixel at the current nside (ang2pix_nest(nside, theta, phi), ray_list.f90:218) and gone = 0.
 __global__ void k_fill_ext(DreList l, DreUnits u, int which, const int* __restrict__ sel, const int* __restrict__ pos,
                            const int* __restrict__ ext_seg, int* __restrict__ ext, int* __restrict__ ipx,
-                           int* __restrict__ gone) {
+                           int* __restrict__ gone, int* __restrict__ hasprev) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= l.n || !sel[i]) return;
   const int un = l.unit[i];
   const int x = ext_seg[un] + (pos[i] - pos[l.seg[un]]);
   ext[x] = i;
-  gone[x] = 0;
+  gone[x] = 0; hasprev[x] = 0;
   if (which == 2) {
     const unsigned m = l.meta[i];
     ipx[x] = l.dir_ipix[i] >> (2 * (META_DIRK(m) - u.nk[un]));
@@ -99,32 +99,39 @@ __global__ void k_fill_ext(DreList l, DreUnits u, int which, const int* __restri
 // leader).  `gone` is NOT consulted for the members, as in the reference (SURVEY A.3 note).
 __global__ void k_cand(DreList w, DreUnits u, const int* __restrict__ ext_seg, const int* __restrict__ ext,
                        const int* __restrict__ unit_of_ext, const int* __restrict__ ipx, int next,
-                       int* __restrict__ cand, int* __restrict__ ncand) {
+                       int* __restrict__ cand, int* __restrict__ ncand, int* __restrict__ nxt, int* __restrict__ hasprev) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= next) return;
   const int un = unit_of_ext[x];
-  if (u.mode[un] != 2) { ncand[x] = 0; return; }
+  if (u.mode[un] != 2) { ncand[x] = 0; nxt[x] = -1; return; }
   const int i = ext[x];
   const int end = ext_seg[un + 1];
   const int ip = ipx[x], isel = META_ISEL(w.meta[i]);
   const double dpl = w.dplane[i];
-  int n = 0;
-  for (int y = x + 1; y < end && n < 3; y++) {
+  int n = 0, first = -1;
+  for (int y = x + 1; y < end && (n < 3 || first < 0); y++) {
     if (ipx[y] != ip) continue;
+    if (first < 0) first = y;
+    if (n == 3) break;
     const int j = ext[y];
     if (META_ISEL(w.meta[j]) != isel) continue;
     if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) cand[3 * (size_t)x + n++] = y;
   }
   ncand[x] = n;
+  nxt[x] = first;                 // chain of the entries of this unit with the same parent pixel
+  if (first >= 0) hasprev[first] = 1;
 }
 
 // leader resolution in list order (ray_list.f90:222-226, 268, 290): an entry is a leader unless an
-// earlier leader already consumed it.  One thread per LOW-mode unit.
-__global__ void k_resolve(DreUnits u, const int* __restrict__ ext_seg, const int* __restrict__ cand,
-                          const int* __restrict__ ncand, int* __restrict__ gone, int* __restrict__ leader) {
-  const int un = blockIdx.x * blockDim.x + threadIdx.x;
-  if (un >= u.U || u.mode[un] != 2) return;
-  for (int x = ext_seg[un]; x < ext_seg[un + 1]; x++) {
+// earlier leader already consumed it.  Members always share the leader's parent pixel, so the entries
+// of one (unit, parent pixel) chain are independent of every other chain: one thread walks each chain
+// in list order (the head is the entry no earlier entry links to).
+__global__ void k_resolve(DreUnits u, const int* __restrict__ unit_of_ext, int next, const int* __restrict__ cand,
+                          const int* __restrict__ ncand, const int* __restrict__ nxt, const int* __restrict__ hasprev,
+                          int* __restrict__ gone, int* __restrict__ leader) {
+  const int x0 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x0 >= next || u.mode[unit_of_ext[x0]] != 2 || hasprev[x0]) return;
+  for (int x = x0; x >= 0; x = nxt[x]) {
     if (gone[x]) { leader[x] = 0; continue; }
     leader[x] = 1;
     for (int m = 0; m < ncand[x]; m++) gone[cand[3 * (size_t)x + m]] = 1;
