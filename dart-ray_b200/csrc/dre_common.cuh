@@ -15,6 +15,9 @@
 #define DRE_MAXLVL 8        // tree levels packed 8 bits each into one 64-bit word per axis
 #define DRE_MAXK 13         // log2 of the largest HEALPix nside (8192, healpix_routines.f90:9)
 #define DRE_KL 4            // wavelengths per lane: lnum <= 32*DRE_KL
+#ifndef DRE_TRACE_THREADS
+#define DRE_TRACE_THREADS 512   // threads per CTA of the ray-march kernel (register budget = 65536 / threads)
+#endif
 #define DRE_MAXCLASS 4      // scattering-resolution classes kp = 0..3 (set_npix_arr rt_routines.f90:5289)
 #define DRE_NSIDE_MIN_K 2   // nside_min = 4, rt_routines.f90:60
 
@@ -70,7 +73,7 @@ struct DreDev {
   const int* npix_hp;       // [L]
   const int* npix;          // [L] npix_hp + ndir
   const int* off;           // [L] offset of wavelength l inside an accumulator row
-  const unsigned short* lamof; // [ROW] element -> index into the per-warp en2[2L] array (u slots: l, scaspe slots: L+l)
+  const unsigned short* lamof; // [ROW] scaspe element -> byte offset 8*l of its wavelength in the per-warp en_sca array
   int ROW;                  // doubles per accumulator row: [0,L) u_final, then scaspe blocks (even-padded)
   int nclass;
   int class_kp[DRE_MAXCLASS], class_np[DRE_MAXCLASS], class_nhp[DRE_MAXCLASS];

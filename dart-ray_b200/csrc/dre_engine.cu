@@ -270,8 +270,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   g.ROW = off;
   DRE_REQUIRE(g.ROW < 65536, "dre_set_opacity: accumulator row too long");
   std::vector<unsigned short> lam(g.ROW, 0);
-  for (int l = 0; l < L; l++) lam[l] = (unsigned short)l;
-  for (int l = 0; l < L; l++) for (int p = 0; p < e->h_npix[l] + (e->h_npix[l] & 1); p++) lam[e->h_off[l] + p] = (unsigned short)(L + l);
+  for (int l = 0; l < L; l++) for (int p = 0; p < e->h_npix[l] + (e->h_npix[l] & 1); p++) lam[e->h_off[l] + p] = (unsigned short)(8 * l);   // byte offset of en_sca(l) in the per-warp array
   e->lamof.upload(lam.data(), g.ROW, e->st);
   e->ik_sca.upload(e->h_ik.data(), L, e->st); e->npix_hp.upload(e->h_npix_hp.data(), L, e->st);
   e->npix.upload(e->h_npix.data(), L, e->st); e->off.upload(e->h_off.data(), L, e->st);
@@ -487,7 +486,7 @@ int build_source_list(dre_engine* e) {
 int trace_warps(dre_engine* e, size_t* smem) {
   const DreDev& g = e->g;
   int w = std::max(1, std::min(e->opt_warps, 32));
-  w = std::min(w, 16);
+  w = std::min(w, DRE_TRACE_THREADS / 32);
   while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) * e->opt_ctas_per_sm > (size_t)224 * 1024) w--;
   *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split);
   DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
@@ -930,6 +929,19 @@ int dre_pix2vec(dre_engine* e, int32_t nside, int32_t npix, const int32_t* ipix,
   CK(cudaMemcpyAsync(vec, dv.p, (size_t)3 * npix * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
   if (theta && phi) for (int i = 0; i < npix; i++) hp::pix2ang_nest(nside, ipix[i], theta[i], phi[i]);
+  DRE_CATCH(e)
+}
+
+int dre_eval_exp(dre_engine* e, int32_t n, const double* x, double* y) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  if (n <= 0) return 0;
+  DRE_REQUIRE(x && y, "dre_eval_exp: null pointer");
+  DBuf<double> dx, dy;
+  dx.upload(x, n, e->st); dy.ensure(n);
+  (e->n_launch++, k_eval_exp)<<<cdiv(n, 256), 256, 0, e->st>>>(n, dx.p, dy.p);
+  CK(cudaMemcpyAsync(y, dy.p, (size_t)n * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
   DRE_CATCH(e)
 }
 

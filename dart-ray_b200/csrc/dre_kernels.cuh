@@ -55,7 +55,7 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL>
-__global__ void __launch_bounds__(512, 1) k_trace(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
+__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
                         DreList out, int* __restrict__ counter) {
   extern __shared__ __align__(128) unsigned char smem[];
   const DreDev& g = c_g;
@@ -307,6 +307,10 @@ __global__ void k_locate(int n, const double* __restrict__ xyz, const int* __res
   int cc_new = -1, clvl = 0;
   const int rc = dre_locate(g, src, d, 1.0, cc_old[i], cc_new, clvl);
   out[i] = (rc == 0) ? cc_new : -1;
+}
+__global__ void k_eval_exp(int n, const double* __restrict__ x, double* __restrict__ y) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = dre_exp(x[i]);
 }
 // pix2vec = pix2ang_nest + calc_cproj from the direction table
 __global__ void k_pix2vec(const DreDir* __restrict__ tab, int n, const int* __restrict__ ipix, double* __restrict__ vec) {

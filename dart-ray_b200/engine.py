@@ -22,7 +22,7 @@ SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
     "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_build_source_list",
-    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
+    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
 
@@ -236,6 +236,12 @@ class Engine:
         out = np.zeros(len(cc_old), dtype=np.int32)
         self._ck(self.l.dre_locate_points(self.h, C.c_int32(len(cc_old)), abi.dptr(xyz), abi.iptr(cc_old), abi.iptr(out)))
         return out
+
+    def eval_exp(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.zeros_like(x)
+        self._ck(self.l.dre_eval_exp(self.h, C.c_int32(x.size), abi.dptr(x), abi.dptr(y)))
+        return y
 
     def pix2vec(self, nside, ipix):
         ipix = np.ascontiguousarray(ipix, dtype=np.int32)

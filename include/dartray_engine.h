@@ -163,6 +163,8 @@ int dre_pix2vec(dre_engine*, int32_t nside, int32_t npix, const int32_t* ipix,
 int dre_set_record(dre_engine*, int64_t max_records);   /* 0 disables */
 int dre_get_records(dre_engine*, dre_isect* out, int64_t cap, int64_t* n);
 int dre_set_option(dre_engine*, const char* name, double value);
+/* evaluates the ray-march kernel's exp() (attenuation, deposit rt_routines.f90:2380-2381) on n host values */
+int dre_eval_exp(dre_engine*, int32_t n, const double* x, double* y);
 /* timing hooks: CUDA events on the engine's stream (print_time io_routines.f90:4268 is wall clock) */
 int dre_mark(dre_engine*, int slot /*0..7*/);
 int dre_elapsed_ms(dre_engine*, int slot_a, int slot_b, double* ms /*out; synchronises*/);

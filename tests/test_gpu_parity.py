@@ -140,3 +140,19 @@ def test_galaxy_small_counters(small_galaxy):
     """C3 at 3 levels: 2909 sources x 48 sectors; counters + order-independent intersection checksum
     (1.1e8 intersections: the record list is not kept)."""
     run_sequence(small_galaxy, record=0, iterations=1)
+
+
+def test_kernel_exp_within_one_ulp(tiny_trusti):
+    """The ray-march kernel's exp (constant-bank coefficients) against glibc/numpy exp: <= 1 ulp over the
+    attenuation range, exact at 0, and finite / correct beyond the fast range."""
+    eng = _engine(tiny_trusti)
+    rng = np.random.default_rng(11)
+    x = -np.concatenate([[0.0], 10.0 ** rng.uniform(-12, 2.8, 200000), [707.9, 708.0, 709.5, 745.0, 800.0]])
+    y = eng.eval_exp(x)
+    ref = np.exp(x)
+    assert y[0] == 1.0
+    big = ref > 1e-300
+    ulp = np.abs(y[big] - ref[big]) / np.spacing(ref[big])
+    assert ulp.max() <= 1.0, ulp.max()
+    assert np.allclose(y[~big], ref[~big], rtol=1e-10, atol=5e-324)
+    eng.close()
