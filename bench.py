@@ -35,6 +35,17 @@ def load_scene(name):
         return scenes.trusti_scene(), "TRUST-I slab tau=0.01 (input_trustI_tau0.01_LD.in): 21801 cells, 32 wavelengths, 1 point source"
     if name == "trustI_small":
         return scenes.trusti_scene(lnum=4, max_lvl=3), "TRUST-I slab reduced (5801 cells, 4 wavelengths)"
+    if name == "galaxy":
+        sc = scenes.galaxy_scene(max_lvl=3, min_lvl=2)
+        return sc, ("galaxy-shaped grid, input_galaxy_example1.in parameters with max_lvl=3 (one level less than EX1 so that a "
+                    f"step takes about a second): {sc.grid.ncell} cells, {int((sc.lumcell.sum(axis=1) > 0).sum())} emitting leaf cells, {sc.lnum} wavelengths")
+    if name == "galaxy_full":
+        sc = scenes.galaxy_scene()
+        return sc, (f"galaxy-shaped grid at the EX1 depth (max_lvl=4): {sc.grid.ncell} cells, "
+                    f"{int((sc.lumcell.sum(axis=1) > 0).sum())} emitting leaf cells, {sc.lnum} wavelengths")
+    if name == "magtar":
+        sc = scenes.magtar_scene()
+        return sc, f"MAGTAR ellipsoidal shell (input_shell.in): {sc.grid.ncell} cells, {sc.lnum} wavelengths, 1 point source"
     fn = getattr(scenes, name + "_scene", None)
     if fn is None:
         raise SystemExit(f"unknown workload {name}")
@@ -158,47 +169,68 @@ def solve_host(eng, scene, abi, hs, max_iterations=30):
     has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
     up = down = 0
     isect = 0
+    t_call = 0.0
     seq = ([abi.RTT_PRECALC_CELL] if has_cell else []) + ([abi.RTT_PRECALC_SRC] if has_src else []) + \
           ([abi.RTT_DIR_CELL] if has_cell else []) + ([abi.RTT_DIR_SRC] if has_src else [])
     for rt in seq:
         pre = rt in (abi.RTT_PRECALC_CELL, abi.RTT_PRECALC_SRC)
+        t0 = time.perf_counter()
         c = eng.rt_loop_host(rt, 0, hs)
+        t_call += time.perf_counter() - t0
         isect += c.intersections
         up += hs.nbytes_up(pre, False); down += hs.nbytes_down(pre)
     leaf = scene.grid.cchild == -1
     tot_rad_en = np.zeros(scene.lnum)
     nhp = scene.npix_hp
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1))   # the Fortran host runs these array loops under OpenMP
     for it in range(1, max_iterations + 1):
         hs.u_fest[...] = hs.u_final
         hs.lum_lost_prev[...] = hs.lum_lost
-        for l in range(scene.lnum):
+
+        def prep(l):
+            sca = hs.scaspe[l]
+            row = sca[:, :nhp[l]].sum(axis=1)
             if it == 1:
-                hs.scaspe_tot[l][...] = hs.scaspe[l]
-                tot_rad_en[l] = hs.scaspe[l][:, :nhp[l]].sum()
-            hs.scaspe_prev[l][...] = hs.scaspe[l]
-            hs.lumcell[:, l] = np.where(leaf, hs.scaspe[l][:, :nhp[l]].sum(axis=1), 0.0)
+                hs.scaspe_tot[l][...] = sca
+                tot_rad_en[l] = row.sum()
+            else:
+                hs.scaspe_tot[l] += sca
+            hs.scaspe_prev[l][...] = sca
+            hs.lumcell[:, l] = np.where(leaf, row, 0.0)
+            sca[...] = 0
+
+        list(pool.map(prep, range(scene.lnum)))
         tl = hs.lumcell.sum(axis=0)
         conv = bool(np.all(tl / tot_rad_en < scene.conv_en_lim)) if tot_rad_en.sum() > 0 else True
-        for l in range(scene.lnum):
-            if it > 1:
-                hs.scaspe_tot[l] += hs.scaspe[l]
-            hs.scaspe[l][...] = 0
         if conv:
             break
         eng.set_sources(hs.lumcell)
         up += hs.lumcell.nbytes
+        t0 = time.perf_counter()
         c = eng.rt_loop_host(abi.RTT_SCATT, it, hs)
+        t_call += time.perf_counter() - t0
         isect += c.intersections
         up += hs.nbytes_up(False, True); down += hs.nbytes_down(False)
-    return isect, up, down
+    pool.shutdown()
+    return isect, up, down, t_call
 
 
-def cpu_sample(scene, abi, st, target_s=15.0, nthreads=None):
-    """Oracle on all host cores: scattering iteration 1 restricted to units with gid % K == 0."""
+def sample_pass(scene, abi):
+    """The pass the CPU baseline samples: the one that dominates the solve (direct light of the emitting
+    cells when every leaf emits, else scattering iteration 1)."""
+    if bool(np.any(scene.lumcell)):
+        return abi.RTT_DIR_CELL, 0, "direct light of the emitting cells (rtt_dir_cell)"
+    return abi.RTT_SCATT, 1, "scattering iteration 1 (rtt_scatt)"
+
+
+def cpu_sample(scene, abi, st, target_s=15.0, nthreads=None, K_fixed=None):
+    """Oracle on all host cores: the sampled pass restricted to units with gid % K == 0."""
     from oracle import oracle as O
     nthreads = nthreads or os.cpu_count() or 1
     orc = O.Oracle(scene, nthreads=nthreads)
-    orc.set_sources(st.lumcell)
+    rt, it, what = sample_pass(scene, abi)
+    orc.set_sources(st.lumcell if rt == abi.RTT_SCATT else scene.lumcell)
 
     def run(K):
         s2 = O.State(scene)
@@ -206,17 +238,63 @@ def cpu_sample(scene, abi, st, target_s=15.0, nthreads=None):
         for l in range(scene.lnum):
             s2.scaspe_prev[l][...] = st.scaspe_prev[l]
         t0 = time.perf_counter()
-        c = orc.run_pass(abi.RTT_SCATT, 1, s2, rank=0, nranks=K)
+        c = orc.run_pass(rt, it, s2, rank=0, nranks=K)
         return c, time.perf_counter() - t0
 
-    K = 64
+    if K_fixed is not None:
+        c, dt = run(K_fixed)
+        return c, dt, K_fixed, nthreads, what
+    K = 256
     c, dt = run(K)
     full_est = dt * K
     K2 = max(1, int(round(full_est / target_s)))
     if K2 < K:
         c, dt = run(K2)
         K = K2
-    return c, dt, K, nthreads
+    return c, dt, K, nthreads, what
+
+
+def cpu_state_oracle(scene, abi):
+    """State in front of the sampled pass, produced by the oracle itself (reference arm: no GPU)."""
+    from oracle import oracle as O
+    orc = O.Oracle(scene, nthreads=os.cpu_count() or 1)
+    st = O.State(scene)
+    rt, it, _ = sample_pass(scene, abi)
+    has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
+    if has_cell:
+        orc.run_pass(abi.RTT_PRECALC_CELL, 0, st)
+    if has_src:
+        orc.run_pass(abi.RTT_PRECALC_SRC, 0, st)
+    if rt == abi.RTT_SCATT:
+        if has_cell:
+            orc.run_pass(abi.RTT_DIR_CELL, 0, st)
+        if has_src:
+            orc.run_pass(abi.RTT_DIR_SRC, 0, st)
+        orc.prepare_scatt(1, st)
+    return st
+
+
+def cpu_state_engine(eng, scene, abi):
+    """The same state produced by the engine (our arm: untimed setup of the CPU sample)."""
+    from oracle import oracle as O
+    st = O.State(scene)
+    for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST):
+        eng.zero(a)
+    eng.set_sources(scene.lumcell)
+    rt, it, _ = sample_pass(scene, abi)
+    has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
+    if has_cell:
+        eng.rt_loop(abi.RTT_PRECALC_CELL)
+    if has_src:
+        eng.rt_loop(abi.RTT_PRECALC_SRC)
+    if rt == abi.RTT_SCATT:
+        if has_cell:
+            eng.rt_loop(abi.RTT_DIR_CELL)
+        if has_src:
+            eng.rt_loop(abi.RTT_DIR_SRC)
+        eng.rt_prepare_scatt(1, np.zeros(scene.lnum))
+    eng.download_state(st)
+    return st
 
 
 def main():
@@ -225,7 +303,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="trustI")
+    ap.add_argument("--workload", default="galaxy")
+    ap.add_argument("--no-also", action="store_true", help="skip the secondary workloads (TRUST-I, MAGTAR)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--option", action="append", default=[], help="engine option name=value")
@@ -239,30 +318,25 @@ def main():
     scene, desc = load_scene(args.workload)
     metric, unit = "ray-cell intersections/s (direct+scatter solve)", "intersections/s"
     config = {"workload": desc, "solve": "precalc + direct + scattering iterations to conv_en_lim=%g" % scene.conv_en_lim,
-              "l2_policy": "working set (accumulator rows %.0f MB) exceeds the 126 MB L2" %
+              "l2_policy": "L2 flushed (256 MB written) before every timed step; accumulator rows %.0f MB" %
                            (scene.grid.ncell * (scene.lnum + int(scene.npix.sum())) * 8 / 1e6)}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        from oracle import oracle as O
         ncores = os.cpu_count() or 1
-        orc = O.Oracle(scene, nthreads=ncores)
-        st = O.State(scene)
         t0 = time.perf_counter()
-        orc.run_pass(abi.RTT_PRECALC_SRC if scene.nsrc else abi.RTT_PRECALC_CELL, 0, st)
-        orc.run_pass(abi.RTT_DIR_SRC if scene.nsrc else abi.RTT_DIR_CELL, 0, st)
-        orc.prepare_scatt(1, st)
+        st = cpu_state_oracle(scene, abi)
         setup_s = time.perf_counter() - t0
         vals = []
         K = None
-        for i in range(args.warmup + args.steps):
-            c, dt, K, nth = cpu_sample(scene, abi, st, target_s=12.0 if K is None else 12.0, nthreads=ncores)
-            if i >= args.warmup:
+        for i in range(max(1, args.warmup) + args.steps):   # the first (warm-up) call also calibrates the sample size
+            c, dt, K, nth, what = cpu_sample(scene, abi, st, target_s=10.0, nthreads=ncores, K_fixed=K)
+            if i >= max(1, args.warmup):
                 vals.append((c.intersections, dt))
         n = sum(v[0] for v in vals); t = sum(v[1] for v in vals)
         v = n / t
-        sample = f"scattering iteration 1, units with id % {K} == 0 ({vals[-1][0]} intersections per step); untimed setup {setup_s:.1f} s"
+        sample = f"{what}, units with id % {K} == 0 ({vals[-1][0]} intersections per step); untimed setup {setup_s:.1f} s"
         print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
                           "warmup": args.warmup, "ms_per_step": 1e3 * t / max(1, len(vals)), "higher_is_better": True,
                           "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
@@ -280,6 +354,11 @@ def main():
         obj = [engine.Engine.get_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(obj, src=0)
         nccl_id = obj[0]
+    def new_id():
+        obj = [engine.Engine.get_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        return obj[0]
+
     eng = engine.Engine(scene, device=local_rank, rank=rank, nranks=world, nccl_id=nccl_id)
     for o in args.option:
         k, v = o.split("=")
@@ -305,46 +384,90 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    for _ in range(args.warmup):
-        solve_resident(eng, scene, abi)
-    barrier()
-    l0 = eng.launch_count()
-    step_ms, last = [], None
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def flush_l2():
+        flush_buf.zero_()
+        torch.cuda.synchronize()
+
+    def measure(e_, sc_, steps, warmup):
+        """`steps` timed solves (device time between two events on the engine's stream, max over ranks)."""
+        for _ in range(warmup):
+            solve_resident(e_, sc_, abi)
+        barrier()
+        l0 = e_.launch_count()
+        step_ms, last = [], None
+        for _ in range(steps):
+            flush_l2()
+            barrier()
+            e_.mark(0)
+            last = solve_resident(e_, sc_, abi)
+            e_.mark(1)
+            step_ms.append(maxr(e_.elapsed_ms(0, 1)))
+            barrier()
+        launches = e_.launch_count() - l0
+        isect = sumr(float(sum(c.intersections for _, c in last)))
+        deposits = sumr(float(sum(c.deposits for _, c in last)))
+        ms = float(np.mean(step_ms))
+        dep = [c for n, c in last if n.startswith("dir") or n.startswith("scatt")]
+        abytes = sumr(float(sum(algorithmic_bytes(c) for c in dep)))
+        kms = maxr(float(sum(c.kernel_ms for c in dep)))
+        return {"ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "kms": kms, "last": last, "launches": launches,
+                "trace_launches": int(sum(c.trace_launches for c in dep))}
+
     with ClockSampler(local_rank) as clk:
-        for _ in range(args.steps):
-            barrier()
-            eng.mark(0)
-            last = solve_resident(eng, scene, abi)
-            eng.mark(1)
-            step_ms.append(maxr(eng.elapsed_ms(0, 1)))
-            barrier()
-    launches = eng.launch_count() - l0
+        m = measure(eng, scene, args.steps, args.warmup)
     clocks = clk.summary()
-    isect = sumr(float(sum(c.intersections for _, c in last)))
-    deposits = sumr(float(sum(c.deposits for _, c in last)))
-    ms = float(np.mean(step_ms))
+    ms, isect, last = m["ms"], m["isect"], m["last"]
     value = isect / (ms * 1e-3)
-    dep = [c for n, c in last if n.startswith("dir") or n.startswith("scatt")]
-    abytes = sum(algorithmic_bytes(c) for c in dep)
-    kms = sum(c.kernel_ms for c in dep)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    ach = abytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+
+    def roofline(mm):
+        # algorithmic bytes of all ranks / (ranks x the slowest rank's ray-march kernel time): per-GPU GB/s
+        ach = mm["abytes"] / world / (mm["kms"] * 1e-3) / 1e9 if mm["kms"] > 0 else 0.0
+        return ach
+
+    ach = roofline(m)
+    traffic = None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of the captured launch (profiles/, ncu --set full)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj["bytes_per_launch"] if args.workload == "galaxy" else None
+    except Exception:
+        tj = None
     roof = {"bound": "hbm", "kernel": "k_trace<MODE_DEP>", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
-            "algorithmic_bytes_per_step": abytes, "kernel_ms_per_step": kms,
-            "launches_per_step": int(sum(c.trace_launches for c in dep))}
+            "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
+            "algorithmic_bytes_per_step": m["abytes"], "kernel_ms_per_step": m["kms"], "launches_per_step": m["trace_launches"],
+            "per": "GPU (algorithmic bytes of the whole job / n_gpus / slowest rank's kernel time)",
+            "traffic_note": (tj or {}).get("launch") if traffic is not None else None}
     line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(launches),
-            "s_per_wavelength": ms * 1e-3 / scene.lnum, "intersections_per_step": isect, "deposits_per_step": deposits,
+            "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(m["launches"]),
+            "s_per_wavelength": ms * 1e-3 / scene.lnum, "intersections_per_step": isect, "deposits_per_step": m["deposits"],
             "passes": {n: {"ms": round(c.pass_ms, 3), "kernel_ms": round(c.kernel_ms, 3), "intersections": c.intersections,
                            "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
             "roofline": roof}
+
+    # the other workloads the metric is quoted on (north star: TRUST-I slab and the MAGTAR shell), same engine options
+    if not args.no_also:
+        also = {}
+        for w in [x for x in ("trustI", "magtar") if x != args.workload]:
+            sc2, desc2 = load_scene(w)
+            e2 = engine.Engine(sc2, device=local_rank, rank=rank, nranks=world, nccl_id=None if world == 1 else new_id())
+            for o in args.option:
+                k, v = o.split("=")
+                e2.set_option(k, float(v))
+            m2 = measure(e2, sc2, 2, 1)
+            a2 = roofline(m2)
+            also[w] = {"workload": desc2, "value": m2["isect"] / (m2["ms"] * 1e-3), "ms_per_step": m2["ms"],
+                       "s_per_wavelength": m2["ms"] * 1e-3 / sc2.lnum, "intersections_per_step": m2["isect"],
+                       "roofline_frac": a2 / peak, "roofline_achieved_gbs": a2, "steps": 2, "warmup": 1}
+            e2.close()
+        line["also"] = also
 
     if not args.no_e2e:
         hs = HostState(scene)
@@ -353,26 +476,18 @@ def main():
         t0 = time.perf_counter()
         n_e2e = 1
         for _ in range(n_e2e):
-            isect_h, up, down = solve_host(eng, scene, abi, hs)
+            isect_h, up, down, t_call = solve_host(eng, scene, abi, hs)
         barrier()
         dt = maxr(time.perf_counter() - t0) / n_e2e
         line["e2e"] = {"value": sumr(float(isect_h)) / dt, "unit": unit, "h2d_bytes_per_step": int(up), "d2h_bytes_per_step": int(down),
-                       "ms_per_step": dt * 1e3, "timing": "host wall clock around dre_run_pass calls (uploads and downloads inside)"}
+                       "ms_per_step": dt * 1e3, "ms_in_dre_run_pass": t_call * 1e3,
+                       "ms_host_rt_prepare": (dt - t_call) * 1e3, "timing": "host wall clock around dre_run_pass calls (uploads and downloads inside)"}
 
     if rank == 0 and world == 1 and not args.no_cpu:
-        from oracle import oracle as O
-        st = O.State(scene)
-        # state before scattering iteration 1, produced by the engine (setup only, untimed)
-        for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST):
-            eng.zero(a)
-        eng.set_sources(scene.lumcell)
-        eng.rt_loop(abi.RTT_PRECALC_SRC if scene.nsrc else abi.RTT_PRECALC_CELL)
-        eng.rt_loop(abi.RTT_DIR_SRC if scene.nsrc else abi.RTT_DIR_CELL)
-        eng.rt_prepare_scatt(1, np.zeros(scene.lnum))
-        eng.download_state(st)
-        c, dt, K, nth = cpu_sample(scene, abi, st)
+        st = cpu_state_engine(eng, scene, abi)      # untimed setup on the GPU; the timed part below is CPU only
+        c, dt, K, nth, what = cpu_sample(scene, abi, st)
         line["cpu_baseline"] = {"value": c.intersections / dt, "unit": unit, "cores": nth, "kind": "port",
-                                "sample": f"scattering iteration 1, units with id % {K} == 0: {c.intersections} intersections in {dt:.1f} s"}
+                                "sample": f"{what}, units with id % {K} == 0: {c.intersections} intersections in {dt:.1f} s"}
     if rank == 0:
         print(json.dumps(line))
     eng.close()

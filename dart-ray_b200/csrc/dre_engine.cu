@@ -78,6 +78,9 @@ struct dre_engine {
   int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 5;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
+  long long peak_entries = 0;
+  size_t list_budget = 0;          // bytes the ray lists of a batch may take (half of the memory free after configuration)
+  double per_unit_est[16] = {0};   // list entries per unit of the last pass, by rt_type
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
   cudaEvent_t marks[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
@@ -287,6 +290,8 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   e->u_fest.zero(NL, e->st); e->lum_lost.zero(L, e->st); e->lum_lost_prev.zero(L, e->st);
   e->lumcell.zero(NL, e->st); g.lumcell = e->lumcell.p;
   CK(cudaStreamSynchronize(e->st));
+  for (double& x : e->per_unit_est) x = 0;
+  e->list_budget = 0;
   e->have_opacity = true; e->have_sources = false;
   DRE_CATCH(e)
 }
@@ -343,16 +348,23 @@ double* rows_of(dre_engine* e, int which) {
   return nullptr;
 }
 void planes_io(dre_engine* e, double* rows, double* const* planes, int dir) {
+  // The Fortran side holds one (P(l), N) plane per wavelength (ragged scaspe_arr(l)%a).  All planes go through
+  // one device staging buffer: the copies are queued back to back on the stream, the transposes to / from the
+  // accumulator-row layout follow, and the host waits once.
   const DreDev& g = e->g;
+  size_t tot = 0;
+  std::vector<size_t> offs(g.L);
+  for (int l = 0; l < g.L; l++) { offs[l] = tot; tot += (size_t)g.N * e->h_npix[l]; }
+  e->tmp_d.ensure(tot);
   for (int l = 0; l < g.L; l++) {
     const int P = e->h_npix[l];
     const size_t n = (size_t)g.N * P;
-    e->tmp_d.ensure(n);
-    if (dir == 0) CK(cudaMemcpyAsync(e->tmp_d.p, planes[l], n * 8, cudaMemcpyHostToDevice, e->st));
-    (e->n_launch++, k_plane_rows)<<<cdiv(n, 256), 256, 0, e->st>>>(rows, e->tmp_d.p, g.N, P, g.ROW, e->h_off[l], dir);
-    if (dir == 1) CK(cudaMemcpyAsync(planes[l], e->tmp_d.p, n * 8, cudaMemcpyDeviceToHost, e->st));
-    CK(cudaStreamSynchronize(e->st));
+    double* t = e->tmp_d.p + offs[l];
+    if (dir == 0) CK(cudaMemcpyAsync(t, planes[l], n * 8, cudaMemcpyHostToDevice, e->st));
+    (e->n_launch++, k_plane_rows)<<<cdiv(n, 256), 256, 0, e->st>>>(rows, t, g.N, P, g.ROW, e->h_off[l], dir);
+    if (dir == 1) CK(cudaMemcpyAsync(planes[l], t, n * 8, cudaMemcpyDeviceToHost, e->st));
   }
+  CK(cudaStreamSynchronize(e->st));
 }
 void u_final_io(dre_engine* e, double* host, int dir) {
   const DreDev& g = e->g;
@@ -537,7 +549,9 @@ void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const Dre
   }
 }
 
-void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
+// returns the largest number of list entries + tasks alive in one step of the batch
+long long run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
+  long long peak = U;
   const DreDev& g = e->g;
   unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
   const int L = g.L;
@@ -608,6 +622,7 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
     CK(cudaStreamSynchronize(e->st));
     if (nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; }
     const int nH2 = tot2[0], nW2 = tot2[1];
+    peak = std::max(peak, (long long)nH + nW + nT + nH2 + nW2);
     // the seg arrays were just written: grow the payload arrays only (seg is sized U+1 already)
     e->H[nx].ensure(std::max(nH2, 1), L, U); e->W[nx].ensure(std::max(nW2, 1), L, U);
     e->H[nx].n = nH2; e->W[nx].n = nW2;
@@ -631,6 +646,7 @@ void run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
     if (hv[0] == 0) break;
     nkmask = (unsigned)hmask;
   }
+  return peak;
 }
 
 void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
@@ -678,10 +694,33 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   const long long total_units = (long long)nsrc * 48;
   const long long mine = total_units > e->rank ? (total_units - e->rank + e->nranks - 1) / e->nranks : 0;
   DreAccum A = make_accum(e, e->prev.p);
-  for (long long u0 = 0; u0 < mine; u0 += e->opt_batch_units) {
-    const int U = (int)std::min<long long>(e->opt_batch_units, mine - u0);
-    run_batch(e, mode, A, (int)u0, U);
+  // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known
+  // in advance.  Start from a quarter of the configured batch, measure list entries per unit, and size the
+  // following batches so that the lists stay within a third of the free device memory.
+  if (e->list_budget == 0) {     // once per configuration: cudaMemGetInfo costs ~10 ms, and the list buffers are kept afterwards
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    e->list_budget = free_b / 2;
   }
+  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0;   // H/W double buffers + OUT + index arrays, DBuf slack
+  const double max_entries = std::max(1.0e6, (double)e->list_budget / bytes_per_entry);
+  // entries per unit seen in the previous pass of this type (same scene): lets a warm engine start with full batches
+  double& est = e->per_unit_est[rt_type % 16];
+  double per_unit = 0;
+  long long U_next = est > 0 ? (long long)(max_entries / (1.5 * est))
+                             : std::max<long long>(e->opt_batch_units / 4, 3072);
+  U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
+  for (long long u0 = 0; u0 < mine;) {
+    const int U = (int)std::min<long long>(U_next, mine - u0);
+    const long long peak = run_batch(e, mode, A, (int)u0, U);
+    e->peak_entries = std::max(e->peak_entries, peak);
+    per_unit = std::max(per_unit, (double)peak / U);
+    if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries (%.1f per unit)\n", rt_type, u0, U, peak, (double)peak / U);
+    u0 += U;
+    U_next = (long long)(max_entries / (1.5 * std::max(per_unit, est)));   // x1.5: headroom for units richer than those seen so far
+    U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
+  }
+  est = std::max(est, per_unit);   // high-water mark (the scattering iterations share one rt_type and shrink)
   CK(cudaEventRecord(e->ev[1], e->st));
   CK(cudaStreamSynchronize(e->st));
   float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));

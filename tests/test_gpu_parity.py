@@ -156,3 +156,17 @@ def test_kernel_exp_within_one_ulp(tiny_trusti):
     assert ulp.max() <= 1.0, ulp.max()
     assert np.allclose(y[~big], ref[~big], rtol=1e-10, atol=5e-324)
     eng.close()
+
+
+@pytest.mark.parametrize("kind", ["trusti", "galaxy"])
+def test_two_gpus_match_one(kind):
+    """(e) multi-GPU: 2 ranks over NCCL (units sharded cyclically, dre_allreduce = rt_mpi) against one GPU."""
+    import os, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29517", os.path.join(root, "tests", "multigpu_check.py"), kind],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "multigpu_check ok" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
