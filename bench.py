@@ -109,22 +109,32 @@ def solve_resident(eng, scene, abi, max_iterations=30):
     eng.set_sources(scene.lumcell)
     has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
     cs = []
+    mpi_t = [0.0]
+    _rt_mpi = eng.rt_mpi
+
+    def rt_mpi(rt):
+        t0 = time.perf_counter()
+        _rt_mpi(rt)
+        mpi_t[0] += time.perf_counter() - t0
+
+    eng_rt_mpi = rt_mpi
     if has_cell:
         cs.append(("precalc_cell", eng.rt_loop(abi.RTT_PRECALC_CELL)))
     if has_src:
         cs.append(("precalc_src", eng.rt_loop(abi.RTT_PRECALC_SRC)))
-    eng.rt_mpi(abi.RTT_PRECALC_SRC)
+    eng_rt_mpi(abi.RTT_PRECALC_SRC)
     if has_cell:
         cs.append(("dir_cell", eng.rt_loop(abi.RTT_DIR_CELL)))
     if has_src:
         cs.append(("dir_src", eng.rt_loop(abi.RTT_DIR_SRC)))
-    eng.rt_mpi(abi.RTT_DIR_SRC)
+    eng_rt_mpi(abi.RTT_DIR_SRC)
     tot = np.zeros(scene.lnum)
     for it in range(1, max_iterations + 1):
         if eng.rt_prepare_scatt(it, tot):
             break
         cs.append((f"scatt{it}", eng.rt_loop(abi.RTT_SCATT, it)))
-        eng.rt_mpi(abi.RTT_SCATT)
+        eng_rt_mpi(abi.RTT_SCATT)
+    solve_resident.last_mpi_ms = mpi_t[0] * 1e3
     return cs
 
 
@@ -310,6 +320,7 @@ def main():
     ap.add_argument("--option", action="append", default=[], help="engine option name=value")
     args = ap.parse_args()
 
+    os.environ["NCCL_DEBUG"] = os.environ.get("DRE_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout (one JSON line)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -412,7 +423,10 @@ def main():
         dep = [c for n, c in last if n.startswith("dir") or n.startswith("scatt")]
         abytes = sumr(float(sum(algorithmic_bytes(c) for c in dep)))
         kms = maxr(float(sum(c.kernel_ms for c in dep)))
-        return {"ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "kms": kms, "last": last, "launches": launches,
+        mpi_ms = maxr(getattr(solve_resident, "last_mpi_ms", 0.0))
+        psum = float(sum(c.pass_ms for _, c in last))
+        pass_minmax = [-maxr(-psum), maxr(psum)]     # fastest / slowest rank: device time inside the passes
+        return {"pass_minmax": pass_minmax, "mpi_ms": mpi_ms, "ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "kms": kms, "last": last, "launches": launches,
                 "trace_launches": int(sum(c.trace_launches for c in dep))}
 
     with ClockSampler(local_rank) as clk:
@@ -450,7 +464,7 @@ def main():
             "s_per_wavelength": ms * 1e-3 / scene.lnum, "intersections_per_step": isect, "deposits_per_step": m["deposits"],
             "passes": {n: {"ms": round(c.pass_ms, 3), "kernel_ms": round(c.kernel_ms, 3), "intersections": c.intersections,
                            "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
-            "roofline": roof}
+            "rt_mpi_ms_per_step": m["mpi_ms"], "rank_pass_ms_min_max": m["pass_minmax"], "roofline": roof}
 
     # the other workloads the metric is quoted on (north star: TRUST-I slab and the MAGTAR shell), same engine options
     if not args.no_also:
