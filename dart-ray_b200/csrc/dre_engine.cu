@@ -971,6 +971,30 @@ int dre_pix2vec(dre_engine* e, int32_t nside, int32_t npix, const int32_t* ipix,
   DRE_CATCH(e)
 }
 
+int dre_calc_sed(dre_engine* e, double dist_obs, int units, const double* lambda_si, double* sed) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  const DreDev& g = e->g;
+  DRE_REQUIRE(sed != nullptr && dist_obs > 0, "dre_calc_sed: bad arguments");
+  DRE_REQUIRE(units >= 0 && units <= 2 && (units != 2 || lambda_si), "dre_calc_sed: units must be 0, 1 or 2 (2 needs lambda_si)");
+  DRE_REQUIRE(e->i_obs.p && g.ndir > 0, "dre_calc_sed: no i_obs pass was run");
+  DBuf<double> dl, ds; DBuf<int> dc;
+  std::vector<double> lam(g.L, 0.0);
+  if (lambda_si) lam.assign(lambda_si, lambda_si + g.L);
+  dl.upload(lam.data(), g.L, e->st);
+  std::vector<int> cs(std::max(e->S, 1), 0);
+  for (int i = 0; i < e->S; i++) cs[i] = e->h_cell_src[i];
+  dc.upload(cs.data(), cs.size(), e->st);
+  ds.ensure((size_t)g.ndir * g.L);
+  sync_g(e);
+  (e->n_launch++, k_sed)<<<g.ndir * g.L, 256, 0, e->st>>>(e->i_obs.p, dc.p, dist_obs, units, dl.p, ds.p);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(sed, ds.p, (size_t)g.ndir * g.L * 8, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
 int dre_eval_exp(dre_engine* e, int32_t n, const double* x, double* y) {
   DRE_TRY(e)
   CK(cudaSetDevice(e->device));

@@ -379,6 +379,29 @@ __global__ void k_totrad(const double* __restrict__ rows, double* __restrict__ o
   for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
   if (threadIdx.x == 0) out[l] = sh[0];
 }
+// calc_sed / sum_i_obs sed_routines.f90:90-146, 212-246 on the device-resident i_obs array [ndir][N+S][L]:
+// sed[j][l] = sum_c i_obs * conv(l) * (csize(c)/dist_obs)^2 + the point sources (size of their host cell).
+// One block per (direction, wavelength); strided partial sums + a tree: fixed order for a fixed block size.
+__global__ void k_sed(const double* __restrict__ i_obs, const int* __restrict__ cell_src, double dist_obs, int units,
+                      const double* __restrict__ lambda_si, double* __restrict__ sed) {
+  const DreDev& g = c_g;
+  __shared__ double sh[256];
+  const int l = blockIdx.x % g.L, j = blockIdx.x / g.L;
+  const size_t NS = (size_t)g.N + g.S;
+  const double parsec = (double)3.08567758e16f, cspeed = (double)2.99792458e8f;
+  double s = 0;
+  for (size_t q = threadIdx.x; q < NS; q += blockDim.x) {
+    double v = i_obs[((size_t)j * NS + q) * g.L + l];
+    if (units == 0) { v = v * 1e-7; v = v * 1e26 / (parsec * parsec); }
+    else if (units == 1) { v = v * 1e26 / (parsec * parsec); }
+    else { v = v * (lambda_si[l] * lambda_si[l]) / cspeed; v = v * 1e26 / (parsec * parsec); }
+    const double cs = (q < (size_t)g.N) ? g.csize[q] : g.csize[cell_src[q - g.N]];
+    s += v * ((cs / dist_obs) * (cs / dist_obs));
+  }
+  sh[threadIdx.x] = s; __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) sed[(size_t)j * g.L + l] = sh[0];
+}
 // u part of the rows <-> (N,L) array.  dir 0: rows <- u ; 1: u <- rows
 __global__ void k_u_rows(double* __restrict__ rows, double* __restrict__ u, int N, int L, int ROW, int dir) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("DARTRAY_ENGINE_LIB", os.path.join(_HERE, "libdartray_
 SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
-    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_build_source_list",
+    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_calc_sed", "dre_build_source_list",
     "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
@@ -211,6 +211,14 @@ class Engine:
                                      abi.dptr(st.i_obs) if st is not None else None,
                                      abi.dptr(st.i_obs_in) if (st is not None and nin) else None, C.byref(cnt)))
         return cnt
+
+    def calc_sed(self, dist_obs, units, lambda_si=None):
+        """calc_sed (sed_routines.f90:90) from the device-resident i_obs array; returns (ndir, L) [Jy]."""
+        sed = np.zeros((self.scene.ndir, self.scene.lnum))
+        lam = None if lambda_si is None else np.ascontiguousarray(lambda_si, dtype=np.float64)
+        self._ck(self.l.dre_calc_sed(self.h, C.c_double(dist_obs), C.c_int(units), abi.dptr(lam) if lam is not None else None,
+                                     abi.dptr(sed)))
+        return sed
 
     def rt_mpi(self, rt_type):
         self._ck(self.l.dre_allreduce(self.h, C.c_int(rt_type)))

@@ -149,6 +149,12 @@ int dre_allreduce(dre_engine*, int rt_type);
 int dre_prepare_scatt(dre_engine*, int iterations, double conv_en_lim,
                       double* tot_rad_en /*(L) inout*/, int32_t* cnflag /*out*/);
 
+/* calc_sed / sum_i_obs (sed_routines.f90:90-146, 212-246) on the i_obs array left on the device by dre_run_iobs:
+ * sed(l, j) = sum over cells and point sources of i_obs(l, c, j) * conv(l) * (csize / dist_obs)^2  [Jy].
+ * units: 0 'erg/s/Hz/pc^2/sr', 1 'W/Hz/pc^2/sr', 2 'W/m/pc^2/sr' (lambda_si (L) required).  sed is (lnum, ndir). */
+int dre_calc_sed(dre_engine*, double dist_obs, int units, const double* lambda_si /*(L) or NULL*/,
+                 double* sed /*(L,ndir) out*/);
+
 /* ---- separate small kernels (north star: cell-list and bounding-box kernels) */
 /* leaf && sum(lum)>0 gate of rt_loop rt_routines.f90:1016; returns the list length */
 int dre_build_source_list(dre_engine*, int rt_type, int32_t* n_sources, int32_t* list_out /*(N) or NULL*/);

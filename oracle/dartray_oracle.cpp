@@ -1168,6 +1168,33 @@ int orc_prepare_scatt(orc_ctx* o, int iterations, double conv_en_lim, double* u_
   return 0;
 }
 
+// calc_sed / sum_i_obs sed_routines.f90:90-146, 212-246: sed(l, j) = sum_c i_obs(l, c, j) * conv(l) * (csize(c)/dist_obs)^2
+// (+ the point sources with the size of their host cell), sequential sums in cell order.
+// units: 0 'erg/s/Hz/pc^2/sr', 1 'W/Hz/pc^2/sr', 2 'W/m/pc^2/sr' (needs lambda_si).  i_obs is (L, N+S, ndir) Fortran order.
+int orc_calc_sed(orc_ctx* o, int32_t ndir, const double* i_obs, double dist_obs, int units, const double* lambda_si,
+                 double* sed /*(L, ndir) Fortran order*/) {
+  Ctx& c = o->c;
+  const int L = c.L, N = c.N, S = c.S;
+  const size_t NS = (size_t)N + S;
+  const double parsec = (double)3.08567758e16f, cspeed = (double)2.99792458e8f;
+  for (int l = 0; l < L; l++) {
+    for (int j = 0; j < ndir; j++) {
+      double s = 0, sp = 0;
+      for (size_t q = 0; q < NS; q++) {
+        double v = i_obs[((size_t)j * NS + q) * L + l];
+        if (units == 0) { v = v * 1e-7; v = v * 1e26 / (parsec * parsec); }
+        else if (units == 1) { v = v * 1e26 / (parsec * parsec); }
+        else { v = v * (lambda_si[l] * lambda_si[l]) / cspeed; v = v * 1e26 / (parsec * parsec); }
+        const double cs = (q < (size_t)N) ? c.csize[q] : c.csize[c.cell_src[q - N]];
+        const double w = (cs / dist_obs) * (cs / dist_obs);
+        if (q < (size_t)N) s += v * w; else sp += v * w;
+      }
+      sed[(size_t)j * L + l] = (S > 0) ? s + sp : s;
+    }
+  }
+  return 0;
+}
+
 int orc_get_lumcell(orc_ctx* o, double* out) { memcpy(out, o->c.lumcell.data(), sizeof(double) * o->c.lumcell.size()); return 0; }
 
 void orc_pix2ang_nest(int nside, int n, const int32_t* ipix, double* theta, double* phi) {

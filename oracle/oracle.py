@@ -127,6 +127,14 @@ class Oracle:
             raise RuntimeError(self.l.orc_last_error(self.h).decode())
         return cnt
 
+    def calc_sed(self, st, dist_obs, units, lambda_si=None):
+        """calc_sed (sed_routines.f90:90) on st.i_obs; returns (ndir, L)."""
+        sed = np.zeros((self.scene.ndir, self.scene.lnum))
+        lam = np.ascontiguousarray(lambda_si if lambda_si is not None else np.zeros(self.scene.lnum), dtype=np.float64)
+        self.l.orc_calc_sed(self.h, C.c_int32(self.scene.ndir), abi.dptr(st.i_obs), C.c_double(dist_obs), C.c_int(units),
+                            abi.dptr(lam), abi.dptr(sed))
+        return sed
+
     def prepare_scatt(self, iterations, st):
         flag = C.c_int32(0)
         self.l.orc_prepare_scatt(self.h, C.c_int(iterations), C.c_double(self.scene.conv_en_lim), abi.dptr(st.u_fest),

@@ -83,6 +83,9 @@ def run_sequence(scene, record=0, iterations=2):
         c_g = eng.rt_loop_iobs(rt, gst)
         assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
         assert_fields_close(gst.i_obs, st.i_obs, f"i_obs after pass {rt}")
+        assert_fields_close(eng.calc_sed(1.0e4, 0), orc.calc_sed(st, 1.0e4, 0), f"SED (direct light) after pass {rt}")
+        if len(scene.ccoord_obs):
+            assert_fields_close(gst.i_obs_in, st.i_obs_in, f"i_obs_in after pass {rt}")
     # scattering iterations
     tot_g = np.zeros(scene.lnum)
     for it in range(1, iterations + 1):
@@ -115,6 +118,11 @@ def run_sequence(scene, record=0, iterations=2):
     c_g = eng.rt_loop_iobs(abi.RTT_I_OBS, gst)
     assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
     assert_fields_close(gst.i_obs, st.i_obs, "i_obs after rtt_i_obs")
+    lam_si = np.asarray(scene.lambda_um) * 1e-6
+    for units in (0, 1, 2):     # N1: calc_sed / sum_i_obs (sed_routines.f90:90-246) in the three i_obs unit systems
+        assert_fields_close(eng.calc_sed(1.0e6, units, lam_si), orc.calc_sed(st, 1.0e6, units, lam_si), f"SED units {units}")
+    if len(scene.ccoord_obs):
+        assert_fields_close(gst.i_obs_in, st.i_obs_in, "i_obs_in after rtt_i_obs")
     eng.close()
 
 
@@ -170,3 +178,13 @@ def test_two_gpus_match_one(kind):
                         "127.0.0.1", "--master-port", "29517", os.path.join(root, "tests", "multigpu_check.py"), kind],
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "multigpu_check ok" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_internal_observer_iobs(tiny_galaxy):
+    """C4 (2DTO3D example: rt_algorithm 'i_obs' with an internal observer at (8000, 0, 0)): rt_loop_iobs rays
+    towards internal observers (find_theta_phi_obs_in rt_routines.f90:3164-3217, ray_type_i_obs_in :1762-1769),
+    direct and scattered light, on the galaxy-shaped grid."""
+    import copy
+    sc = copy.copy(tiny_galaxy)
+    sc.ccoord_obs = np.array([[8000.0, 0.0, 0.0], [-3000.0, 5000.0, 700.0]])
+    run_sequence(sc, record=0, iterations=1)
