@@ -73,6 +73,7 @@ struct DreDev {
   const int* npix_hp;       // [L]
   const int* npix;          // [L] npix_hp + ndir
   const int* off;           // [L] offset of wavelength l inside an accumulator row
+  int off_c[32 * DRE_KL], npix_c[32 * DRE_KL];   // the same tables in the constant bank (warp-uniform lookups)
   const unsigned short* lamof; // [ROW] scaspe element -> byte offset 8*l of its wavelength in the per-warp en_sca array
   int ROW;                  // doubles per accumulator row: [0,L) u_final, then scaspe blocks (even-padded)
   int nclass;

@@ -74,8 +74,9 @@ struct dre_engine {
   DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, leader, unit_of_ext, ntask, nreco,
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
+  DBuf<DreRay> rays;
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 5;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 4;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
@@ -284,6 +285,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   CK(cudaStreamSynchronize(e->st));
   g.dens = e->dens.p; g.ksca = e->ksca.p; g.gsca = e->gsca.p; g.ik_sca = e->ik_sca.p; g.npix_hp = e->npix_hp.p;
   g.npix = e->npix.p; g.off = e->off.p; g.lamof = e->lamof.p;
+  for (int l = 0; l < 32 * DRE_KL; l++) { g.off_c[l] = l < L ? e->h_off[l] : 0; g.npix_c[l] = l < L ? e->h_npix[l] : 0; }
   // device-resident accumulators (zero-initialised)
   const size_t NL = (size_t)N * L;
   e->acc.zero(e->rows_elems(), e->st); e->prev.zero(e->rows_elems(), e->st); e->tot.zero(e->rows_elems(), e->st);
@@ -531,10 +533,15 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
   }
   const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
+  // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance
+  const int chunk = std::max(1, std::min(e->opt_chunk, nT / (ctas * warps * 8)));
+  e->rays.ensure(nT);
+  e->n_launch++;
+  k_prep_rays<MODE><<<cdiv(nT, 128), 128, 0, e->st>>>(u, H, W, e->tasks.p, nT, e->rays.p);
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, u, H, W, e->tasks.p, nT, out, e->counter.p);
+  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, H, W, e->rays.p, nT, out, e->counter.p, chunk);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
   e->last_launches++;
@@ -653,6 +660,16 @@ void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
   unsigned long long c[16];
   CK(cudaMemcpyAsync(c, e->counters.p, sizeof(c), cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
+#ifdef DRE_TIMING
+  { unsigned long long t[16]; CK(cudaMemcpyFromSymbol(t, g_dre_tim, sizeof(t)));
+    double tot = 0; for (int i = 0; i < 16; i++) tot += (double)t[i];
+    const char* nm[16] = {"setup:runs+Fload", "psel", "math", "ringwait", "u+en", "next", "product-loop", "fence+issue", "setup:end+fetch",
+                          "setup:record", "setup:dir+div", "setup:lum+mask", "setup:fwait", "", "", ""};
+    fprintf(stderr, "[dre timing] rt_type %d (per intersection %.0f cycles):", e->g.rt_type, c[CNT_ISECT] ? tot / (double)c[CNT_ISECT] : 0.0);
+    for (int i = 0; i < 13; i++) fprintf(stderr, " %s %.1f%%", nm[i], 100 * t[i] / tot);
+    fprintf(stderr, "\n");
+    memset(t, 0, sizeof(t)); CK(cudaMemcpyToSymbol(g_dre_tim, t, sizeof(t))); }
+#endif
   if (!out) return;
   memset(out, 0, sizeof(*out));
   out->sources = e->nsrc_list; out->rays = c[CNT_RAYS]; out->intersections = c[CNT_ISECT]; out->deposits = c[CNT_DEP];
@@ -702,7 +719,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     CK(cudaMemGetInfo(&free_b, &total_b));
     e->list_budget = free_b / 2;
   }
-  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0;   // H/W double buffers + OUT + index arrays, DBuf slack
+  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0 + 160.0;   // H/W double buffers + OUT + index arrays, DBuf slack
   const double max_entries = std::max(1.0e6, (double)e->list_budget / bytes_per_entry);
   // entries per unit seen in the previous pass of this type (same scene): lets a warm engine start with full batches
   double& est = e->per_unit_est[rt_type % 16];
@@ -1035,6 +1052,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
+  else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));
   else if (s == "dir_kmax") e->opt_dir_kmax = std::max(2, std::min(10, (int)value));
   else DRE_REQUIRE(false, "dre_set_option: unknown option");
   DRE_CATCH(e)

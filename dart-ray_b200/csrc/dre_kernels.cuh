@@ -21,7 +21,7 @@ __host__ __device__ inline int dre_stage_len(int ROW, int split) {
   int n = (ROW + split - 1) / split; n += n & 1; return n < 2 ? 2 : n;
 }
 __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split) {
-  ws.pending = 0; ws.stage_len = 0;
+  ws.pending = 0; ws.stage_len = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.run_n = 0; ws.run_total = 0;
   ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
@@ -51,46 +51,112 @@ __device__ __forceinline__ void dre_flush_stats(const DreAccum& A, const WarpSta
   atomicAdd(&A.counters[CNT_SCA], st.sca); atomicAdd(&A.counters[CNT_ACT], st.act);
   atomicAdd(&A.counters[CNT_HASH], st.hash);
   atomicAdd(&A.counters[CNT_ACTDEP], st.actdep); atomicAdd(&A.counters[CNT_DESC], st.desc);
+#ifdef DRE_TIMING
+  for (int i = 0; i < 16; i++) atomicAdd(&g_dre_tim[i], st.tim[i]);
+#endif
+}
+
+// ---- ray records: everything one ray_tracing call needs, resolved by one thread per task before the march.
+// The march kernel then reads ONE 128-B record per ray instead of chasing task -> unit arrays -> list entry ->
+// direction table -> find_cc_new2 descent through dependent loads (measured: a third of its warp time).
+struct __align__(16) DreRay {
+  int unit, nc, gid, step;
+  int ray_ord, nk, dk, dip;
+  int type, cc_old, isel_ray, fpix;
+  int cc0, lvl0, loc_rc, lvl_nc;
+  int e0, e1, e2, e3;          // list entries carrying the luminosity (e1..e3 = -1 unless merged)
+  double prev_ray, cs_nc, src[3];
+  int kind, pad;
+};
+template <int MODE>
+__global__ void k_prep_rays(DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt, DreRay* __restrict__ rays) {
+  const DreDev& g = c_g;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nt) return;
+  const DreTask tk = tasks[t];
+  const int un = tk.unit;
+  DreRay q;
+  q.unit = un; q.nc = u.nc[un]; q.nk = u.nk[un]; q.gid = u.gid[un]; q.step = u.step[un]; q.ray_ord = t - u.task_seg[un];
+  double src[3];
+  dre_src_coord(g, q.nc, src);
+  q.src[0] = src[0]; q.src[1] = src[1]; q.src[2] = src[2];
+  const DreList& S = (tk.kind == 2) ? W : H;
+  const unsigned m = S.meta[tk.e0];
+  if (tk.kind == 0) { q.dk = q.nk; q.dip = 4 * (S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - (q.nk - 1)))) + tk.sub; q.type = RT_HIGH; }
+  else if (tk.kind == 1) { q.dk = META_DIRK(m); q.dip = S.dir_ipix[tk.e0]; q.type = RT_RECO; }
+  else { q.dk = q.nk; q.dip = S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - q.nk)); q.type = RT_LOW; }
+  q.fpix = -1;
+  if (MODE == MODE_DEP && g.ftab[q.nk] != nullptr) q.fpix = (q.type == RT_RECO) ? 1 : q.dip;
+  q.cc_old = S.cc_old[tk.e0]; q.isel_ray = META_ISEL(m);
+  q.prev_ray = S.prev[tk.e0];
+  if (tk.kind == 2) q.prev_ray = (((S.prev[tk.e0] + S.prev[tk.e1]) + S.prev[tk.e2]) + S.prev[tk.e3]) / 4;   // ray_list.f90:266
+  q.e0 = tk.e0; q.e1 = tk.e1; q.e2 = tk.e2; q.e3 = tk.e3; q.kind = tk.kind; q.pad = 0;
+  const DreCell* cn = &g.cell[q.nc];
+  q.lvl_nc = cn->lvl; q.cs_nc = g.csize[q.nc];
+  q.cc0 = -1; q.lvl0 = 0; q.loc_rc = 0;
+  if (q.cc_old != q.nc) {                                   // relaunched ray: find_cc_new2 :1962-2066
+    const DreDir dir = g.dirtab[q.dk][q.dip];
+    const double d[3] = {dir.st * dir.cp, dir.st * dir.sp, dir.ct};   // calc_cproj :1945-1953
+    q.loc_rc = dre_locate(g, src, d, q.prev_ray, q.cc_old, q.cc0, q.lvl0);
+  }
+  rays[t] = q;
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL>
-__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
-                        DreList out, int* __restrict__ counter) {
+__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreList H, DreList W, const DreRay* __restrict__ rays, int nt,
+                        DreList out, int* __restrict__ counter, int chunk) {
   extern __shared__ __align__(128) unsigned char smem[];
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpSmem ws;
   dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split);
   WarpStats st; memset(&st, 0, sizeof(st));
+#ifdef DRE_TIMING
+  st.tprev = clock64();
+#endif
   double lost[KL];
 #pragma unroll
   for (int k = 0; k < KL; k++) lost[k] = 0;
   const int L = g.L;
+  LamK lk[KL]; int lam_off[KL], lam_nhp[KL], lam_kp[KL];
+#pragma unroll
+  for (int k = 0; k < KL; k++) {
+    const int l = lane + 32 * k;
+    const bool ok = (k < g.KLn && l < L);
+    lk[k].npix = ok ? g.npix[l] : 0; lk[k].alb = ok ? g.ksca[l] : 0.0;
+    lam_off[k] = ok ? g.off[l] : 0; lam_nhp[k] = ok ? g.npix_hp[l] : 1;
+    const int ik = ok ? g.ik_sca[l] : -1;
+    lam_kp[k] = (ik >= 0) ? g.class_kp[ik] : -1;
+  }
+  int t = 0, t_end = 0;
   for (;;) {
-    int t = 0;
-    if (lane == 0) t = atomicAdd(counter, 1);
-    t = __shfl_sync(0xffffffffu, t, 0);
-    if (t >= nt) break;
-    const DreTask tk = tasks[t];
-    const int un = tk.unit;
+    if (t >= t_end) {                         // next chunk of consecutive rays
+      if (lane == 0) t = atomicAdd(counter, chunk);
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (t >= nt) break;
+      t_end = min(t + chunk, nt);
+    }
+    DRE_TICK(8);    // setup: ray end (outputs) + chunk fetch
+    const DreRay* qp = rays + t;
+    const int4 q0 = __ldg(reinterpret_cast<const int4*>(qp)), q1 = __ldg(reinterpret_cast<const int4*>(qp) + 1),
+               q2 = __ldg(reinterpret_cast<const int4*>(qp) + 2), q3 = __ldg(reinterpret_cast<const int4*>(qp) + 3),
+               q4 = __ldg(reinterpret_cast<const int4*>(qp) + 4);
+    const double2 d0 = __ldg(reinterpret_cast<const double2*>(qp) + 5), d1 = __ldg(reinterpret_cast<const double2*>(qp) + 6);
+    const double d2 = __ldg(reinterpret_cast<const double*>(qp) + 14);
+    const int kind = __ldg(reinterpret_cast<const int*>(qp) + 30);
     RayIn r;
-    r.nc = u.nc[un]; r.nk = u.nk[un]; r.gid = u.gid[un]; r.step = u.step[un]; r.ray_ord = t - u.task_seg[un];
+    const int un = q0.x;
+    r.nc = q0.y; r.gid = q0.z; r.step = q0.w; r.ray_ord = q1.x; r.nk = q1.y;
+    const int dk = q1.z, dip = q1.w;
+    r.type = q2.x; r.cc_old = q2.y; r.isel_ray = q2.z; r.fpix = q2.w;
+    r.cc0 = q3.x; r.lvl0 = q3.y; r.loc_rc = q3.z; r.lvl_nc = q3.w;
+    const int e0 = q4.x, e1 = q4.y, e2 = q4.z, e3 = q4.w;
+    r.prev_ray = d0.x; r.cs_nc = d0.y; r.src[0] = d1.x; r.src[1] = d1.y; r.src[2] = d2;
     r.vec_mod = 0;
-    dre_src_coord(g, r.nc, r.src);
-    const DreList& S = (tk.kind == 2) ? W : H;
-    const unsigned m = S.meta[tk.e0];
-    int dk, dip;
-    if (tk.kind == 0) { dk = r.nk; dip = 4 * (S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - (r.nk - 1)))) + tk.sub; r.type = RT_HIGH; }
-    else if (tk.kind == 1) { dk = META_DIRK(m); dip = S.dir_ipix[tk.e0]; r.type = RT_RECO; }
-    else { dk = r.nk; dip = S.dir_ipix[tk.e0] >> (2 * (META_DIRK(m) - r.nk)); r.type = RT_LOW; }
+    const DreList& S = (kind == 2) ? W : H;
     r.dir = g.dirtab[dk][dip];
     r.fdir = (r.type == RT_RECO && r.nk <= 8) ? g.dirtab[r.nk][1] : r.dir;   // Q2: ipix = 1 for ray_type_reco
-    r.fpix = -1;
-    if (MODE == MODE_DEP && g.ftab[r.nk] != nullptr) r.fpix = (r.type == RT_RECO) ? 1 : dip;
-    r.cc_old = S.cc_old[tk.e0]; r.isel_ray = META_ISEL(m);
-    r.prev_ray = S.prev[tk.e0];
-    if (tk.kind == 2) r.prev_ray = (((S.prev[tk.e0] + S.prev[tk.e1]) + S.prev[tk.e2]) + S.prev[tk.e3]) / 4;   // ray_list.f90:266
     double I[KL];
 #pragma unroll
     for (int k = 0; k < KL; k++) {
@@ -98,19 +164,19 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreU
       I[k] = 0;
       if (k < g.KLn && l < L) {
         if (g.rt_type == DRE_RTT_SCATT && r.cc_old == r.nc) {       // assign_src_lum :3043-3071
-          const int ik = g.ik_sca[l];
-          const int ip = (ik >= 0) ? (dip >> (2 * (dk - g.class_kp[ik]))) : 0;
-          I[k] = A.prev[(size_t)r.nc * g.ROW + g.off[l] + ip] * g.npix_hp[l];
-        } else if (tk.kind == 2) {
-          double s = S.lum[(size_t)tk.e0 * L + l];
-          s = s + S.lum[(size_t)tk.e1 * L + l]; s = s + S.lum[(size_t)tk.e2 * L + l]; s = s + S.lum[(size_t)tk.e3 * L + l];
+          const int ip = (lam_kp[k] >= 0) ? (dip >> (2 * (dk - lam_kp[k]))) : 0;
+          I[k] = A.prev[(size_t)r.nc * g.ROW + lam_off[k] + ip] * lam_nhp[k];
+        } else if (kind == 2) {
+          double s = S.lum[(size_t)e0 * L + l];
+          s = s + S.lum[(size_t)e1 * L + l]; s = s + S.lum[(size_t)e2 * L + l]; s = s + S.lum[(size_t)e3 * L + l];
           I[k] = s / 4;                                              // ray_list.f90:261-264
-        } else I[k] = S.lum[(size_t)tk.e0 * L + l];
+        } else I[k] = S.lum[(size_t)e0 * L + l];
       }
     }
+    DRE_TICK(9);    // setup: record load + issue of direction / luminosity loads
     RayOut o;
     st.psel = 0; st.npsel = 0;
-    trace_ray<MODE, KL>(g, A, ws, lane, r, I, lost, st, o);
+    trace_ray<MODE, KL>(g, A, ws, lane, r, I, lost, st, o, lk);
     if (MODE == MODE_DEP && lane == 0 && st.npsel > 0) {
       const int sid = (g.rt_type == DRE_RTT_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
       atomicAdd(&A.psel_sum[sid], st.psel);
@@ -128,6 +194,7 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreU
         if (k < g.KLn && l < L) out.lum[(size_t)t * L + l] = I[k];
       }
     }
+    t++;
   }
   if (MODE == MODE_DEP) {
     if (ws.fwait) { mbar_wait(ws.mbar, ws.fphase); ws.fwait = 0; }
@@ -156,7 +223,7 @@ template <int KL>
 __global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31;
-  WarpSmem ws; ws.pending = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
+  WarpSmem ws; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
 #pragma unroll
@@ -173,6 +240,7 @@ __global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
     r.nc = q.srclist[si]; r.nk = DRE_NSIDE_MIN_K; r.gid = t; r.step = 0; r.ray_ord = 0;
     dre_src_coord(g, r.nc, r.src);
     r.cc_old = r.nc; r.isel_ray = 0; r.prev_ray = 0; r.vec_mod = 0;
+    r.cc0 = -1; r.lvl0 = 0; r.loc_rc = 0; r.lvl_nc = g.cell[r.nc].lvl; r.cs_nc = g.csize[r.nc];
     const bool inner = (j >= q.ndir);
     const int jj = inner ? j - q.ndir : j;
     if (!inner) { r.dir = q.obs_dir[jj]; r.type = RT_IOBS; }
@@ -196,7 +264,10 @@ __global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
       }
     }
     RayOut o;
-    trace_ray<MODE_IOBS, KL>(g, A, ws, lane, r, I, lost, st, o);
+    LamK lk0[KL];
+#pragma unroll
+    for (int k = 0; k < KL; k++) { lk0[k].npix = 0; lk0[k].alb = 0; }
+    trace_ray<MODE_IOBS, KL>(g, A, ws, lane, r, I, lost, st, o, lk0);
     const int sid = (g.rt_type == DRE_RTT_I_OBS_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
     double* dst = (inner ? q.i_obs_in : q.i_obs) + ((size_t)jj * (g.N + g.S) + sid) * L;
     if (o.iobs_valid) {
@@ -217,7 +288,7 @@ __global__ void k_build_ftab(int k, double* __restrict__ rows) {
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long npix = 12ll << (2 * k);
   if (w >= npix) return;
-  WarpSmem ws; ws.pending = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
+  WarpSmem ws; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   ws.F = rows + (size_t)w * g.ROW;
   unsigned act[DRE_KL];
   for (int q = 0; q < DRE_KL; q++) { const int rem = g.L - 32 * q; act[q] = rem >= 32 ? 0xffffffffu : (rem > 0 ? ((1u << rem) - 1u) : 0u); }

@@ -1,12 +1,11 @@
-# A/B: threads per CTA of the ray-march kernel (variant libraries under ab/) x stage_split
+# A/B helper: engine options (and variant libraries under ab/) on the TRUST-I workload
 run() { lib=$1; shift; o="$*"; args=""; for kv in $o; do args="$args --option $kv"; done
-  DARTRAY_ENGINE_LIB=$lib python bench.py --no-cpu --no-e2e --steps 2 --warmup 1 $args 2>/dev/null | python -c "
+  DARTRAY_ENGINE_LIB=$lib python bench.py --workload ${WL:-trustI} --no-also --no-cpu --no-e2e --steps 2 --warmup 1 $args 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); print('$lib $o', round(d['ms_per_step'],1), round(d['roofline']['kernel_ms_per_step'],1))"; }
-run dart-ray_b200/libdartray_engine.so stage_split=2 warps=16
-run ab/eng_640.so stage_split=4 warps=20
-run ab/eng_640.so stage_split=8 warps=20
-run ab/eng_640.so stage_split=4 warps=18
-run ab/eng_768.so stage_split=8 warps=24
-run ab/eng_768.so stage_split=8 warps=22
-run ab/eng_768.so stage_split=4 warps=20
+d=json.loads(sys.stdin.read()); print('${WL:-trustI} $lib $o', round(d['ms_per_step'],1), round(d['roofline']['kernel_ms_per_step'],1), round(d['roofline']['frac'],4))"; }
+run dart-ray_b200/libdartray_engine.so ftab_kmax=5
+run dart-ray_b200/libdartray_engine.so ftab_kmax=6
+run dart-ray_b200/libdartray_engine.so ftab_kmax=7
+run dart-ray_b200/libdartray_engine.so ftab_kmax=8
+WL=galaxy run dart-ray_b200/libdartray_engine.so ftab_kmax=5
+WL=galaxy run dart-ray_b200/libdartray_engine.so ftab_kmax=8
