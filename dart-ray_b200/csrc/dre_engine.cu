@@ -530,7 +530,7 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
   if (MODE == MODE_DEP) {
     warps = trace_warps(e, &smem);
     CK(cudaFuncSetAttribute(k_trace<MODE, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  }
+  } else smem = (size_t)warps * (8 + 32 * e->g.KLn) * 8;
   const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
   // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance

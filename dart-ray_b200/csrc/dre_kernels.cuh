@@ -23,23 +23,28 @@ __host__ __device__ inline int dre_stage_len(int ROW, int split) {
 __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split) {
   ws.pending = 0; ws.stage_len = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.run_n = 0; ws.run_total = 0;
   ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
-  if (!need) { ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; return; }
+  if (!need) {   // precalc: only the look-ahead buffer lives in (dynamic) shared memory
+    ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr;
+    ws.pre = reinterpret_cast<double*>(smem) + (size_t)warp * (8 + 32 * g.KLn);
+    return;
+  }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
   const int sl = dre_stage_len(g.ROW, split);
-  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6) * 8;   // keeps 16-B alignment
+  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6 + 8 + 32 * g.KLn) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
   ws.lamof = lam; ws.stage = base; ws.F = base + sl; ws.en2 = base + sl + g.ROW; ws.stage_len = sl;
   ws.mbar = (unsigned long long*)(base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
   ws.runs = (int*)(ws.mbar + 2);
+  ws.pre = base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 6;
   ws.fphase = 0; ws.fwait = 0;
   if (lane == 0) mbar_init(ws.mbar);
   __syncthreads();
 }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6) * 8;
+  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6 + 8 + 32 * ((L + 31) / 32)) * 8;
   return lam_bytes + per * warps;
 }
 
@@ -223,7 +228,9 @@ template <int KL>
 __global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31;
+  __shared__ double s_pre[8][8 + 32 * KL];      // look-ahead buffers of the 8 warps of a CTA
   WarpSmem ws; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
+  ws.pre = s_pre[threadIdx.x >> 5];
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
 #pragma unroll
