@@ -664,9 +664,9 @@ void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
   { unsigned long long t[16]; CK(cudaMemcpyFromSymbol(t, g_dre_tim, sizeof(t)));
     double tot = 0; for (int i = 0; i < 16; i++) tot += (double)t[i];
     const char* nm[16] = {"setup:runs+Fload", "psel", "math", "ringwait", "u+en", "next", "product-loop", "fence+issue", "setup:end+fetch",
-                          "setup:record", "setup:dir+div", "setup:lum+mask", "setup:fwait", "", "", ""};
+                          "setup:record", "setup:dir+div", "setup:lum+mask", "setup:fwait", "end:return", "end:outputs", ""};
     fprintf(stderr, "[dre timing] rt_type %d (per intersection %.0f cycles):", e->g.rt_type, c[CNT_ISECT] ? tot / (double)c[CNT_ISECT] : 0.0);
-    for (int i = 0; i < 13; i++) fprintf(stderr, " %s %.1f%%", nm[i], 100 * t[i] / tot);
+    for (int i = 0; i < 15; i++) fprintf(stderr, " %s %.1f%%", nm[i], 100 * t[i] / tot);
     fprintf(stderr, "\n");
     memset(t, 0, sizeof(t)); CK(cudaMemcpyToSymbol(g_dre_tim, t, sizeof(t))); }
 #endif

@@ -199,6 +199,7 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreL
         if (k < g.KLn && l < L) out.lum[(size_t)t * L + l] = I[k];
       }
     }
+    DRE_TICK(14);   // ray end: outcome record + luminosity written
     t++;
   }
   if (MODE == MODE_DEP) {
