@@ -74,9 +74,9 @@ struct dre_engine {
   DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, leader, unit_of_ext, ntask, nreco,
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
-  DBuf<DreRay> rays;
+  DBuf<double> pkts;     // ray packets of the current step
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 4;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
@@ -501,7 +501,7 @@ int trace_warps(dre_engine* e, size_t* smem) {
   const DreDev& g = e->g;
   int w = std::max(1, std::min(e->opt_warps, 32));
   w = std::min(w, DRE_TRACE_THREADS / 32);
-  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) * e->opt_ctas_per_sm > (size_t)224 * 1024) w--;
+  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) * e->opt_ctas_per_sm > (size_t)226 * 1024) w--;
   *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split);
   DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
   return w;
@@ -530,18 +530,19 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
   if (MODE == MODE_DEP) {
     warps = trace_warps(e, &smem);
     CK(cudaFuncSetAttribute(k_trace<MODE, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  } else smem = (size_t)warps * (8 + 32 * e->g.KLn) * 8;
+  } else smem = (size_t)warps * (8 + 32 * e->g.KLn + 2 + dre_pkt_stride(e->g.L)) * 8;
   const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
   // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance
   const int chunk = std::max(1, std::min(e->opt_chunk, nT / (ctas * warps * 8)));
-  e->rays.ensure(nT);
+  const int pstride = dre_pkt_stride(e->g.L);
+  e->pkts.ensure((size_t)nT * pstride);
   e->n_launch++;
-  k_prep_rays<MODE><<<cdiv(nT, 128), 128, 0, e->st>>>(u, H, W, e->tasks.p, nT, e->rays.p);
+  k_prep_rays<MODE><<<cdiv(nT, 128), 128, 0, e->st>>>(A, u, H, W, e->tasks.p, nT, e->pkts.p, pstride);
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, H, W, e->rays.p, nT, out, e->counter.p, chunk);
+  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, e->pkts.p, pstride, nT, out, e->counter.p, chunk);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
   e->last_launches++;
@@ -719,7 +720,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     CK(cudaMemGetInfo(&free_b, &total_b));
     e->list_budget = free_b / 2;
   }
-  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0 + 160.0;   // H/W double buffers + OUT + index arrays, DBuf slack
+  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0 + 8.0 * (22 + e->g.L) * 1.25;   // H/W double buffers + OUT + index arrays, DBuf slack
   const double max_entries = std::max(1.0e6, (double)e->list_budget / bytes_per_entry);
   // entries per unit seen in the previous pass of this type (same scene): lets a warm engine start with full batches
   double& est = e->per_unit_est[rt_type % 16];

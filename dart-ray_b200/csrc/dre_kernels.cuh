@@ -17,6 +17,8 @@ __device__ __forceinline__ double dre_src_lum(const DreDev& g, int nc, int l) { 
   return g.lumcell[(size_t)nc * g.L + l];
 }
 
+#define DRE_PKT_HDR 20      // doubles of a ray packet in front of the luminosities (record 16 + direction 4)
+__host__ __device__ inline int dre_pkt_stride(int L) { return DRE_PKT_HDR + L + (L & 1); }
 __host__ __device__ inline int dre_stage_len(int ROW, int split) {
   int n = (ROW + split - 1) / split; n += n & 1; return n < 2 ? 2 : n;
 }
@@ -25,26 +27,33 @@ __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* sm
   ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   if (!need) {   // precalc: only the look-ahead buffer lives in (dynamic) shared memory
     ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr;
-    ws.pre = reinterpret_cast<double*>(smem) + (size_t)warp * (8 + 32 * g.KLn);
+    ws.pre = reinterpret_cast<double*>(smem) + (size_t)warp * (8 + 32 * g.KLn + 2 + dre_pkt_stride(g.L));
+    ws.pmbar = (unsigned long long*)(ws.pre + 8 + 32 * g.KLn);
+    ws.pkt = ws.pre + 8 + 32 * g.KLn + 2;
+    if (lane == 0) mbar_init(ws.pmbar);
+    __syncthreads();
     return;
   }
   const size_t lam_bytes = ((size_t)g.ROW * 2 + 15) & ~(size_t)15;
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
   const int sl = dre_stage_len(g.ROW, split);
-  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6 + 8 + 32 * g.KLn) * 8;   // keeps 16-B alignment
+  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6 + 8 + 32 * g.KLn + 2 + dre_pkt_stride(g.L)) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
   ws.lamof = lam; ws.stage = base; ws.F = base + sl; ws.en2 = base + sl + g.ROW; ws.stage_len = sl;
   ws.mbar = (unsigned long long*)(base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
   ws.runs = (int*)(ws.mbar + 2);
   ws.pre = base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 6;
+  ws.pmbar = (unsigned long long*)(ws.pre + 8 + 32 * g.KLn);
+  ws.pkt = ws.pre + 8 + 32 * g.KLn + 2;
+  if (lane == 0) mbar_init(ws.pmbar);
   ws.fphase = 0; ws.fwait = 0;
   if (lane == 0) mbar_init(ws.mbar);
   __syncthreads();
 }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6 + 8 + 32 * ((L + 31) / 32)) * 8;
+  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6 + 8 + 32 * ((L + 31) / 32) + 2 + dre_pkt_stride(L)) * 8;
   return lam_bytes + per * warps;
 }
 
@@ -73,11 +82,12 @@ struct __align__(16) DreRay {
   double prev_ray, cs_nc, src[3];
   int kind, pad;
 };
+// A ray packet = [DreRay record (128 B) | direction (32 B) | launch luminosity of every wavelength (8 L B)], `pstride`
+// doubles apart: the march kernel fetches the packet of ray t+1 with ONE TMA bulk copy while it traces ray t.
 template <int MODE>
-__global__ void k_prep_rays(DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt, DreRay* __restrict__ rays) {
-  const DreDev& g = c_g;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nt) return;
+__device__ __forceinline__ void dre_prep_record(const DreDev& g, const DreUnits& u, const DreList& H, const DreList& W,
+                                                const DreTask* __restrict__ tasks, int t, double* __restrict__ pkts, int pstride,
+                                                int (*s_e)[128], int* s_mode, int* s_w, int* s_nc, int* s_dk, int* s_dip) {
   const DreTask tk = tasks[t];
   const int un = tk.unit;
   DreRay q;
@@ -99,17 +109,58 @@ __global__ void k_prep_rays(DreUnits u, DreList H, DreList W, const DreTask* __r
   const DreCell* cn = &g.cell[q.nc];
   q.lvl_nc = cn->lvl; q.cs_nc = g.csize[q.nc];
   q.cc0 = -1; q.lvl0 = 0; q.loc_rc = 0;
+  const DreDir dir = g.dirtab[q.dk][q.dip];
   if (q.cc_old != q.nc) {                                   // relaunched ray: find_cc_new2 :1962-2066
-    const DreDir dir = g.dirtab[q.dk][q.dip];
     const double d[3] = {dir.st * dir.cp, dir.st * dir.sp, dir.ct};   // calc_cproj :1945-1953
     q.loc_rc = dre_locate(g, src, d, q.prev_ray, q.cc_old, q.cc0, q.lvl0);
   }
-  rays[t] = q;
+  double* pk = pkts + (size_t)t * pstride;
+  *reinterpret_cast<DreRay*>(pk) = q;
+  *reinterpret_cast<DreDir*>(pk + 16) = dir;
+  s_e[0][threadIdx.x] = tk.e0; s_e[1][threadIdx.x] = tk.e1; s_e[2][threadIdx.x] = tk.e2; s_e[3][threadIdx.x] = tk.e3;
+  // mode of the luminosity gather: 0 list entry, 1 merged siblings, 2 scattering source (assign_src_lum), -1 no ray
+  s_mode[threadIdx.x] = (g.rt_type == DRE_RTT_SCATT && q.cc_old == q.nc) ? 2 : (tk.kind == 2 ? 1 : 0);
+  s_w[threadIdx.x] = (tk.kind == 2) ? 1 : 0;
+  s_nc[threadIdx.x] = q.nc; s_dk[threadIdx.x] = q.dk; s_dip[threadIdx.x] = q.dip;
+}
+
+// luminosities of the packets of one block of rays, L consecutive threads per ray (coalesced rows)
+__device__ __forceinline__ void dre_prep_lum(const DreDev& g, const DreAccum& A, const DreList& H, const DreList& W, int t0, int nrays,
+                                             double* __restrict__ pkts, int pstride, const int (*s_e)[128], const int* s_mode,
+                                             const int* s_w, const int* s_nc, const int* s_dk, const int* s_dip) {
+  const int L = g.L;
+  for (int idx = threadIdx.x; idx < nrays * L; idx += blockDim.x) {
+    const int i = idx / L, l = idx - i * L;
+    const int mode = s_mode[i];
+    const double* lumS = s_w[i] ? W.lum : H.lum;
+    double v;
+    if (mode == 2) {                                            // assign_src_lum :3043-3071
+      const int ik = g.ik_sca[l];
+      const int ip = (ik >= 0) ? (s_dip[i] >> (2 * (s_dk[i] - g.class_kp[ik]))) : 0;
+      v = A.prev[(size_t)s_nc[i] * g.ROW + g.off[l] + ip] * g.npix_hp[l];
+    } else if (mode == 1) {                                     // merged siblings: ray_list.f90:261-264
+      v = lumS[(size_t)s_e[0][i] * L + l];
+      v = v + lumS[(size_t)s_e[1][i] * L + l]; v = v + lumS[(size_t)s_e[2][i] * L + l]; v = v + lumS[(size_t)s_e[3][i] * L + l];
+      v = v / 4;
+    } else v = lumS[(size_t)s_e[0][i] * L + l];
+    pkts[(size_t)(t0 + i) * pstride + DRE_PKT_HDR + l] = v;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) k_prep_rays(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
+                                                   double* __restrict__ pkts, int pstride) {
+  const DreDev& g = c_g;
+  __shared__ int s_e[4][128], s_mode[128], s_w[128], s_nc[128], s_dk[128], s_dip[128];
+  const int t0 = blockIdx.x * 128, t = t0 + threadIdx.x;
+  if (t < nt) dre_prep_record<MODE>(g, u, H, W, tasks, t, pkts, pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+  __syncthreads();
+  dre_prep_lum(g, A, H, W, t0, min(128, nt - t0), pkts, pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL>
-__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreList H, DreList W, const DreRay* __restrict__ rays, int nt,
+__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, const double* __restrict__ pkts, int pstride, int nt,
                         DreList out, int* __restrict__ counter, int chunk) {
   extern __shared__ __align__(128) unsigned char smem[];
   const DreDev& g = c_g;
@@ -124,16 +175,16 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreL
 #pragma unroll
   for (int k = 0; k < KL; k++) lost[k] = 0;
   const int L = g.L;
-  LamK lk[KL]; int lam_off[KL], lam_nhp[KL], lam_kp[KL];
+  LamK lk[KL];
 #pragma unroll
   for (int k = 0; k < KL; k++) {
     const int l = lane + 32 * k;
     const bool ok = (k < g.KLn && l < L);
     lk[k].npix = ok ? g.npix[l] : 0; lk[k].alb = ok ? g.ksca[l] : 0.0;
-    lam_off[k] = ok ? g.off[l] : 0; lam_nhp[k] = ok ? g.npix_hp[l] : 1;
-    const int ik = ok ? g.ik_sca[l] : -1;
-    lam_kp[k] = (ik >= 0) ? g.class_kp[ik] : -1;
   }
+  const unsigned pbytes = (unsigned)pstride * 8u;
+  unsigned pphase = 0;
+  bool pk_inflight = false;
   int t = 0, t_end = 0;
   for (;;) {
     if (t >= t_end) {                         // next chunk of consecutive rays
@@ -142,43 +193,33 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreL
       if (t >= nt) break;
       t_end = min(t + chunk, nt);
     }
-    DRE_TICK(8);    // setup: ray end (outputs) + chunk fetch
-    const DreRay* qp = rays + t;
-    const int4 q0 = __ldg(reinterpret_cast<const int4*>(qp)), q1 = __ldg(reinterpret_cast<const int4*>(qp) + 1),
-               q2 = __ldg(reinterpret_cast<const int4*>(qp) + 2), q3 = __ldg(reinterpret_cast<const int4*>(qp) + 3),
-               q4 = __ldg(reinterpret_cast<const int4*>(qp) + 4);
-    const double2 d0 = __ldg(reinterpret_cast<const double2*>(qp) + 5), d1 = __ldg(reinterpret_cast<const double2*>(qp) + 6);
-    const double d2 = __ldg(reinterpret_cast<const double*>(qp) + 14);
-    const int kind = __ldg(reinterpret_cast<const int*>(qp) + 30);
+    if (!pk_inflight) {                       // first ray of a chunk: its packet was not requested ahead
+      if (lane == 0) bulk_load_row(ws.pkt, pkts + (size_t)t * pstride, pbytes, ws.pmbar);
+    }
+    mbar_wait(ws.pmbar, pphase); pphase ^= 1u;
+    DRE_TICK(8);    // setup: ray end (outputs) + chunk fetch + packet wait
     RayIn r;
-    const int un = q0.x;
-    r.nc = q0.y; r.gid = q0.z; r.step = q0.w; r.ray_ord = q1.x; r.nk = q1.y;
-    const int dk = q1.z, dip = q1.w;
-    r.type = q2.x; r.cc_old = q2.y; r.isel_ray = q2.z; r.fpix = q2.w;
-    r.cc0 = q3.x; r.lvl0 = q3.y; r.loc_rc = q3.z; r.lvl_nc = q3.w;
-    const int e0 = q4.x, e1 = q4.y, e2 = q4.z, e3 = q4.w;
-    r.prev_ray = d0.x; r.cs_nc = d0.y; r.src[0] = d1.x; r.src[1] = d1.y; r.src[2] = d2;
+    const int* qi = reinterpret_cast<const int*>(ws.pkt);
+    const int un = qi[0];
+    r.nc = qi[1]; r.gid = qi[2]; r.step = qi[3]; r.ray_ord = qi[4]; r.nk = qi[5];
+    const int dk = qi[6], dip = qi[7];
+    r.type = qi[8]; r.cc_old = qi[9]; r.isel_ray = qi[10]; r.fpix = qi[11];
+    r.cc0 = qi[12]; r.lvl0 = qi[13]; r.loc_rc = qi[14]; r.lvl_nc = qi[15];
+    r.prev_ray = ws.pkt[10]; r.cs_nc = ws.pkt[11]; r.src[0] = ws.pkt[12]; r.src[1] = ws.pkt[13]; r.src[2] = ws.pkt[14];
     r.vec_mod = 0;
-    const DreList& S = (kind == 2) ? W : H;
-    r.dir = g.dirtab[dk][dip];
-    r.fdir = (r.type == RT_RECO && r.nk <= 8) ? g.dirtab[r.nk][1] : r.dir;   // Q2: ipix = 1 for ray_type_reco
+    r.dir.st = ws.pkt[16]; r.dir.ct = ws.pkt[17]; r.dir.sp = ws.pkt[18]; r.dir.cp = ws.pkt[19];
+    r.fdir = r.dir;
+    if (r.type == RT_RECO && r.nk <= 8 && r.fpix < 0) r.fdir = g.dirtab[r.nk][1];   // Q2: ipix = 1 for ray_type_reco
     double I[KL];
 #pragma unroll
     for (int k = 0; k < KL; k++) {
       const int l = lane + 32 * k;
-      I[k] = 0;
-      if (k < g.KLn && l < L) {
-        if (g.rt_type == DRE_RTT_SCATT && r.cc_old == r.nc) {       // assign_src_lum :3043-3071
-          const int ip = (lam_kp[k] >= 0) ? (dip >> (2 * (dk - lam_kp[k]))) : 0;
-          I[k] = A.prev[(size_t)r.nc * g.ROW + lam_off[k] + ip] * lam_nhp[k];
-        } else if (kind == 2) {
-          double s = S.lum[(size_t)e0 * L + l];
-          s = s + S.lum[(size_t)e1 * L + l]; s = s + S.lum[(size_t)e2 * L + l]; s = s + S.lum[(size_t)e3 * L + l];
-          I[k] = s / 4;                                              // ray_list.f90:261-264
-        } else I[k] = S.lum[(size_t)e0 * L + l];
-      }
+      I[k] = (k < g.KLn && l < L) ? ws.pkt[DRE_PKT_HDR + l] : 0.0;
     }
-    DRE_TICK(9);    // setup: record load + issue of direction / luminosity loads
+    __syncwarp();                             // every lane has read the packet: the buffer is free again
+    pk_inflight = (t + 1 < t_end);
+    if (pk_inflight && lane == 0) bulk_load_row(ws.pkt, pkts + (size_t)(t + 1) * pstride, pbytes, ws.pmbar);
+    DRE_TICK(9);    // setup: packet fields to registers, next packet requested
     RayOut o;
     st.psel = 0; st.npsel = 0;
     trace_ray<MODE, KL>(g, A, ws, lane, r, I, lost, st, o, lk);
