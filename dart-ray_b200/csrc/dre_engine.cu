@@ -70,7 +70,7 @@ struct dre_engine {
   long long rec_cap = 0; DBuf<dre_isect> rec; DBuf<unsigned long long> rec_n;
   // wavefront scratch
   ListStore H[2], W[2], OUT;
-  DBuf<int> u_nc, u_gid, u_nk, u_step, u_mode, u_task_seg;
+  DBuf<int> u_nc, u_gid, u_nk, u_nk_prev, u_step, u_mode, u_task_seg;
   DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, leader, unit_of_ext, ntask, nreco,
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
@@ -105,6 +105,7 @@ void scan_level(dre_engine* e, const int* in, int* out, int n, int level) {
 }
 void scan(dre_engine* e, const int* in, int* out, int n) {
   if (n <= 0) { (e->n_launch++, k_set_int)<<<1, 1, 0, e->st>>>(out, 0); return; }
+  if (n <= SCAN_TILE) { (e->n_launch++, k_scan_small)<<<1, SCAN_THREADS, 0, e->st>>>(in, out, n); return; }
   scan_level(e, in, out, n, 0);
 }
 
@@ -563,8 +564,8 @@ long long run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U
   const DreDev& g = e->g;
   unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
   const int L = g.L;
-  e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
-  DreUnits u; u.nc = e->u_nc.p; u.gid = e->u_gid.p; u.nk = e->u_nk.p; u.step = e->u_step.p; u.mode = e->u_mode.p;
+  e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_nk_prev.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
+  DreUnits u; u.nc = e->u_nc.p; u.gid = e->u_gid.p; u.nk = e->u_nk.p; u.nk_prev = e->u_nk_prev.p; u.step = e->u_step.p; u.mode = e->u_mode.p;
   u.task_seg = e->u_task_seg.p; u.U = U;
   for (int i = 0; i < 2; i++) { e->H[i].ensure(U, L, U); e->W[i].ensure(64, L, U); }
   int cur = 0;
@@ -624,13 +625,22 @@ long long run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U
                                       nExt > 0 ? 1 : 0, nT > 0 ? 1 : 0, e->keptH.p, e->keptW.p, e->newHcnt.p, e->newWcnt.p);
     scan(e, e->newHcnt.p, e->H[nx].seg.p, U);
     scan(e, e->newWcnt.p, e->W[nx].seg.p, U);
-    int tot2[2];
+    // define_next_level only needs the new segment offsets: run it now and read the list sizes, the number of
+    // unfinished units, their nside mask and the error flag with ONE synchronisation
+    CK(cudaMemsetAsync(e->active.p, 0, 2 * sizeof(int), e->st));
+    (e->n_launch++, k_next)<<<ub, 256, 0, e->st>>>(u, e->H[nx].seg.p, e->W[nx].seg.p, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
+    int tot2[2], hv[2], hmask = 0;
     CK(cudaMemcpyAsync(&tot2[0], e->H[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CK(cudaMemcpyAsync(&tot2[1], e->W[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&hmask, e->active.p + 1, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
+    CK(cudaGetLastError());
     if (nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; }
     const int nH2 = tot2[0], nW2 = tot2[1];
     peak = std::max(peak, (long long)nH + nW + nT + nH2 + nW2);
+    if (hv[1] != 0) throw DreError{err_text(hv[1])};
     // the seg arrays were just written: grow the payload arrays only (seg is sized U+1 already)
     e->H[nx].ensure(std::max(nH2, 1), L, U); e->W[nx].ensure(std::max(nW2, 1), L, U);
     e->H[nx].n = nH2; e->W[nx].n = nW2;
@@ -642,14 +652,6 @@ long long run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U
     if (nT > 0) (e->n_launch++, k_build_out)<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
                                                              e->keptH.p, e->keptW.p, e->reco_cnt.p, L);
     cur = nx;
-    CK(cudaMemsetAsync(e->active.p, 0, 2 * sizeof(int), e->st));
-    (e->n_launch++, k_next)<<<ub, 256, 0, e->st>>>(u, Hn.seg, Wn.seg, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
-    int hv[2], hmask = 0;
-    CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&hmask, e->active.p + 1, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaStreamSynchronize(e->st));
-    CK(cudaGetLastError());
     if (hv[1] != 0) throw DreError{err_text(hv[1])};
     if (hv[0] == 0) break;
     nkmask = (unsigned)hmask;

@@ -39,6 +39,29 @@ __global__ void k_scan_tile(const int* __restrict__ in, int* __restrict__ out, i
   for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
   if (threadIdx.x == SCAN_THREADS - 1) sums[blockIdx.x] = excl;
 }
+// n <= SCAN_TILE: the whole scan (and the total out[n]) in one launch
+__global__ void k_scan_small(const int* __restrict__ in, int* __restrict__ out, int n) {
+  __shared__ int wsum[SCAN_THREADS / 32];
+  const int base = threadIdx.x * SCAN_ITEMS;
+  int v[SCAN_ITEMS], tot = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? in[base + i] : 0; tot += v[i]; }
+  int x = tot;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
+  }
+  __syncthreads();
+  int excl = x - tot + (w > 0 ? wsum[w - 1] : 0);
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
+  if (threadIdx.x == SCAN_THREADS - 1) out[n] = excl;
+}
 __global__ void k_scan_add(int* __restrict__ out, const int* __restrict__ sums_scanned, int n, int nblocks) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] += sums_scanned[i / SCAN_TILE];
@@ -249,7 +272,7 @@ __global__ void k_build_reco(DreList dstH, DreList srcW, DreUnits u, const int* 
     dre_copy_entry(dstH, di, srcW, si, L, un);
     const unsigned mt = srcW.meta[si];
     const int isel = META_ISEL(mt);
-    dstH.meta[di] = dre_meta(META_DIRK(mt), u.nk[un], isel, RT_RECO);
+    dstH.meta[di] = dre_meta(META_DIRK(mt), u.nk_prev[un], isel, RT_RECO);
     if (isel == 0) { dstH.dplane[di] = 0.; dstH.prev[di] = 0.; }
   }
 }
@@ -273,6 +296,7 @@ __global__ void k_next(DreUnits u, const int* __restrict__ segH, const int* __re
   // active[0] = units that still have rays, active[1] = bit mask of their log2(nside)
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= u.U) return;
+  u.nk_prev[i] = u.nk[i];
   if (u.mode[i] == 0) return;
   u.step[i]++;
   atomicAdd(steps, 1ull);
