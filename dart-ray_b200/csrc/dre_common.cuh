@@ -232,6 +232,7 @@ struct DreAccum {
   int* err;             // first reference STOP condition hit
   int stage_split;      // the deposit row is staged and reduced in this many chunks (smem vs occupancy)
   int want_hash;        // accumulate the intersection checksum (parity runs)
+  int ring_slots;       // stage buffer used as 1 slot (wait for all reads when it wraps) or as a 2-slot ring
   int use_bulk;         // 1: TMA bulk reduce of the whole row; 0: per-lane red.global.add.f64
 };
 enum { CNT_RAYS = 0, CNT_ISECT, CNT_DEP, CNT_BEAM, CNT_SPLIT, CNT_MERGE, CNT_SCA, CNT_ACT, CNT_HASH, CNT_N, CNT_ACTDEP, CNT_DESC };

@@ -76,7 +76,7 @@ struct dre_engine {
   DBuf<DreTask> tasks;
   DBuf<double> pkts;     // ray packets of the current step
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
@@ -466,7 +466,7 @@ DreAccum make_accum(dre_engine* e, const double* prev_rows) {
   DreAccum A;
   A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
   A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
-  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash; A.stage_split = e->opt_stage_split;
+  A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash; A.stage_split = e->opt_stage_split; A.ring_slots = e->opt_ring_slots;
   return A;
 }
 
@@ -1055,6 +1055,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
+  else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));
   else if (s == "dir_kmax") e->opt_dir_kmax = std::max(2, std::min(10, (int)value));
   else DRE_REQUIRE(false, "dre_set_option: unknown option");

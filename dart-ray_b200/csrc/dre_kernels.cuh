@@ -38,12 +38,12 @@ __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* sm
   unsigned short* lam = (unsigned short*)smem;
   for (int j = threadIdx.x; j < g.ROW; j += blockDim.x) lam[j] = g.lamof[j];
   const int sl = dre_stage_len(g.ROW, split);
-  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 6 + 8 + 32 * g.KLn + 2 + dre_pkt_stride(g.L)) * 8;   // keeps 16-B alignment
+  const size_t per = (size_t)(g.ROW + sl + 2 * g.L + (g.L & 1 ? 2 : 0) + 8 + 8 + 32 * g.KLn + 2 + dre_pkt_stride(g.L)) * 8;   // keeps 16-B alignment
   double* base = (double*)(smem + lam_bytes + per * warp);
   ws.lamof = lam; ws.stage = base; ws.F = base + sl; ws.en2 = base + sl + g.ROW; ws.stage_len = sl;
   ws.mbar = (unsigned long long*)(base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0));
   ws.runs = (int*)(ws.mbar + 2);
-  ws.pre = base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 6;
+  ws.pre = base + sl + g.ROW + 2 * g.L + (g.L & 1 ? 2 : 0) + 8;
   ws.pmbar = (unsigned long long*)(ws.pre + 8 + 32 * g.KLn);
   ws.pkt = ws.pre + 8 + 32 * g.KLn + 2;
   if (lane == 0) mbar_init(ws.pmbar);
@@ -53,7 +53,7 @@ __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* sm
 }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
-  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 6 + 8 + 32 * ((L + 31) / 32) + 2 + dre_pkt_stride(L)) * 8;
+  const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 8 + 8 + 32 * ((L + 31) / 32) + 2 + dre_pkt_stride(L)) * 8;
   return lam_bytes + per * warps;
 }
 
