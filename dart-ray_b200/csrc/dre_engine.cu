@@ -7,6 +7,7 @@
 #include "dre_host.h"
 #include "dre_lists.cuh"
 #include "dre_kernels.cuh"
+#include "dre_maps.cuh"
 
 namespace {
 
@@ -58,6 +59,7 @@ struct dre_engine {
   DBuf<double> ftab[DRE_MAXK + 1];
   std::vector<int> h_npix, h_npix_hp, h_off, h_ik, h_cell_src;
   std::vector<double> h_dir_i_out;
+  double h_csize0 = 0;      // csize(0): the root cell
   int S = 0;
   // device-resident accumulators
   DBuf<double> acc, prev, tot, u_fest, lum_lost, lum_lost_prev, psel_sum, psel_av, i_obs, i_obs_in, tmp_d, red_d;
@@ -217,7 +219,7 @@ int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2
   for (int i = 0; i < N; i++) { DRE_REQUIRE(lvl[i] >= 0 && lvl[i] <= max_lvl, "dre_set_grid: lvl out of range"); l8[i] = (unsigned char)lvl[i]; }
   e->cchild.upload(cchild, N, e->st); e->lvl.upload(l8.data(), N, e->st);
   e->cindex.upload((const long long*)cindex, N, e->st);
-  e->ccoord.upload(ccoord, 3 * (size_t)N, e->st); e->csize.upload(csize, N, e->st);
+  e->ccoord.upload(ccoord, 3 * (size_t)N, e->st); e->csize.upload(csize, N, e->st); e->h_csize0 = csize[0];
   CK(cudaStreamSynchronize(e->st));
   g.cchild = e->cchild.p; g.lvl = e->lvl.p; g.cindex = e->cindex.p; g.ccoord = e->ccoord.p; g.csize = e->csize.p;
   for (int i = 0; i <= max_lvl; i++) { g.csize_arr[i] = csize_arr[i]; g.carea_arr[i] = carea_arr[i]; g.cvol_arr[i] = cvol_arr[i]; }
@@ -1012,6 +1014,156 @@ int dre_calc_sed(dre_engine* e, double dist_obs, int units, const double* lambda
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(sed, ds.p, (size_t)g.ndir * g.L * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+namespace {
+// ---- host part of make_maps: the projected-cube textures of one line of sight -------------------------------
+// calc_texture_array (visual_routines.f90:314-453) with find_ray_cell_intersections / calc_ray_inters (:456-566).
+// Default-real literals of the reference (1E-3, 1E-6, 0.99, 2.5, 1+1E-7) are single precision and kept so.
+struct HostTex { int nt = 0, im0 = 0, im1 = 0; std::vector<double> prof; };
+
+double cube_chord(double half_tol, double half, const double* ro, const double* dir) {
+  // cube centred on the origin; faces in the order x+, x-, y+, y-, z+, z- (j = 0..5 of calc_ray_inters);
+  // the first two faces whose intersection point lies inside the face (tolerance (1+1E-7)*cellsize/2 on the two
+  // other axes) give the chord
+  double hit[2][3]; int nhit = 0;
+  for (int j = 0; j < 6 && nhit < 2; j++) {
+    const int ax = j >> 1;
+    const double dx = (j & 1) ? -half : half;
+    const double den = dir[ax];
+    if (den == 0.) continue;
+    const double dist = ((0.0 + dx) - ro[ax]) / den;
+    double pc[3]; bool inside = true;
+    for (int i = 0; i < 3; i++) { pc[i] = ro[i] + dist * dir[i]; if (i != ax && fabs(pc[i] - 0.0) > half_tol) inside = false; }
+    if (!inside) continue;
+    for (int i = 0; i < 3; i++) hit[nhit][i] = pc[i];
+    nhit++;
+  }
+  if (nhit < 2) return 0.0;
+  double s = 0;
+  for (int i = 0; i < 3; i++) { const double d = hit[1][i] - hit[0][i]; s += d * d; }
+  return pow(s, 0.5);      // (sum((p2-p1)**2.))**0.5
+}
+
+void host_textures(const dre_engine* e, int npix_hd, double size_map, double pixel_size_hd, double theta, double phi,
+                   DreMapGeom& m, std::vector<HostTex>& tex) {
+  const DreDev& g = e->g;
+  double dtheta = (double)1E-3f;
+  double* o = m.obs_vec; double* xi = m.xi_dir; double* yi = m.yi_dir;
+  o[0] = sin(theta) * cos(phi); o[1] = sin(theta) * sin(phi); o[2] = cos(theta);
+  double z_zi = 0.0 + o[0] * 0.0; z_zi = z_zi + o[1] * 0.0; z_zi = z_zi + o[2] * 1.0;      // scal_prod(obs_vec, z_dir)
+  const double pi_ref = 2 * (double)1.57079637050628662109375f;                             // pi = 2*asin(1.)
+  if (fabs(fabs(z_zi) - 1.) > (double)1E-6f) {
+    yi[0] = 0.0 - z_zi * o[0]; yi[1] = 0.0 - z_zi * o[1]; yi[2] = 1.0 - z_zi * o[2];
+  } else {                                                                                  // line of sight along Z :360-372
+    if (fabs(theta - pi_ref) < (double)1E-6f) dtheta = -dtheta;
+    o[0] = sin(theta + dtheta) * cos(phi); o[1] = sin(theta + dtheta) * sin(phi); o[2] = cos(theta + dtheta);
+    z_zi = 0.0 + o[0] * 0.0; z_zi = z_zi + o[1] * 0.0; z_zi = z_zi + o[2] * 1.0;
+    yi[0] = 0.0 - z_zi * o[0]; yi[1] = 0.0 - z_zi * o[1]; yi[2] = 1.0 - z_zi * o[2];
+    z_zi = 0.0 + yi[0] * 0.0; z_zi = z_zi + yi[1] * 0.0; z_zi = z_zi + yi[2] * 1.0;
+    yi[0] = yi[0] - z_zi * 0.0; yi[1] = yi[1] - z_zi * 0.0; yi[2] = yi[2] - z_zi * 1.0;
+    o[0] = sin(theta - dtheta) * cos(phi); o[1] = sin(theta - dtheta) * sin(phi); o[2] = cos(theta - dtheta);
+  }
+  const double nrm = sqrt(yi[0] * yi[0] + yi[1] * yi[1] + yi[2] * yi[2]);
+  for (int i = 0; i < 3; i++) yi[i] = yi[i] / nrm;
+  xi[0] = yi[1] * o[2] - yi[2] * o[1];
+  xi[1] = -(yi[0] * o[2] - yi[2] * o[0]);
+  xi[2] = yi[0] * o[1] - yi[1] * o[0];
+  tex.assign(g.max_lvl + 1, HostTex());
+  for (int lev = 1; lev <= g.max_lvl; lev++) {
+    int div = g.base[0]; for (int k = 1; k < lev; k++) div *= g.base[1];
+    const double lside = e->h_csize0 / div;
+    const int nt = (int)lround(npix_hd / size_map * lside * (double)2.5f);
+    HostTex& t = tex[lev]; t.nt = nt; t.prof.assign((size_t)nt * nt, 0.0);
+    std::vector<double> xpp(nt);
+    for (int ip = 0; ip < nt; ip++) {
+      double x = ip * pixel_size_hd - nt * pixel_size_hd / 2;
+      if (nt & 1) x = x + pixel_size_hd / 2;
+      xpp[ip] = x;
+    }
+    const double cellsize = g.csize_arr[lev] * (double)0.99f;
+    const double half = cellsize / 2., half_tol = (double)(1.0f + 1E-7f) * cellsize / 2.;
+    double tot = 0;
+    for (int iy = 0; iy < nt; iy++)          // array-element order of prof2d (ix fastest), the order sum() adds in
+      for (int ix = 0; ix < nt; ix++) {
+        double ro[3];
+        for (int a = 0; a < 3; a++) ro[a] = 0.0 + o[a] * g.par.modelsize + xpp[ix] * xi[a] + xpp[iy] * yi[a];
+        const double len = cube_chord(half_tol, half, ro, o);
+        if (len > 0) t.prof[ix + (size_t)nt * iy] = len;
+        tot += t.prof[ix + (size_t)nt * iy];
+      }
+    for (double& v : t.prof) v = v / tot;
+    std::vector<char> used(nt, 0);           // row ix or column ix holds a positive value
+    for (int iy = 0; iy < nt; iy++) for (int ix = 0; ix < nt; ix++) if (t.prof[ix + (size_t)nt * iy] > 0) { used[ix] = 1; used[iy] = 1; }
+    t.im0 = 0; t.im1 = nt - 1;
+    for (int ix = 1; ix <= nt - 1; ix++) if (used[ix]) { t.im0 = ix - 1; break; }
+    for (int ix = nt - 1; ix >= 1; ix--) if (used[ix]) { t.im1 = ix + 1; break; }
+  }
+}
+}  // namespace
+
+int dre_make_maps(dre_engine* e, int npixel_maps, double map_size_factor, int units, const double* lambda_si, double* maps) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  const DreDev& g = e->g;
+  DRE_REQUIRE(maps != nullptr && npixel_maps > 0 && map_size_factor > 0, "dre_make_maps: bad arguments");
+  DRE_REQUIRE(units >= 0 && units <= 2 && (units != 2 || lambda_si), "dre_make_maps: units must be 0, 1 or 2 (2 needs lambda_si)");
+  DRE_REQUIRE(e->i_obs.p && g.ndir > 0, "dre_make_maps: no i_obs pass was run");
+  DRE_REQUIRE(g.L <= 1024, "dre_make_maps: more than 1024 wavelengths");
+  const int np = npixel_maps, nh = 4 * npixel_maps, L = g.L;
+  const size_t NS = (size_t)g.N + g.S, plane = (size_t)np * np, plane_hd = (size_t)nh * nh;
+  const double size_map = map_size_factor * g.par.modelsize;                   // create_map_arrays :256-269
+  const double pixel_size = size_map / np, pixel_size_hd = size_map / nh;
+  DreMapGeom m; m.npix = np; m.npix_hd = nh; m.area_pixel = pixel_size * pixel_size; m.area_pixel_hd = pixel_size_hd * pixel_size_hd;
+  std::vector<double> xpp_hd(nh), xpp(np);
+  for (int ip = 0; ip < nh; ip++) xpp_hd[ip] = ip * pixel_size_hd - nh * pixel_size_hd / 2;     // :593-596
+  for (int ip = 0; ip < np; ip++) xpp[ip] = ip * pixel_size - np * pixel_size / 2;              // :747-750
+  DBuf<double> d_xhd, d_x, d_hd, d_old, d_tmp, d_map, d_out, d_flux, d_lam, d_prof;
+  DBuf<int> d_list, d_n, d_csrc;
+  d_xhd.upload(xpp_hd.data(), nh, e->st); d_x.upload(xpp.data(), np, e->st);
+  d_hd.ensure(plane_hd * L, 1.0); d_old.ensure(plane_hd * L, 1.0); d_tmp.ensure(plane * L, 1.0); d_map.ensure(plane * L, 1.0);
+  d_out.ensure(plane * L, 1.0); d_flux.ensure(2 * (size_t)L, 1.0); d_list.ensure(g.N, 1.0); d_n.ensure(1, 1.0);
+  std::vector<double> lam(L, 0.0);
+  if (lambda_si) lam.assign(lambda_si, lambda_si + L);
+  d_lam.upload(lam.data(), L, e->st);
+  std::vector<int> cs(std::max(e->S, 1), 0);
+  for (int i = 0; i < e->S; i++) cs[i] = e->h_cell_src[i];
+  d_csrc.upload(cs.data(), cs.size(), e->st);
+  sync_g(e);
+  for (int idir = 0; idir < g.ndir; idir++) {
+    const double theta = e->h_dir_i_out[idir], phi = e->h_dir_i_out[g.ndir + idir];
+    std::vector<HostTex> tex;
+    host_textures(e, nh, size_map, pixel_size_hd, theta, phi, m, tex);
+    const double* io = e->i_obs.p + (size_t)idir * NS * L;
+    CK(cudaMemsetAsync(d_map.p, 0, plane * L * 8, e->st));
+    for (int lev = 1; lev <= g.max_lvl; lev++) {
+      const HostTex& ht = tex[lev];
+      int ncell = 0;
+      CK(cudaMemsetAsync(d_n.p, 0, sizeof(int), e->st));
+      (e->n_launch++, k_map_select)<<<cdiv(g.N, 256), 256, 0, e->st>>>(io, lev, d_list.p, d_n.p);
+      CK(cudaMemcpyAsync(&ncell, d_n.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+      CK(cudaStreamSynchronize(e->st));
+      if (ncell == 0) continue;              // an empty level adds nothing (tot_flux_new = 0, :732)
+      if (ht.prof.empty()) continue;         // a level whose cells are narrower than 0.2 oversampled pixels
+      d_prof.upload(ht.prof.data(), ht.prof.size(), e->st);
+      DreMapTex t; t.prof = d_prof.p; t.nt = ht.nt; t.im0 = ht.im0; t.im1 = ht.im1;
+      CK(cudaMemsetAsync(d_hd.p, 0, plane_hd * L * 8, e->st));
+      (e->n_launch++, k_map_splat)<<<ncell, 256, 0, e->st>>>(m, t, io, d_xhd.p, d_list.p, d_hd.p);
+      (e->n_launch++, k_map_flux)<<<L, 512, 0, e->st>>>(d_hd.p, plane_hd, m.area_pixel_hd, d_flux.p);
+      (e->n_launch++, k_map_median)<<<dim3(cdiv(nh, 128), nh), 128, 0, e->st>>>(d_hd.p, d_old.p, nh, L);
+      (e->n_launch++, k_map_rebin)<<<dim3(cdiv(np, 128), np, L), 128, 0, e->st>>>(d_old.p, d_tmp.p, np, L);
+      (e->n_launch++, k_map_flux)<<<L, 512, 0, e->st>>>(d_tmp.p, plane, m.area_pixel, d_flux.p + L);
+      (e->n_launch++, k_map_accum)<<<dim3(cdiv(plane, 256), L), 256, 0, e->st>>>(d_map.p, d_tmp.p, d_flux.p, d_flux.p + L, plane, L);
+      CK(cudaStreamSynchronize(e->st));      // d_prof is re-uploaded for the next level
+    }
+    if (e->S > 0) (e->n_launch++, k_map_psrc)<<<e->S, std::max(32, (L + 31) / 32 * 32), 0, e->st>>>(m, io, d_x.p, d_csrc.p, d_map.p);
+    (e->n_launch++, k_map_convert)<<<dim3(cdiv(plane, 256), L), 256, 0, e->st>>>(d_map.p, d_out.p, plane, units, d_lam.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(maps + (size_t)idir * L * plane, d_out.p, plane * L * 8, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+  }
   DRE_CATCH(e)
 }
 

@@ -155,6 +155,14 @@ int dre_prepare_scatt(dre_engine*, int iterations, double conv_en_lim,
 int dre_calc_sed(dre_engine*, double dist_obs, int units, const double* lambda_si /*(L) or NULL*/,
                  double* sed /*(L,ndir) out*/);
 
+/* make_maps / map_projection (visual_routines.f90:59-126, 570-772) + convert_maps_to_MJy_sr (:180-246) on the i_obs array
+ * left on the device by dre_run_iobs: external-observer surface-brightness maps of every wavelength and line of sight
+ * (dir_i_out of dre_set_opacity), npixel_maps x npixel_maps pixels over map_size_factor * modelsize, in MJy/sr.
+ * maps is map_arr_out(0:npixel_maps-1, 0:npixel_maps-1, 0:lnum-1, 0:tot_ndir-1), column-major (X' pixel fastest).
+ * units as for dre_calc_sed.  The internal-observer maps (map_in_projection :917) are not built yet. */
+int dre_make_maps(dre_engine*, int npixel_maps, double map_size_factor, int units, const double* lambda_si /*(L) or NULL*/,
+                  double* maps /*(npix,npix,L,ndir) out*/);
+
 /* ---- separate small kernels (north star: cell-list and bounding-box kernels) */
 /* leaf && sum(lum)>0 gate of rt_loop rt_routines.f90:1016; returns the list length */
 int dre_build_source_list(dre_engine*, int rt_type, int32_t* n_sources, int32_t* list_out /*(N) or NULL*/);

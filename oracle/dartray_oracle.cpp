@@ -1228,3 +1228,257 @@ int orc_locate_points(orc_ctx* o, int32_t npts, const double* xyz, const int32_t
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// External-observer surface-brightness maps: make_maps / map_projection (visual_routines.f90:59-177, 251-284,
+// 287-309, 314-453, 456-566, 570-772, 801-863) + convert_maps_to_MJy_sr (:180-246).
+// All wavelengths are mapped (ind_out_maps = every index, iq_maps_id(il) = il: io_routines.f90:2439-2445).
+// Literal restatement; three things a reader of the Fortran would otherwise miss:
+//  * `map_section = map_arr_hd_old(ix0:ix1, iy0:iy1, il)` (:689) assigns a 5x5 section to the 4x4 array
+//    `map_section(0:ns-1,0:ns-1)`; gfortran scalarises over the explicit-shape left-hand side, so the filter
+//    window is [ix-2, ix+1] x [iy-2, iy+1].
+//  * the splat at :639 writes (2*(delta_p/2)+1)^2 pixels from a (delta_p+1)^2 texture section; identical
+//    when delta_p is even (it is, for the symmetric textures built at :378-450); the left-hand extents are used.
+//  * default-real literals: dtheta = 1E-3, the 1E-6 tests, cellsize = csize*0.99, (1+1E-7) are single precision.
+namespace {
+
+struct MapTex { int nt = 0, im0 = 0, im1 = 0; std::vector<double> prof; };   // prof2d(ix,iy) = prof[ix + nt*iy]
+
+double scal_prod3(const double* a, const double* b) { double s = 0.0; for (int i = 0; i < 3; i++) s = s + a[i] * b[i]; return s; }
+
+// calc_ray_inters :479-566 ; returns through flag_ray/p1/p2
+void calc_ray_inters(int j, const double* rc, double cellsize, const double* ro, const double* obs_vec, int& flag_ray, double* p1, double* p2) {
+  const int isel_ray = j / 2;
+  const double dx = (j == 0 || j == 2 || j == 4) ? cellsize / 2. : -cellsize / 2.;
+  double po[3];
+  for (int i = 0; i < 3; i++) po[i] = rc[i] + ((i == isel_ray) ? 1.0 : 0.0) * dx;
+  double num = 0, den = 0;
+  for (int i = 0; i < 3; i++) { const double n = (i == isel_ray) ? 1.0 : 0.0; num += (po[i] - ro[i]) * n; den += obs_vec[i] * n; }
+  if (den == 0.) return;
+  const double dist = num / den;
+  double pcoord[3], rel_vec[3];
+  for (int i = 0; i < 3; i++) { pcoord[i] = ro[i] + dist * obs_vec[i]; rel_vec[i] = pcoord[i] - rc[i]; }
+  int out = 0;
+  for (int i = 0; i < 3; i++) if ((fabs(rel_vec[i]) > (double)(1.0f + 1E-7f) * cellsize / 2.) && i != isel_ray) out++;
+  if (out > 0) return;
+  if (flag_ray == 0) { for (int i = 0; i < 3; i++) p1[i] = pcoord[i]; flag_ray = 1; }
+  else if (flag_ray == 1) { for (int i = 0; i < 3; i++) p2[i] = pcoord[i]; flag_ray = 2; }
+}
+
+// find_ray_cell_intersections :456-475
+double ray_cell_length(const double* rc, double cellsize, const double* ro, const double* obs_vec) {
+  int flag_ray = 0; double p1[3] = {0, 0, 0}, p2[3] = {0, 0, 0};
+  for (int j = 0; j <= 5; j++) {
+    calc_ray_inters(j, rc, cellsize, ro, obs_vec, flag_ray, p1, p2);
+    if (flag_ray == 2) {
+      double s = 0; for (int i = 0; i < 3; i++) s += (p2[i] - p1[i]) * (p2[i] - p1[i]);
+      return pow(s, 0.5);
+    }
+  }
+  return 0.0;
+}
+
+struct MapGeom { int npix, npix_hd; double size_map, pixel_size, pixel_size_hd, area_pixel, area_pixel_hd; };
+MapGeom map_geom(const Ctx& c, int npixel_maps, double map_size_factor) {   // create_map_arrays :252-271
+  MapGeom m; m.npix = npixel_maps; m.npix_hd = 4 * npixel_maps;
+  m.size_map = map_size_factor * c.par.modelsize;
+  m.pixel_size = m.size_map / m.npix; m.pixel_size_hd = m.size_map / m.npix_hd;
+  m.area_pixel = m.pixel_size * m.pixel_size; m.area_pixel_hd = m.pixel_size_hd * m.pixel_size_hd;
+  return m;
+}
+
+// create_texture_array :287-309 + calc_texture_array :314-453
+void calc_texture_array(const Ctx& c, const MapGeom& m, double theta, double phi, double* obs_vec, double* xi_dir, double* yi_dir,
+                        std::vector<MapTex>& tex) {
+  double dtheta = (double)1E-3f;
+  const double z_dir[3] = {0, 0, 1};
+  obs_vec[0] = sin(theta) * cos(phi); obs_vec[1] = sin(theta) * sin(phi); obs_vec[2] = cos(theta);
+  double z_zi = scal_prod3(obs_vec, z_dir);
+  if (fabs(fabs(z_zi) - 1.) > (double)1E-6f) {
+    for (int i = 0; i < 3; i++) yi_dir[i] = z_dir[i] - z_zi * obs_vec[i];
+  } else {
+    if (fabs(theta - PI) < (double)1E-6f) dtheta = -dtheta;
+    obs_vec[0] = sin(theta + dtheta) * cos(phi); obs_vec[1] = sin(theta + dtheta) * sin(phi); obs_vec[2] = cos(theta + dtheta);
+    z_zi = scal_prod3(obs_vec, z_dir);
+    for (int i = 0; i < 3; i++) yi_dir[i] = z_dir[i] - z_zi * obs_vec[i];
+    z_zi = scal_prod3(yi_dir, z_dir);
+    for (int i = 0; i < 3; i++) yi_dir[i] = yi_dir[i] - z_zi * z_dir[i];
+    obs_vec[0] = sin(theta - dtheta) * cos(phi); obs_vec[1] = sin(theta - dtheta) * sin(phi); obs_vec[2] = cos(theta - dtheta);
+  }
+  { double s = 0; for (int i = 0; i < 3; i++) s += yi_dir[i] * yi_dir[i]; const double n = sqrt(s); for (int i = 0; i < 3; i++) yi_dir[i] = yi_dir[i] / n; }
+  xi_dir[0] = yi_dir[1] * obs_vec[2] - yi_dir[2] * obs_vec[1];          // cross_prod(yi_dir, obs_vec, xi_dir) :897-914
+  xi_dir[1] = -(yi_dir[0] * obs_vec[2] - yi_dir[2] * obs_vec[0]);
+  xi_dir[2] = yi_dir[0] * obs_vec[1] - yi_dir[1] * obs_vec[0];
+  tex.assign(c.max_lvl + 1, MapTex());
+  const double rc[3] = {0, 0, 0};
+  for (int i = 1; i <= c.max_lvl; i++) {
+    int den = c.base[0]; for (int k = 0; k < i - 1; k++) den *= c.base[1];
+    const double lside = c.csize[0] / den;
+    const int nt = (int)lround(m.npix_hd / m.size_map * lside * (double)2.5f);
+    MapTex& t = tex[i]; t.nt = nt; t.prof.assign((size_t)nt * nt, 0.0);
+    std::vector<double> xpp(nt);
+    for (int ip = 0; ip < nt; ip++) {
+      if (nt % 2 == 0) xpp[ip] = ip * m.pixel_size_hd - nt * m.pixel_size_hd / 2;
+      else xpp[ip] = ip * m.pixel_size_hd - nt * m.pixel_size_hd / 2 + m.pixel_size_hd / 2;
+    }
+    const double cellsize = c.csize_arr[i] * (double)0.99f;
+    for (int ix = 0; ix < nt; ix++)
+      for (int iy = 0; iy < nt; iy++) {
+        double ro[3];
+        for (int a = 0; a < 3; a++) ro[a] = rc[a] + obs_vec[a] * c.par.modelsize + xpp[ix] * xi_dir[a] + xpp[iy] * yi_dir[a];
+        const double length = ray_cell_length(rc, cellsize, ro, obs_vec);
+        if (length > 0) t.prof[ix + (size_t)nt * iy] = length;
+      }
+    double tot = 0; for (size_t k = 0; k < t.prof.size(); k++) tot += t.prof[k];     // sum() in array element order
+    for (size_t k = 0; k < t.prof.size(); k++) t.prof[k] = t.prof[k] / tot;
+    t.im0 = 0; t.im1 = nt - 1;
+    auto rowcol = [&](int ix) {
+      double sr = 0, sc = 0;
+      for (int k = 0; k < nt; k++) { sr += t.prof[ix + (size_t)nt * k]; sc += t.prof[k + (size_t)nt * ix]; }
+      return sr > 0 || sc > 0;
+    };
+    for (int ix = 1; ix <= nt - 1; ix++) if (rowcol(ix)) { t.im0 = ix - 1; break; }
+    for (int ix = nt - 1; ix >= 1; ix--) if (rowcol(ix)) { t.im1 = ix + 1; break; }
+  }
+}
+
+// value_locate (sed_routines.f90:1662-1693, reverse_order = .FALSE.): ig0
+int value_locate0(double val, const std::vector<double>& a) {
+  const int num = (int)a.size();
+  if (val <= a[0]) return 0;
+  if (val >= a[num - 1]) return num - 2;
+  for (int i = 0; i < num - 1; i++) if (val > a[i] && val <= a[i + 1]) return i;
+  return 0;
+}
+// find_projected_point :839-863
+void find_projected_point(const double* r, const double* obs_vec, const double* xi_dir, const double* yi_dir,
+                          const std::vector<double>& xpp, int& ix_p, int& iy_p) {
+  const double vec_n = scal_prod3(obs_vec, r);
+  double ri[3]; for (int i = 0; i < 3; i++) ri[i] = r[i] - vec_n * obs_vec[i];
+  ix_p = value_locate0(scal_prod3(ri, xi_dir), xpp);
+  iy_p = value_locate0(scal_prod3(ri, yi_dir), xpp);
+}
+// median_section :801-836 on the 16 values of the window (any correct ascending sort gives the same array)
+double median_section16(double* v, bool zero_value) {
+  const int ntot = 16;
+  std::sort(v, v + ntot);
+  int i = 0; while (i < ntot && v[i] == 0) i++;
+  int iel = 0;
+  if (i < ntot && !(zero_value && i > (ntot - 1) / 2)) iel = (ntot - i) / 2 + i;
+  return v[iel];
+}
+
+}  // namespace
+
+extern "C" {
+
+// Textures of one line of sight (for tests): prof of level `level` (nt*nt, ix fastest), returns nt; info = {im0, im1}
+int orc_map_texture(orc_ctx* o, int npixel_maps, double map_size_factor, double theta, double phi, int level,
+                    double* prof, int cap, int32_t* info, double* axes /*obs_vec, xi_dir, yi_dir: 9*/) {
+  const Ctx& c = o->c;
+  const MapGeom m = map_geom(c, npixel_maps, map_size_factor);
+  std::vector<MapTex> tex;
+  calc_texture_array(c, m, theta, phi, axes, axes + 3, axes + 6, tex);
+  if (level < 1 || level > c.max_lvl) return -1;
+  const MapTex& t = tex[level];
+  if (prof && (size_t)cap >= t.prof.size()) memcpy(prof, t.prof.data(), t.prof.size() * 8);
+  if (info) { info[0] = t.im0; info[1] = t.im1; }
+  return t.nt;
+}
+
+// make_maps :59-126 + 169-173.  i_obs (L, N+S, ndir), maps (npix, npix, L, ndir) Fortran order, units as orc_calc_sed.
+int orc_make_maps(orc_ctx* o, int32_t ndir, const double* i_obs, int npixel_maps, double map_size_factor, int units,
+                  const double* lambda_si, double* maps) {
+  const Ctx& c = o->c;
+  const int L = c.L, N = c.N, S = c.S;
+  const size_t NS = (size_t)N + S;
+  const MapGeom m = map_geom(c, npixel_maps, map_size_factor);
+  const int nh = m.npix_hd, np = m.npix;
+  const size_t plane_hd = (size_t)nh * nh, plane = (size_t)np * np;
+  std::vector<double> hd(plane_hd * L), hd_old(plane_hd * L), tmp(plane * L), map(plane * L);
+  std::vector<double> xpp_hd(nh), xpp(np);
+  for (int ip = 0; ip < nh; ip++) xpp_hd[ip] = ip * m.pixel_size_hd - nh * m.pixel_size_hd / 2;     // :593-596
+  for (int ip = 0; ip < np; ip++) xpp[ip] = ip * m.pixel_size - np * m.pixel_size / 2;              // :747-750
+  const double parsec = (double)3.08567758e16f, cspeed = (double)2.99792458e8f;
+  for (int idir = 0; idir < ndir; idir++) {
+    const double theta = c.dir_i_out[idir], phi = c.dir_i_out[ndir + idir];      // dir_i_out(idir,1), (idir,2)
+    double obs_vec[3], xi_dir[3], yi_dir[3];
+    std::vector<MapTex> tex;
+    calc_texture_array(c, m, theta, phi, obs_vec, xi_dir, yi_dir, tex);
+    const double* io = i_obs + (size_t)idir * NS * L;
+    std::fill(map.begin(), map.end(), 0.0);
+    std::vector<double> flux_old(L), flux_new(L);
+    for (int ilevel = 1; ilevel <= c.max_lvl; ilevel++) {       // map_projection :601-737
+      std::fill(hd.begin(), hd.end(), 0.0); std::fill(tmp.begin(), tmp.end(), 0.0);
+      const MapTex& t = tex[ilevel];
+      for (int i = 0; i < N; i++) {
+        if (c.cchild[i] != -1 || c.lvl[i] != ilevel) continue;
+        double s = 0; for (int l = 0; l < L; l++) s += io[(size_t)i * L + l];
+        if (s == 0) continue;
+        int ix_p, iy_p;
+        find_projected_point(&c.ccoord[3 * (size_t)i], obs_vec, xi_dir, yi_dir, xpp_hd, ix_p, iy_p);
+        const int delta_p = t.im1 - t.im0;
+        const int ix0 = ix_p - delta_p / 2, ix1 = ix_p + delta_p / 2, iy0 = iy_p - delta_p / 2, iy1 = iy_p + delta_p / 2;
+        if (ix0 < 0 || ix1 > nh - 1 || iy0 < 0 || iy1 > nh - 1) continue;
+        for (int il = 0; il < L; il++) {
+          const double v = io[(size_t)i * L + il];
+          for (int b = 0; b <= iy1 - iy0; b++)
+            for (int a = 0; a <= ix1 - ix0; a++) {
+              // im1 can reach nt for textures narrower than ~3 pixels (maps far below the npixel_maps >= 200 rule,
+              // io_routines.f90:3207); the Fortran then reads past prof2d — guarded, the element counts as 0
+              if (t.im0 + a >= t.nt || t.im0 + b >= t.nt) continue;
+              hd[(size_t)il * plane_hd + (size_t)(iy0 + b) * nh + ix0 + a] +=
+                  v * t.prof[(t.im0 + a) + (size_t)t.nt * (t.im0 + b)] * (c.csize[i] * c.csize[i]) / m.area_pixel_hd;
+            }
+        }
+      }
+      for (int il = 0; il < L; il++) { double s = 0; for (size_t k = 0; k < plane_hd; k++) s += hd[il * plane_hd + k]; flux_old[il] = s * m.area_pixel_hd; }
+      hd_old = hd; std::fill(hd.begin(), hd.end(), 0.0);
+      for (int ix = 0; ix < nh; ix++)
+        for (int iy = 0; iy < nh; iy++) {
+          double s = 0; for (int il = 0; il < L; il++) s += hd_old[il * plane_hd + (size_t)iy * nh + ix];
+          const bool zero_value = (s == 0);
+          const int ix0 = ix - 2, ix1 = ix + 2, iy0 = iy - 2, iy1 = iy + 2;
+          if (ix0 < 0 || iy0 < 0 || ix1 > nh - 1 || iy1 > nh - 1) {
+            for (int il = 0; il < L; il++) hd[il * plane_hd + (size_t)iy * nh + ix] = hd_old[il * plane_hd + (size_t)iy * nh + ix];
+            continue;
+          }
+          for (int il = 0; il < L; il++) {
+            double v[16];
+            for (int b = 0; b < 4; b++) for (int a = 0; a < 4; a++) v[b * 4 + a] = hd_old[il * plane_hd + (size_t)(iy0 + b) * nh + ix0 + a];
+            hd[il * plane_hd + (size_t)iy * nh + ix] = median_section16(v, zero_value);
+          }
+        }
+      for (int ix = 0; ix < np; ix++)           // rebinning :702-720 (the all-zero shortcut at :707 gives the same zeros)
+        for (int iy = 0; iy < np; iy++)
+          for (int il = 0; il < L; il++) {
+            double s = 0;
+            for (int b = 0; b < 4; b++) for (int a = 0; a < 4; a++) s += hd[il * plane_hd + (size_t)(iy * 4 + b) * nh + ix * 4 + a];
+            tmp[il * plane + (size_t)iy * np + ix] = s / 16;
+          }
+      for (int il = 0; il < L; il++) {
+        double s = 0; for (size_t k = 0; k < plane; k++) s += tmp[il * plane + k];
+        flux_new[il] = s * m.area_pixel;
+        if (flux_new[il] > 0) for (size_t k = 0; k < plane; k++) map[il * plane + k] = map[il * plane + k] + tmp[il * plane + k] * flux_old[il] / flux_new[il];
+      }
+    }
+    for (int i = 0; i < S; i++) {               // point sources :742-770
+      const int ihost = c.cell_src[i];
+      int ix_p, iy_p;
+      find_projected_point(&c.ccoord_p_src[3 * (size_t)i], obs_vec, xi_dir, yi_dir, xpp, ix_p, iy_p);
+      for (int il = 0; il < L; il++)
+        map[il * plane + (size_t)iy_p * np + ix_p] += io[((size_t)N + i) * L + il] * (c.csize[ihost] * c.csize[ihost]) / m.area_pixel;
+    }
+    for (int il = 0; il < L; il++)               // map_arr_out(:,:,kall,idir) = map_arr ; convert_maps_to_MJy_sr :180-246
+      for (size_t k = 0; k < plane; k++) {
+        double v = map[il * plane + k];
+        if (units == 0) { v = v * 1e-7; v = v * 1e20 / (parsec * parsec); }
+        else if (units == 1) { v = v * 1e20 / (parsec * parsec); }
+        else { v = v * (lambda_si[il] * lambda_si[il]) / cspeed; v = v * 1e20 / (parsec * parsec); }
+        maps[((size_t)idir * L + il) * plane + k] = v;
+      }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -135,6 +135,31 @@ class Oracle:
                             abi.dptr(lam), abi.dptr(sed))
         return sed
 
+    def make_maps(self, st, npixel_maps, map_size_factor, units, lambda_si=None):
+        """make_maps / map_projection (visual_routines.f90:59, 570) on st.i_obs; returns (ndir, L, npix, npix) [MJy/sr],
+        the memory image of map_arr_out(0:npix-1, 0:npix-1, 0:L-1, 0:ndir-1) (last index = X' pixel)."""
+        sc = self.scene
+        par = abi.make_params(sc, abi.RTT_I_OBS)          # modelsize
+        self.l.orc_set_params(self.h, C.byref(par))
+        maps = np.zeros((sc.ndir, sc.lnum, npixel_maps, npixel_maps))
+        lam = np.ascontiguousarray(lambda_si if lambda_si is not None else np.zeros(sc.lnum), dtype=np.float64)
+        self.l.orc_make_maps(self.h, C.c_int32(sc.ndir), abi.dptr(st.i_obs), C.c_int(npixel_maps), C.c_double(map_size_factor),
+                             C.c_int(units), abi.dptr(lam), abi.dptr(maps))
+        return maps
+
+    def map_texture(self, npixel_maps, map_size_factor, theta, phi, level):
+        """calc_texture_array (visual_routines.f90:314): (prof2d[iy, ix], im0, im1, axes(3,3) = obs_vec, xi_dir, yi_dir)."""
+        par = abi.make_params(self.scene, abi.RTT_I_OBS)   # modelsize
+        self.l.orc_set_params(self.h, C.byref(par))
+        axes = np.zeros((3, 3)); info = np.zeros(2, dtype=np.int32)
+        self.l.orc_map_texture.restype = C.c_int
+        nt = self.l.orc_map_texture(self.h, C.c_int(npixel_maps), C.c_double(map_size_factor), C.c_double(theta), C.c_double(phi),
+                                    C.c_int(level), None, C.c_int(0), info.ctypes.data_as(C.c_void_p), abi.dptr(axes))
+        prof = np.zeros((nt, nt))
+        self.l.orc_map_texture(self.h, C.c_int(npixel_maps), C.c_double(map_size_factor), C.c_double(theta), C.c_double(phi),
+                               C.c_int(level), abi.dptr(prof), C.c_int(nt * nt), info.ctypes.data_as(C.c_void_p), abi.dptr(axes))
+        return prof, int(info[0]), int(info[1]), axes
+
     def prepare_scatt(self, iterations, st):
         flag = C.c_int32(0)
         self.l.orc_prepare_scatt(self.h, C.c_int(iterations), C.c_double(self.scene.conv_en_lim), abi.dptr(st.u_fest),

@@ -84,6 +84,7 @@ def run_sequence(scene, record=0, iterations=2):
         assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
         assert_fields_close(gst.i_obs, st.i_obs, f"i_obs after pass {rt}")
         assert_fields_close(eng.calc_sed(1.0e4, 0), orc.calc_sed(st, 1.0e4, 0), f"SED (direct light) after pass {rt}")
+        assert_fields_close(eng.make_maps(32, 1.5, 1), orc.make_maps(st, 32, 1.5, 1), f"maps (direct light) after pass {rt}")
         if len(scene.ccoord_obs):
             assert_fields_close(gst.i_obs_in, st.i_obs_in, f"i_obs_in after pass {rt}")
     # scattering iterations
@@ -121,6 +122,10 @@ def run_sequence(scene, record=0, iterations=2):
     lam_si = np.asarray(scene.lambda_um) * 1e-6
     for units in (0, 1, 2):     # N1: calc_sed / sum_i_obs (sed_routines.f90:90-246) in the three i_obs unit systems
         assert_fields_close(eng.calc_sed(1.0e6, units, lam_si), orc.calc_sed(st, 1.0e6, units, lam_si), f"SED units {units}")
+    # N2: make_maps / map_projection (visual_routines.f90:59-177, 570-772): external-observer maps of every direction
+    for npx, fac, units in ((40, 1.0, 0), (24, 2.0, 2)):
+        assert_fields_close(eng.make_maps(npx, fac, units, lam_si), orc.make_maps(st, npx, fac, units, lam_si),
+                            f"maps {npx} px, size factor {fac}, units {units}")
     if len(scene.ccoord_obs):
         assert_fields_close(gst.i_obs_in, st.i_obs_in, "i_obs_in after rtt_i_obs")
     eng.close()
@@ -142,6 +147,25 @@ def test_magtar_small_full_sequence(small_magtar):
 def test_galaxy_tiny_full_sequence(tiny_galaxy):
     """C3: emitting cells (rtt_precalc_cell / rtt_dir_cell / rtt_i_obs_dir_cell, quirk Q3), z wall."""
     run_sequence(tiny_galaxy, record=2_000_000, iterations=2)
+
+
+def test_maps_at_reference_resolution(tiny_galaxy):
+    """N2 at the smallest map the reference accepts (npixel_maps = 200, io_routines.f90:3207): 800 x 800 oversampled
+    pixels, 8 lines of sight from face-on (theta = 0: the tilted-axis branch of calc_texture_array) to edge-on."""
+    from dartray_b200 import abi
+    eng = _engine(tiny_galaxy)
+    orc, st = _oracle(tiny_galaxy)
+    from oracle import oracle as O
+    gst = O.State(tiny_galaxy)
+    for rt in (abi.RTT_PRECALC_CELL, abi.RTT_DIR_CELL):
+        orc.run_pass(rt, 0, st); eng.rt_loop(rt)
+    orc.run_iobs(abi.RTT_I_OBS_DIR_CELL, st)
+    eng.rt_loop_iobs(abi.RTT_I_OBS_DIR_CELL, gst)
+    m_g = eng.make_maps(200, 1.0, 0)
+    m_o = orc.make_maps(st, 200, 1.0, 0)
+    assert m_g.shape == (tiny_galaxy.ndir, tiny_galaxy.lnum, 200, 200) and m_o.max() > 0
+    assert_fields_close(m_g, m_o, "maps 200 px")
+    eng.close()
 
 
 def test_galaxy_small_counters(small_galaxy):
