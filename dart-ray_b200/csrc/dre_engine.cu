@@ -77,8 +77,9 @@ struct dre_engine {
       task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
   DBuf<DreTask> tasks;
   DBuf<double> pkts;     // ray packets of the current step
+  DBuf<unsigned long long> scan_desc; unsigned scan_epoch = 0;   // tile descriptors of the chained scan
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_scan_chained = 1;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
@@ -108,6 +109,13 @@ void scan_level(dre_engine* e, const int* in, int* out, int n, int level) {
 void scan(dre_engine* e, const int* in, int* out, int n) {
   if (n <= 0) { (e->n_launch++, k_set_int)<<<1, 1, 0, e->st>>>(out, 0); return; }
   if (n <= SCAN_TILE) { (e->n_launch++, k_scan_small)<<<1, SCAN_THREADS, 0, e->st>>>(in, out, n); return; }
+  if (e->opt_scan_chained) {
+    const int nb = cdiv(n, SCAN_TILE);
+    if ((size_t)nb > e->scan_desc.cap) { e->scan_desc.ensure(nb, 2.0); CK(cudaMemsetAsync(e->scan_desc.p, 0, e->scan_desc.cap * 8, e->st)); }
+    e->scan_epoch = (e->scan_epoch % 0x3fffffffu) + 1u;      // never 0: a cleared word reads as unpublished
+    (e->n_launch++, k_scan_chained)<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, n, e->scan_desc.p, e->scan_epoch);
+    return;
+  }
   scan_level(e, in, out, n, 0);
 }
 
@@ -1207,6 +1215,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
+  else if (s == "scan_chained") e->opt_scan_chained = value ? 1 : 0;
   else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));
   else if (s == "dir_kmax") e->opt_dir_kmax = std::max(2, std::min(10, (int)value));

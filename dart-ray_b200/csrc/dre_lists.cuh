@@ -62,6 +62,54 @@ __global__ void k_scan_small(const int* __restrict__ in, int* __restrict__ out, 
   for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
   if (threadIdx.x == SCAN_THREADS - 1) out[n] = excl;
 }
+// Any n in ONE launch: chained scan with decoupled look-back.  Tile t publishes {epoch, state, value} as one 64-bit word
+// (state 1 = tile aggregate, 2 = inclusive prefix); a tile adds up the aggregates of its predecessors until it meets an
+// inclusive prefix.  The epoch (one per call, 30 bits) makes the words of earlier scans on the same descriptor array read
+// as "not published", so the array is never cleared.  Tiles are taken in blockIdx order: CUDA dispatches the blocks of
+// a grid in index order, so every predecessor of a resident block has been dispatched and the wait terminates.
+#define SCAN_DESC(epoch, state, val) (((unsigned long long)(epoch) << 34) | ((unsigned long long)(state) << 32) | (unsigned long long)(unsigned)(val))
+__global__ void k_scan_chained(const int* __restrict__ in, int* __restrict__ out, int n, unsigned long long* desc, unsigned epoch) {
+  __shared__ int wsum[SCAN_THREADS / 32];
+  __shared__ int s_prefix;
+  const int tile = blockIdx.x;
+  const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  int v[SCAN_ITEMS], tot = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? in[base + i] : 0; tot += v[i]; }
+  int x = tot;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int agg = wsum[SCAN_THREADS / 32 - 1];
+    volatile unsigned long long* d = desc;
+    int prefix = 0;
+    if (tile > 0) {
+      d[tile] = SCAN_DESC(epoch, 1u, agg);
+      for (int j = tile - 1; j >= 0; ) {
+        const unsigned long long q = d[j];
+        if ((unsigned)(q >> 34) != epoch || ((q >> 32) & 3ull) == 0) continue;      // not published yet
+        prefix += (int)(unsigned)(q & 0xffffffffull);
+        if (((q >> 32) & 3ull) == 2) break;
+        j--;
+      }
+    }
+    d[tile] = SCAN_DESC(epoch, 2u, prefix + agg);
+    s_prefix = prefix;
+  }
+  __syncthreads();
+  int excl = s_prefix + x - tot + (w > 0 ? wsum[w - 1] : 0);
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
+  if (tile == gridDim.x - 1 && threadIdx.x == SCAN_THREADS - 1) out[n] = excl;
+}
 __global__ void k_scan_add(int* __restrict__ out, const int* __restrict__ sums_scanned, int n, int nblocks) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] += sums_scanned[i / SCAN_TILE];

@@ -2,6 +2,5 @@
 run() { lib=$1; shift; o="$*"; args=""; for kv in $o; do args="$args --option $kv"; done
   DARTRAY_ENGINE_LIB=$lib python bench.py --workload ${WL:-trustI} --no-also --no-cpu --no-e2e --steps 2 --warmup 1 $args 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); print('${WL:-trustI} $lib $o', round(d['ms_per_step'],1), round(d['roofline']['kernel_ms_per_step'],1), round(d['roofline']['frac'],4))"; }
-for l in dart-ray_b200/libdartray_engine.so ab/eng_u1.so ab/eng_u4.so ab/eng_u8.so; do run $l; WL=galaxy run $l; done
-DARTRAY_ENGINE_LIB=ab/eng_timing.so python bench.py --workload trustI --no-also --no-cpu --no-e2e --steps 1 --warmup 1 2> gpurun_out/timing_trustI.txt >/dev/null
+d=json.loads(sys.stdin.read()); print('${WL:-trustI} $lib $o', round(d['ms_per_step'],1), round(d['roofline']['kernel_ms_per_step'],1), round(d['roofline']['frac'],4), d['gpu_launches'])"; }
+for o in scan_chained=0 scan_chained=1; do run dart-ray_b200/libdartray_engine.so $o; WL=galaxy run dart-ray_b200/libdartray_engine.so $o; done
