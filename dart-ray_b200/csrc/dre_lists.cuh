@@ -87,22 +87,36 @@ __global__ void k_scan_chained(const int* __restrict__ in, int* __restrict__ out
     if (lane < SCAN_THREADS / 32) wsum[lane] = s;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (w == 0) {          // look-back by one warp: 32 predecessors per round
     const int agg = wsum[SCAN_THREADS / 32 - 1];
     volatile unsigned long long* d = desc;
     int prefix = 0;
     if (tile > 0) {
-      d[tile] = SCAN_DESC(epoch, 1u, agg);
-      for (int j = tile - 1; j >= 0; ) {
-        const unsigned long long q = d[j];
-        if ((unsigned)(q >> 34) != epoch || ((q >> 32) & 3ull) == 0) continue;      // not published yet
-        prefix += (int)(unsigned)(q & 0xffffffffull);
-        if (((q >> 32) & 3ull) == 2) break;
-        j--;
+      if (lane == 0) d[tile] = SCAN_DESC(epoch, 1u, agg);
+      for (int j0 = tile - 1; ; ) {
+        const int j = j0 - lane;
+        // tile -1 stands for "inclusive prefix 0"
+        const unsigned long long q = (j >= 0) ? d[j] : SCAN_DESC(epoch, 2u, 0);
+        const unsigned state = (unsigned)(q >> 32) & 3u;
+        const bool ready = ((unsigned)(q >> 34) == epoch) && state != 0;
+        const unsigned rm = __ballot_sync(0xffffffffu, ready), im = __ballot_sync(0xffffffffu, ready && state == 2u);
+        int upto;                                          // lanes 0..upto take part in this round
+        if (im) {
+          upto = __ffs(im) - 1;                            // nearest predecessor that knows its inclusive prefix
+          const unsigned need = (upto == 31) ? 0xffffffffu : ((2u << upto) - 1u);
+          if ((rm & need) != need) continue;               // an aggregate in between is not published yet
+        } else {
+          if (rm != 0xffffffffu) continue;
+          upto = 31;
+        }
+        int val = (lane <= upto) ? (int)(unsigned)(q & 0xffffffffull) : 0;
+        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+        prefix += val;
+        if (im) break;
+        j0 -= 32;
       }
     }
-    d[tile] = SCAN_DESC(epoch, 2u, prefix + agg);
-    s_prefix = prefix;
+    if (lane == 0) { d[tile] = SCAN_DESC(epoch, 2u, prefix + agg); s_prefix = prefix; }
   }
   __syncthreads();
   int excl = s_prefix + x - tot + (w > 0 ? wsum[w - 1] : 0);
