@@ -60,6 +60,7 @@ struct dre_engine {
   std::vector<int> h_npix, h_npix_hp, h_off, h_ik, h_cell_src;
   std::vector<double> h_dir_i_out;
   double h_csize0 = 0;      // csize(0): the root cell
+  std::vector<double> h_ccoord, h_csize, h_ccoord_p_src; std::vector<int> h_cchild;   // host copies for the map geometry
   int S = 0;
   // device-resident accumulators
   DBuf<double> acc, prev, tot, u_fest, lum_lost, lum_lost_prev, psel_sum, psel_av, i_obs, i_obs_in, tmp_d, red_d;
@@ -228,6 +229,7 @@ int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2
   e->cchild.upload(cchild, N, e->st); e->lvl.upload(l8.data(), N, e->st);
   e->cindex.upload((const long long*)cindex, N, e->st);
   e->ccoord.upload(ccoord, 3 * (size_t)N, e->st); e->csize.upload(csize, N, e->st); e->h_csize0 = csize[0];
+  e->h_ccoord.assign(ccoord, ccoord + 3 * (size_t)N); e->h_csize.assign(csize, csize + N); e->h_cchild.assign(cchild, cchild + N);
   CK(cudaStreamSynchronize(e->st));
   g.cchild = e->cchild.p; g.lvl = e->lvl.p; g.cindex = e->cindex.p; g.ccoord = e->ccoord.p; g.csize = e->csize.p;
   for (int i = 0; i <= max_lvl; i++) { g.csize_arr[i] = csize_arr[i]; g.carea_arr[i] = carea_arr[i]; g.cvol_arr[i] = cvol_arr[i]; }
@@ -322,6 +324,7 @@ int dre_set_sources(dre_engine* e, const double* lumcell, int32_t S, const doubl
   if (S > 0) {
     DRE_REQUIRE(ccoord_p_src && lum_p_src_arr && src_cell && cell_src, "dre_set_sources: point-source arrays missing");
     e->ccoord_p_src.upload(ccoord_p_src, 3 * (size_t)S, e->st); e->lum_p_src.upload(lum_p_src_arr, (size_t)S * g.L, e->st);
+    e->h_ccoord_p_src.assign(ccoord_p_src, ccoord_p_src + 3 * (size_t)S);
     e->src_cell.upload(src_cell, g.N, e->st);
     e->h_cell_src.assign(cell_src, cell_src + S);
   } else {
@@ -1171,6 +1174,122 @@ int dre_make_maps(dre_engine* e, int npixel_maps, double map_size_factor, int un
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(maps + (size_t)idir * L * plane, d_out.p, plane * L * 8, cudaMemcpyDeviceToHost, e->st));
     CK(cudaStreamSynchronize(e->st));
+  }
+  DRE_CATCH(e)
+}
+
+namespace {
+// find_theta_phi_obs_in (rt_routines.f90:3164-3217) for the vector a - b, host libm
+void host_theta_phi(const double* a, const double* b, double& theta, double& phi) {
+  const double pi_ref = 2 * (double)1.57079637050628662109375f, e8 = (double)1E-8f;
+  const double v[3] = {a[0] - b[0], a[1] - b[1], a[2] - b[2]};
+  const double vm = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+  theta = 0; phi = 0;
+  if (!(vm > e8)) return;
+  double tr = (0 * v[0] + 0 * v[1] + 1 * v[2]) / vm;
+  if (fabs(tr - 1.0) < e8) tr = 1.0;
+  if (fabs(tr + 1.0) < e8) tr = -1.0;
+  theta = acos(tr);
+  const double vxy = sin(theta);
+  double pr = (vxy > e8) ? v[0] / (vm * vxy) : 1.;
+  if (fabs(pr - 1.0) < e8) pr = 1.0;
+  if (fabs(pr + 1.0) < e8) pr = -1.0;
+  phi = acos(pr);
+  if (v[1] < 0) phi = 2 * pi_ref - phi;
+}
+}  // namespace
+
+int dre_make_maps_in(dre_engine* e, int32_t ndir_in, const double* ccoord_obs, int kp_maps, int units, const double* lambda_si, double* maps_in) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  const DreDev& g = e->g;
+  DRE_REQUIRE(maps_in && ccoord_obs && ndir_in > 0, "dre_make_maps_in: bad arguments");
+  DRE_REQUIRE(units >= 0 && units <= 2 && (units != 2 || lambda_si), "dre_make_maps_in: units must be 0, 1 or 2 (2 needs lambda_si)");
+  DRE_REQUIRE(e->i_obs_in.p && e->i_obs_ndir_in == ndir_in, "dre_make_maps_in: run dre_run_iobs with the same internal observers first");
+  DRE_REQUIRE(kp_maps >= 0 && kp_maps <= std::min(DRE_MAXK, 12), "dre_make_maps_in: kp_maps out of range");
+  build_dir_table(e, kp_maps);
+  const int L = g.L, N = g.N, S = e->S;
+  const size_t NS = (size_t)N + S;
+  const int nside = 1 << kp_maps, npix = 12 * nside * nside;
+  const double pi_ref = 2 * (double)1.57079637050628662109375f;
+  const double omega_hp = 4 * pi_ref / npix;
+  const int nblk = 2 * e->sm_count;
+  DBuf<DreMapInCell> d_simple, d_flood;
+  DBuf<double> d_map, d_unif, d_out, d_lam, d_len, d_obs;
+  DBuf<int> d_mark, d_list, d_cnt;
+  d_map.ensure((size_t)npix * L, 1.0); d_out.ensure((size_t)npix * L, 1.0); d_unif.ensure(L, 1.0); d_cnt.ensure(1, 1.0);
+  d_mark.zero((size_t)nblk * npix, e->st); d_list.ensure((size_t)nblk * 3 * npix, 1.0); d_len.ensure((size_t)nblk * npix, 1.0);
+  std::vector<double> lam(L, 0.0);
+  if (lambda_si) lam.assign(lambda_si, lambda_si + L);
+  d_lam.upload(lam.data(), L, e->st);
+  sync_g(e);
+  std::vector<DreMapInCell> simple, flood;
+  for (int idir = 0; idir < ndir_in; idir++) {
+    const double* ro = ccoord_obs + 3 * (size_t)idir;
+    simple.clear(); flood.clear();
+    for (int i = 0; i < N; i++) {                       // classification of :959-1014, geometry only
+      if (e->h_cchild[i] != -1) continue;
+      const double* rc = &e->h_ccoord[3 * (size_t)i];
+      const double rel[3] = {rc[0] - ro[0], rc[1] - ro[1], rc[2] - ro[2]};
+      double dist2 = 0; for (int a = 0; a < 3; a++) dist2 += rel[a] * rel[a];
+      const double cellsize = e->h_csize[i];
+      const double omega_cell = (dist2 != 0) ? cellsize * cellsize / dist2 : 4 * pi_ref;
+      DreMapInCell c; c.cell = i; c.pad = 0; c.ip = 0; c.len0 = 0; c.ratio = omega_cell / omega_hp;
+      if (c.ratio < 1) {
+        double th, ph; host_theta_phi(rc, ro, th, ph);
+        c.kind = 1; c.ip = hp::ang2pix_nest(nside, th, ph); simple.push_back(c); continue;
+      }
+      int outs = 0;                                      // calc_outcube rt_routines.f90:2072-2085
+      for (int a = 0; a < 3; a++) if (fabs(rel[a]) > (double)(1.0f + 1E-7f) * cellsize / 2.0) outs++;
+      if (outs == 0) { c.kind = 2; simple.push_back(c); continue; }
+      double th, ph; host_theta_phi(rc, ro, th, ph);
+      c.kind = 3; c.ip = hp::ang2pix_nest(nside, th, ph);
+      const double dir[3] = {sin(th) * cos(ph), sin(th) * sin(ph), cos(th)};
+      // chord of the centre line of sight (find_ray_cell_intersections, cube at rc): translate so that the cube sits at the origin
+      { const double half = cellsize / 2., tol = (double)(1.0f + 1E-7f) * cellsize / 2.;
+        double hit[2][3]; int nhit = 0;
+        for (int j = 0; j < 6 && nhit < 2; j++) {
+          const int ax = j >> 1; const double dx = (j & 1) ? -half : half, den = dir[ax];
+          if (den == 0.) continue;
+          const double dist = ((rc[ax] + dx) - ro[ax]) / den;
+          double pc[3]; bool inside = true;
+          for (int a = 0; a < 3; a++) { pc[a] = ro[a] + dist * dir[a]; if (a != ax && fabs(pc[a] - rc[a]) > tol) inside = false; }
+          if (!inside) continue;
+          for (int a = 0; a < 3; a++) hit[nhit][a] = pc[a];
+          nhit++;
+        }
+        if (nhit == 2) { double q = 0; for (int a = 0; a < 3; a++) q += (hit[1][a] - hit[0][a]) * (hit[1][a] - hit[0][a]); c.len0 = pow(q, 0.5); }
+      }
+      flood.push_back(c);
+    }
+    for (int i = 0; i < S; i++) {                       // point sources :1038-1073 (kind 1, entry N + i)
+      const double* rc = &e->h_ccoord_p_src[3 * (size_t)i];
+      double dist2 = 0; for (int a = 0; a < 3; a++) dist2 += (rc[a] - ro[a]) * (rc[a] - ro[a]);
+      if (dist2 == 0) continue;
+      const double cellsize = e->h_csize[e->h_cell_src[i]];
+      DreMapInCell c; c.cell = N + i; c.kind = 1; c.pad = 0; c.len0 = 0; c.ratio = cellsize * cellsize / dist2 / omega_hp;
+      double th, ph; host_theta_phi(rc, ro, th, ph);
+      c.ip = hp::ang2pix_nest(nside, th, ph);
+      simple.push_back(c);
+    }
+    const double* io = e->i_obs_in.p + (size_t)idir * NS * L;
+    CK(cudaMemsetAsync(d_map.p, 0, (size_t)npix * L * 8, e->st)); CK(cudaMemsetAsync(d_unif.p, 0, (size_t)L * 8, e->st));
+    CK(cudaMemsetAsync(d_cnt.p, 0, sizeof(int), e->st));
+    d_obs.upload(ro, 3, e->st);
+    if (!simple.empty()) {
+      d_simple.upload(simple.data(), simple.size(), e->st);
+      (e->n_launch++, k_mapin_simple)<<<cdiv(simple.size() * L, 256), 256, 0, e->st>>>(d_simple.p, (int)simple.size(), io, npix, L, d_map.p, d_unif.p);
+    }
+    if (!flood.empty()) {
+      d_flood.upload(flood.data(), flood.size(), e->st);
+      (e->n_launch++, k_mapin_flood)<<<nblk, 128, 0, e->st>>>(d_flood.p, (int)flood.size(), io, d_obs.p, kp_maps, npix, L, e->dirtab[kp_maps].p,
+                                                             d_mark.p, d_list.p, d_len.p, d_cnt.p, d_map.p);
+    }
+    (e->n_launch++, k_mapin_finish)<<<dim3(cdiv(npix, 256), L), 256, 0, e->st>>>(d_map.p, d_unif.p, d_out.p, npix, units, d_lam.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(maps_in + (size_t)idir * L * npix, d_out.p, (size_t)npix * L * 8, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));       // host vectors are reused for the next observer
   }
   DRE_CATCH(e)
 }

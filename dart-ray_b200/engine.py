@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("DARTRAY_ENGINE_LIB", os.path.join(_HERE, "libdartray_
 SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
-    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_calc_sed", "dre_make_maps", "dre_build_source_list",
+    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
     "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
@@ -227,6 +227,16 @@ class Engine:
         lam = None if lambda_si is None else np.ascontiguousarray(lambda_si, dtype=np.float64)
         self._ck(self.l.dre_make_maps(self.h, C.c_int(npixel_maps), C.c_double(map_size_factor), C.c_int(units),
                                       abi.dptr(lam) if lam is not None else None, abi.dptr(maps)))
+        return maps
+
+    def make_maps_in(self, kp_maps, units, lambda_si=None):
+        """map_in_projection (visual_routines.f90:917) from the device-resident i_obs_in array; returns
+        (ndir_in, L, 12*4**kp_maps) [MJy/sr] = the memory image of map_in_arr_out(pixel, lambda, observer)."""
+        obs = np.ascontiguousarray(self.scene.ccoord_obs, dtype=np.float64)
+        maps = np.zeros((obs.shape[0], self.scene.lnum, 12 * 4 ** kp_maps))
+        lam = None if lambda_si is None else np.ascontiguousarray(lambda_si, dtype=np.float64)
+        self._ck(self.l.dre_make_maps_in(self.h, C.c_int32(obs.shape[0]), abi.dptr(obs), C.c_int(kp_maps), C.c_int(units),
+                                         abi.dptr(lam) if lam is not None else None, abi.dptr(maps)))
         return maps
 
     def rt_mpi(self, rt_type):

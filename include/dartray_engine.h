@@ -159,9 +159,15 @@ int dre_calc_sed(dre_engine*, double dist_obs, int units, const double* lambda_s
  * left on the device by dre_run_iobs: external-observer surface-brightness maps of every wavelength and line of sight
  * (dir_i_out of dre_set_opacity), npixel_maps x npixel_maps pixels over map_size_factor * modelsize, in MJy/sr.
  * maps is map_arr_out(0:npixel_maps-1, 0:npixel_maps-1, 0:lnum-1, 0:tot_ndir-1), column-major (X' pixel fastest).
- * units as for dre_calc_sed.  The internal-observer maps (map_in_projection :917) are not built yet. */
+ * units as for dre_calc_sed. */
 int dre_make_maps(dre_engine*, int npixel_maps, double map_size_factor, int units, const double* lambda_si /*(L) or NULL*/,
                   double* maps /*(npix,npix,L,ndir) out*/);
+
+/* map_in_projection (visual_routines.f90:917-1076, calc_cube_texture_sphere :1080-1182) + convert_maps_to_MJy_sr on the i_obs_in
+ * array left on the device by dre_run_iobs (same observers): every leaf cell is projected on the observer's HEALPix sphere of
+ * nside 2**kp_maps.  maps_in is map_in_arr_out(0:12*4**kp_maps-1, 0:lnum-1, 0:tot_ndir_in-1), column-major, MJy/sr. */
+int dre_make_maps_in(dre_engine*, int32_t ndir_in, const double* ccoord_obs /*(3,ndir_in)*/, int kp_maps, int units,
+                     const double* lambda_si /*(L) or NULL*/, double* maps_in /*(npix_maps,L,ndir_in) out*/);
 
 /* ---- separate small kernels (north star: cell-list and bounding-box kernels) */
 /* leaf && sum(lum)>0 gate of rt_loop rt_routines.f90:1016; returns the list length */

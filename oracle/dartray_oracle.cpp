@@ -1368,6 +1368,108 @@ double median_section16(double* v, bool zero_value) {
   return v[iel];
 }
 
+
+// ---- internal-observer maps: map_in_projection (visual_routines.f90:917-1076), calc_cube_texture_sphere (:1080-1182) ----
+// neighbours of a NESTED pixel.  The reference's neighbours_nest (healpix_routines.f90:416-852) is the HEALPix library
+// routine; the flood fill below only uses the SET of neighbours (the order changes nothing but the order of a sum), so the
+// set is produced here from the library's face-adjacency tables ((x, y, face) arithmetic) instead of transcribing the
+// 440-line case analysis; tests pin it with the nside = 1 table the reference hard-codes (:466-477) and with symmetry /
+// adjacency invariants.  Returns the number of distinct neighbours (8, or 7 at the eight 3-face corners).
+void nest2xyf(int nside, int ipix, int& ix, int& iy, int& face) {
+  const int nsq = nside * nside;
+  face = ipix / nsq;
+  const int ipf = ipix % nsq;
+  const int ip_low = ipf & 1023, ip_trunc = ipf / 1024, ip_med = ip_trunc & 1023, ip_hi = ip_trunc / 1024;   // pix2xy_nest :947-1010
+  ix = 1024 * pix2x[ip_hi] + 32 * pix2x[ip_med] + pix2x[ip_low];
+  iy = 1024 * pix2y[ip_hi] + 32 * pix2y[ip_med] + pix2y[ip_low];
+}
+int xyf2nest(int nside, int ix, int iy, int face) {      // xy2pix_nest :868-927
+  return x2pix1[ix & 127] + y2pix1[iy & 127] + (x2pix1[ix / 128] + y2pix1[iy / 128]) * 16384 + face * nside * nside;
+}
+int neighbours_set(int nside, int ipix, int* out) {
+  static const int xo[8] = {-1, -1, 0, 1, 1, 1, 0, -1}, yo[8] = {0, 1, 1, 1, 0, -1, -1, -1};
+  static const int facearray[9][12] = {
+      {8, 9, 10, 11, -1, -1, -1, -1, 10, 11, 8, 9},   // S
+      {5, 6, 7, 4, 8, 9, 10, 11, 9, 10, 11, 8},       // SE
+      {-1, -1, -1, -1, 5, 6, 7, 4, -1, -1, -1, -1},   // E
+      {4, 5, 6, 7, 11, 8, 9, 10, 11, 8, 9, 10},       // SW
+      {0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11},         // centre
+      {1, 2, 3, 0, 0, 1, 2, 3, 5, 6, 7, 4},           // NE
+      {-1, -1, -1, -1, 7, 4, 5, 6, -1, -1, -1, -1},   // W
+      {3, 0, 1, 2, 3, 0, 1, 2, 4, 5, 6, 7},           // NW
+      {2, 3, 0, 1, -1, -1, -1, -1, 0, 1, 2, 3}};      // N
+  static const int swaparray[9][3] = {{0, 0, 3}, {0, 0, 6}, {0, 0, 0}, {0, 0, 5}, {0, 0, 0}, {5, 0, 0}, {0, 0, 0}, {6, 0, 0}, {3, 0, 0}};
+  int ix, iy, face; nest2xyf(nside, ipix, ix, iy, face);
+  int n = 0;
+  for (int i = 0; i < 8; i++) {
+    int x = ix + xo[i], y = iy + yo[i], nb = 4;
+    if (x < 0) { x += nside; nb -= 1; } else if (x >= nside) { x -= nside; nb += 1; }
+    if (y < 0) { y += nside; nb -= 3; } else if (y >= nside) { y -= nside; nb += 3; }
+    const int f = facearray[nb][face];
+    if (f < 0) continue;
+    const int bits = swaparray[nb][face >> 2];
+    if (bits & 1) x = nside - x - 1;
+    if (bits & 2) y = nside - y - 1;
+    if (bits & 4) std::swap(x, y);
+    const int p = xyf2nest(nside, x, y, f);
+    bool dup = (p == ipix);
+    for (int k = 0; k < n; k++) if (out[k] == p) dup = true;
+    if (!dup) out[n++] = p;
+  }
+  return n;
+}
+
+// find_theta_phi_obs_in rt_routines.f90:3164-3217 with (ro, rc) = (a, b): angles of a - b
+void theta_phi_of(const double* a, const double* b, double& theta, double& phi) {
+  double vec[3]; for (int i = 0; i < 3; i++) vec[i] = a[i] - b[i];
+  const double vec_mod = sqrt(vec[0] * vec[0] + vec[1] * vec[1] + vec[2] * vec[2]);
+  const double E8 = (double)1E-8f;
+  if (vec_mod > E8) {
+    double theta_ratio = (0 * vec[0] + 0 * vec[1] + 1 * vec[2]) / vec_mod;
+    if (fabs(theta_ratio - 1.0) < E8) theta_ratio = 1.0;
+    if (fabs(theta_ratio + 1.0) < E8) theta_ratio = -1.0;
+    theta = acos(theta_ratio);
+    const double vec_xy = sin(theta);
+    double phi_ratio = (vec_xy > E8) ? vec[0] / (vec_mod * vec_xy) : 1.;
+    if (fabs(phi_ratio - 1.0) < E8) phi_ratio = 1.0;
+    if (fabs(phi_ratio + 1.0) < E8) phi_ratio = -1.0;
+    phi = acos(phi_ratio);
+    if (vec[1] < 0) phi = 2 * PI - phi;
+  } else { theta = 0; phi = 0; }
+}
+
+// calc_cube_texture_sphere :1080-1182: flood fill over the HEALPix neighbours from the pixel of the cell centre while the
+// pixel-centre lines of sight cross the cube; mproj = normalised chord lengths, iq_px = the pixels found (n_px)
+void calc_cube_texture_sphere(double cellsize, const double* rc, const double* ro, int nside_map, std::vector<double>& mproj,
+                              std::vector<int>& iq_px) {
+  iq_px.clear();
+  double theta, phi; theta_phi_of(rc, ro, theta, phi);
+  const int ip = ang2pix_nest(nside_map, theta, phi);
+  double obs_vec[3] = {sin(theta) * cos(phi), sin(theta) * sin(phi), cos(theta)};
+  double length = ray_cell_length(rc, cellsize, ro, obs_vec);
+  iq_px.push_back(ip);
+  if (length > 0) mproj[ip] = length; else { mproj[ip] = 1; return; }
+  std::vector<int> neighbour_list, pix_list;
+  int nb[8]; int nn = neighbours_set(nside_map, ip, nb);
+  neighbour_list.assign(nb, nb + nn);
+  while (!neighbour_list.empty()) {
+    pix_list.swap(neighbour_list); neighbour_list.clear();
+    for (int ipix : pix_list) {
+      if (mproj[ipix] > 0) continue;
+      pix2ang_nest(nside_map, ipix, theta, phi);
+      obs_vec[0] = sin(theta) * cos(phi); obs_vec[1] = sin(theta) * sin(phi); obs_vec[2] = cos(theta);
+      length = ray_cell_length(rc, cellsize, ro, obs_vec);
+      if (length > 0) {
+        mproj[ipix] = length; iq_px.push_back(ipix);
+        nn = neighbours_set(nside_map, ipix, nb);
+        neighbour_list.insert(neighbour_list.end(), nb, nb + nn);
+      }
+    }
+  }
+  double s = 0; for (int p : iq_px) s += mproj[p];
+  for (int p : iq_px) mproj[p] = mproj[p] / s;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1476,6 +1578,74 @@ int orc_make_maps(orc_ctx* o, int32_t ndir, const double* i_obs, int npixel_maps
         else if (units == 1) { v = v * 1e20 / (parsec * parsec); }
         else { v = v * (lambda_si[il] * lambda_si[il]) / cspeed; v = v * 1e20 / (parsec * parsec); }
         maps[((size_t)idir * L + il) * plane + k] = v;
+      }
+  }
+  return 0;
+}
+
+
+// neighbours of a NESTED pixel as a set (see neighbours_set); returns the count
+int orc_neighbours(int nside, int ipix, int32_t* out) { hp_init(); int nb[8]; const int n = neighbours_set(nside, ipix, nb); for (int i = 0; i < n; i++) out[i] = nb[i]; return n; }
+
+// map_in_projection :917-1076 for every internal observer + convert_maps_to_MJy_sr.  i_obs_in (L, N+S, ndir_in),
+// maps_in = map_in_arr_out(0:npix_maps-1, 0:L-1, 0:ndir_in-1) Fortran order, npix_maps = 12 * 4**kp_maps.
+int orc_make_maps_in(orc_ctx* o, int32_t ndir_in, const double* ccoord_obs, const double* i_obs_in, int kp_maps, int units,
+                     const double* lambda_si, double* maps_in) {
+  hp_init();
+  const Ctx& c = o->c;
+  const int L = c.L, N = c.N, S = c.S;
+  const size_t NS = (size_t)N + S;
+  const int nside_map = 1 << kp_maps, npix = 12 * nside_map * nside_map;
+  const double omega_hp = 4 * PI / npix;
+  const double parsec = (double)3.08567758e16f, cspeed = (double)2.99792458e8f;
+  std::vector<double> mproj(npix, 0.0), map((size_t)npix * L);
+  std::vector<int> iq_px;
+  for (int idir = 0; idir < ndir_in; idir++) {
+    const double* ro = ccoord_obs + 3 * (size_t)idir;
+    const double* io = i_obs_in + (size_t)idir * NS * L;
+    std::fill(map.begin(), map.end(), 0.0);
+    for (int i = 0; i < N; i++) {
+      if (c.cchild[i] != -1) continue;
+      double s = 0; for (int l = 0; l < L; l++) s += io[(size_t)i * L + l];
+      if (s == 0) continue;
+      const double* rc = &c.ccoord[3 * (size_t)i];
+      double rel_vec[3]; for (int a = 0; a < 3; a++) rel_vec[a] = rc[a] - ro[a];
+      double dist2 = 0; for (int a = 0; a < 3; a++) dist2 += rel_vec[a] * rel_vec[a];
+      const double cellsize = c.csize[i];
+      const double omega_cell = (dist2 != 0) ? cellsize * cellsize / dist2 : 4 * PI;
+      const double omega_ratio = omega_cell / omega_hp;
+      if (omega_ratio < 1) {                                    // case 1: one pixel holds the whole cell
+        double theta, phi; theta_phi_of(rc, ro, theta, phi);
+        const int ip = ang2pix_nest(nside_map, theta, phi);
+        for (int il = 0; il < L; il++) map[(size_t)il * npix + ip] += io[(size_t)i * L + il] * omega_ratio;
+        continue;
+      }
+      if (calc_outcube_sum(rel_vec, cellsize) == 0) {           // case 2: the observer is inside the cell
+        for (int il = 0; il < L; il++) { const double v = io[(size_t)i * L + il] / 2.; for (int p = 0; p < npix; p++) map[(size_t)il * npix + p] += v; }
+        continue;
+      }
+      calc_cube_texture_sphere(cellsize, rc, ro, nside_map, mproj, iq_px);     // case 3
+      for (int il = 0; il < L; il++)
+        for (int p : iq_px) map[(size_t)il * npix + p] += io[(size_t)i * L + il] * mproj[p] * omega_ratio;
+      for (int p : iq_px) mproj[p] = 0;
+    }
+    for (int i = 0; i < S; i++) {                                // point sources :1038-1073
+      const double* rc = &c.ccoord_p_src[3 * (size_t)i];
+      double dist2 = 0; for (int a = 0; a < 3; a++) dist2 += (rc[a] - ro[a]) * (rc[a] - ro[a]);
+      if (dist2 == 0) continue;
+      const double cellsize = c.csize[c.cell_src[i]];
+      const double omega_ratio = cellsize * cellsize / dist2 / omega_hp;
+      double theta, phi; theta_phi_of(rc, ro, theta, phi);
+      const int ip = ang2pix_nest(nside_map, theta, phi);
+      for (int il = 0; il < L; il++) map[(size_t)il * npix + ip] += io[((size_t)N + i) * L + il] * omega_ratio;
+    }
+    for (int il = 0; il < L; il++)
+      for (int p = 0; p < npix; p++) {
+        double v = map[(size_t)il * npix + p];
+        if (units == 0) { v = v * 1e-7; v = v * 1e20 / (parsec * parsec); }
+        else if (units == 1) { v = v * 1e20 / (parsec * parsec); }
+        else { v = v * (lambda_si[il] * lambda_si[il]) / cspeed; v = v * 1e20 / (parsec * parsec); }
+        maps_in[((size_t)idir * L + il) * npix + p] = v;
       }
   }
   return 0;

@@ -147,6 +147,23 @@ class Oracle:
                              C.c_int(units), abi.dptr(lam), abi.dptr(maps))
         return maps
 
+    def make_maps_in(self, st, kp_maps, units, lambda_si=None):
+        """map_in_projection (visual_routines.f90:917) on st.i_obs_in for every internal observer; returns
+        (ndir_in, L, 12*4**kp_maps) [MJy/sr] = the memory image of map_in_arr_out(pixel, lambda, observer)."""
+        sc = self.scene
+        obs = np.ascontiguousarray(sc.ccoord_obs, dtype=np.float64)
+        npix = 12 * 4 ** kp_maps
+        maps = np.zeros((obs.shape[0], sc.lnum, npix))
+        lam = np.ascontiguousarray(lambda_si if lambda_si is not None else np.zeros(sc.lnum), dtype=np.float64)
+        self.l.orc_make_maps_in(self.h, C.c_int32(obs.shape[0]), abi.dptr(obs), abi.dptr(st.i_obs_in), C.c_int(kp_maps),
+                                C.c_int(units), abi.dptr(lam), abi.dptr(maps))
+        return maps
+
+    def neighbours(self, nside, ipix):
+        out = np.zeros(8, dtype=np.int32)
+        n = self.l.orc_neighbours(C.c_int(nside), C.c_int(int(ipix)), out.ctypes.data_as(C.c_void_p))
+        return out[:n].copy()
+
     def map_texture(self, npixel_maps, map_size_factor, theta, phi, level):
         """calc_texture_array (visual_routines.f90:314): (prof2d[iy, ix], im0, im1, axes(3,3) = obs_vec, xi_dir, yi_dir)."""
         par = abi.make_params(self.scene, abi.RTT_I_OBS)   # modelsize

@@ -128,6 +128,10 @@ def run_sequence(scene, record=0, iterations=2):
                             f"maps {npx} px, size factor {fac}, units {units}")
     if len(scene.ccoord_obs):
         assert_fields_close(gst.i_obs_in, st.i_obs_in, "i_obs_in after rtt_i_obs")
+        # N2, internal observers: map_in_projection (visual_routines.f90:917-1182) on HEALPix spheres of nside 8 and 64
+        for kp, units in ((3, 0), (6, 2)):
+            assert_fields_close(eng.make_maps_in(kp, units, lam_si), orc.make_maps_in(st, kp, units, lam_si),
+                                f"internal-observer maps kp_maps {kp}, units {units}")
     eng.close()
 
 
