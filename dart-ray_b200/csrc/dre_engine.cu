@@ -1208,6 +1208,7 @@ int dre_make_maps_in(dre_engine* e, int32_t ndir_in, const double* ccoord_obs, i
   DRE_REQUIRE(units >= 0 && units <= 2 && (units != 2 || lambda_si), "dre_make_maps_in: units must be 0, 1 or 2 (2 needs lambda_si)");
   DRE_REQUIRE(e->i_obs_in.p && e->i_obs_ndir_in == ndir_in, "dre_make_maps_in: run dre_run_iobs with the same internal observers first");
   DRE_REQUIRE(kp_maps >= 0 && kp_maps <= std::min(DRE_MAXK, 12), "dre_make_maps_in: kp_maps out of range");
+  DRE_REQUIRE((long long)ndir_in * (g.N + 1) < 0x7fffffffLL, "dre_make_maps_in: too many observers x cells");
   build_dir_table(e, kp_maps);
   const int L = g.L, N = g.N, S = e->S;
   const size_t NS = (size_t)N + S;
@@ -1284,7 +1285,7 @@ int dre_make_maps_in(dre_engine* e, int32_t ndir_in, const double* ccoord_obs, i
     if (!flood.empty()) {
       d_flood.upload(flood.data(), flood.size(), e->st);
       (e->n_launch++, k_mapin_flood)<<<nblk, 128, 0, e->st>>>(d_flood.p, (int)flood.size(), io, d_obs.p, kp_maps, npix, L, e->dirtab[kp_maps].p,
-                                                             d_mark.p, d_list.p, d_len.p, d_cnt.p, d_map.p);
+                                                             d_mark.p, d_list.p, d_len.p, d_cnt.p, d_map.p, idir * (N + 1));
     }
     (e->n_launch++, k_mapin_finish)<<<dim3(cdiv(npix, 256), L), 256, 0, e->st>>>(d_map.p, d_unif.p, d_out.p, npix, units, d_lam.p);
     CK(cudaGetLastError());

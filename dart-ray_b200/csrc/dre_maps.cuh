@@ -266,7 +266,7 @@ __global__ void k_mapin_simple(const DreMapInCell* __restrict__ cells, int n, co
 // never cleared), two frontier lists, the found pixels and their chords.
 __global__ void k_mapin_flood(const DreMapInCell* __restrict__ cells, int n, const double* __restrict__ io, const double* __restrict__ obs,
                               int kp, int npix, int L, const DreDir* __restrict__ dirtab, int* __restrict__ mark_all, int* __restrict__ list_all,
-                              double* __restrict__ len_all, int* __restrict__ counter, double* __restrict__ map) {
+                              double* __restrict__ len_all, int* __restrict__ counter, double* __restrict__ map, int token0) {
   const DreDev& g = c_g;
   int* mark = mark_all + (size_t)blockIdx.x * npix;
   int* cur = list_all + (size_t)blockIdx.x * 3 * npix;
@@ -277,7 +277,7 @@ __global__ void k_mapin_flood(const DreMapInCell* __restrict__ cells, int n, con
   __shared__ double s_red[32];
   __shared__ double s_total;
   const double ro[3] = {obs[0], obs[1], obs[2]};
-  int token = 0;
+  int token = token0;      // marks of earlier launches (other observers) hold smaller tokens
   for (;;) {
     if (threadIdx.x == 0) s_k = atomicAdd(counter, 1);
     __syncthreads();
