@@ -18,7 +18,8 @@ __device__ __forceinline__ double dre_src_lum(const DreDev& g, int nc, int l) { 
 }
 
 #define DRE_PKT_HDR 20      // doubles of a ray packet in front of the luminosities (record 16 + direction 4)
-__host__ __device__ inline int dre_pkt_stride(int L) { return DRE_PKT_HDR + L + (L & 1); }
+// The stride is a multiple of 4 doubles: the direction inside a packet is written as one 32-B aligned DreDir.
+__host__ __device__ inline int dre_pkt_stride(int L) { return DRE_PKT_HDR + ((L + 3) & ~3); }
 __host__ __device__ inline int dre_stage_len(int ROW, int split) {
   int n = (ROW + split - 1) / split; n += n & 1; return n < 2 ? 2 : n;
 }
