@@ -521,10 +521,11 @@ def galaxy_grid(base=(3, 3), max_lvl=4, min_lvl=2, max_dtau=0.01, max_dlum=0.5e-
 
 
 def galaxy_scene(max_lvl=4, min_lvl=2, lnum=None, kp_sca_max=1, max_dtau=0.01, max_dlum=0.5e-6, tau_scale=1.0,
-                 name="galaxy") -> Scene:
+                 name="galaxy", base=(3, 3)) -> Scene:
     """C3: GALAXY_GRIDS/input_galaxy_example1.in — no point sources, every leaf with stellar emissivity
     emits (rtt_precalc_cell / rtt_dir_cell), 8 directions theta = 0..pi/2, z wall [0.3, 0.7]."""
-    g, w_old, w_young = galaxy_grid(max_lvl=max_lvl, min_lvl=min_lvl, max_dtau=max_dtau, max_dlum=max_dlum, tau_scale=tau_scale)
+    g, w_old, w_young = galaxy_grid(base=base, max_lvl=max_lvl, min_lvl=min_lvl, max_dtau=max_dtau, max_dlum=max_dlum,
+                                    tau_scale=tau_scale)
     t = _load_table("galaxy")
     sel = np.arange(len(t["lambda_um"]))
     if lnum is not None:

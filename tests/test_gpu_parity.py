@@ -9,10 +9,12 @@ pytestmark = pytest.mark.gpu
 RTOL = 1e-5
 
 
-def _engine(scene):
+def _engine(scene, options=()):
     from dartray_b200 import engine
     eng = engine.Engine(scene)
     eng.set_option("hash", 1)   # intersection checksum (off by default: parity facility)
+    for k, v in options:        # engine tuning options (dre_set_option): none of them may change a result
+        eng.set_option(k, v)
     return eng
 
 
@@ -43,10 +45,10 @@ def assert_counters_equal(c1, c2, keys=("sources", "rays", "intersections", "dep
         assert d1[k] == d2[k], f"counter {k}: engine {d1[k]} oracle {d2[k]}"
 
 
-def run_sequence(scene, record=0, iterations=2):
+def run_sequence(scene, record=0, iterations=2, options=()):
     """precalc_src -> dir_src -> i_obs_dir_src -> scatt x iterations -> i_obs on both sides, comparing after each pass."""
     from dartray_b200 import abi
-    eng = _engine(scene)
+    eng = _engine(scene, options)
     orc, st = _oracle(scene)
     from oracle import oracle as O
     gst = O.State(scene)
