@@ -234,5 +234,12 @@ struct DreAccum {
   int want_hash;        // accumulate the intersection checksum (parity runs)
   int ring_slots;       // stage buffer used as 1 slot (wait for all reads when it wraps) or as a 2-slot ring
   int use_bulk;         // 1: TMA bulk reduce of the whole row; 0: per-lane red.global.add.f64
+  // Order-independent accumulation (option "deterministic"): every contribution is first rounded to a multiple of a
+  // per-wavelength quantum q = 2^(e-52), 2^e >= an a-priori bound of the sum, so that all partial sums are exact in
+  // fp64 whatever the order of the reductions.  qc holds the rounding constants C = 1.5 * 2^52 * q (rq(v) = (v + C) - C):
+  // [0,Lq) scaspe, [Lq,2Lq) u_final / u_fest, [2Lq,3Lq) lum_lost, [3Lq] psel_sum; Lq = L rounded up to even.
+  int det;
+  const double* qc;
 };
+__host__ __device__ inline int dre_lq(int L) { return L + (L & 1); }
 enum { CNT_RAYS = 0, CNT_ISECT, CNT_DEP, CNT_BEAM, CNT_SPLIT, CNT_MERGE, CNT_SCA, CNT_ACT, CNT_HASH, CNT_N, CNT_ACTDEP, CNT_DESC };

@@ -80,7 +80,9 @@ struct dre_engine {
   DBuf<double> pkts;     // ray packets of the current step
   DBuf<unsigned long long> scan_desc; unsigned scan_epoch = 0;   // tile descriptors of the chained scan
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_scan_chained = 1;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_scan_chained = 1, opt_det = 0;
+  // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
+  std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
@@ -480,6 +482,7 @@ DreAccum make_accum(dre_engine* e, const double* prev_rows) {
   A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
   A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
   A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash; A.stage_split = e->opt_stage_split; A.ring_slots = e->opt_ring_slots;
+  A.det = e->opt_det; A.qc = e->opt_det ? e->qc.p : nullptr;
   return A;
 }
 
@@ -515,8 +518,9 @@ int trace_warps(dre_engine* e, size_t* smem) {
   const DreDev& g = e->g;
   int w = std::max(1, std::min(e->opt_warps, 32));
   w = std::min(w, DRE_TRACE_THREADS / 32);
-  while (w > 1 && dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) * e->opt_ctas_per_sm > (size_t)226 * 1024) w--;
-  *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split);
+  const size_t extra = e->opt_det ? dre_det_smem_bytes(g.L) : 0;
+  while (w > 1 && (dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) + extra) * e->opt_ctas_per_sm > (size_t)226 * 1024) w--;
+  *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) + extra;
   DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
   return w;
 }
@@ -538,13 +542,13 @@ void ensure_ftab(dre_engine* e, unsigned nkmask) {
   }
 }
 
-template <int MODE, int KL>
+template <int MODE, int KL, int DET>
 void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
   size_t smem = 0; int warps = 8;
   if (MODE == MODE_DEP) {
     warps = trace_warps(e, &smem);
-    CK(cudaFuncSetAttribute(k_trace<MODE, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  } else smem = (size_t)warps * (8 + 32 * e->g.KLn + 2 + dre_pkt_stride(e->g.L)) * 8;
+    CK(cudaFuncSetAttribute(k_trace<MODE, KL, DET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  } else smem = (size_t)warps * (8 + 32 * e->g.KLn + 2 + dre_pkt_stride(e->g.L)) * 8 + (DET ? dre_det_smem_bytes(e->g.L) : 0);
   const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
   // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance
@@ -556,7 +560,7 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
   CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE, KL><<<ctas, warps * 32, smem, e->st>>>(A, e->pkts.p, pstride, nT, out, e->counter.p, chunk);
+  k_trace<MODE, KL, DET><<<ctas, warps * 32, smem, e->st>>>(A, e->pkts.p, pstride, nT, out, e->counter.p, chunk);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
   e->last_launches++;
@@ -564,11 +568,69 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const 
 
 template <int MODE>
 void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
-  switch (e->g.KLn) {
-    case 1: launch_trace_kl<MODE, 1>(e, A, u, H, W, nT, out); break;
-    case 2: launch_trace_kl<MODE, 2>(e, A, u, H, W, nT, out); break;
-    default: launch_trace_kl<MODE, 4>(e, A, u, H, W, nT, out); break;
+  if (A.det) {
+    switch (e->g.KLn) {
+      case 1: launch_trace_kl<MODE, 1, 1>(e, A, u, H, W, nT, out); break;
+      case 2: launch_trace_kl<MODE, 2, 1>(e, A, u, H, W, nT, out); break;
+      default: launch_trace_kl<MODE, 4, 1>(e, A, u, H, W, nT, out); break;
+    }
+    return;
   }
+  switch (e->g.KLn) {
+    case 1: launch_trace_kl<MODE, 1, 0>(e, A, u, H, W, nT, out); break;
+    case 2: launch_trace_kl<MODE, 2, 0>(e, A, u, H, W, nT, out); break;
+    default: launch_trace_kl<MODE, 4, 0>(e, A, u, H, W, nT, out); break;
+  }
+}
+
+// Deterministic mode (option "deterministic"), start of a list pass.  Bounds of the sums, from the total luminosity
+// Lt(l) of the sources of the pass (every unit of luminosity crosses a cell at most once, over at most sqrt(3) csize):
+//   scaspe element <= Lt, u <= sqrt(3) Lt / (cs csize_min^2), lum_lost <= Lt   (x2 for slack; running maxima, so that
+// what earlier passes left in the accumulators stays on the grid).  Quantum q = 2^(e-52) for a bound <= 2^e: sums stay
+// exact up to 2x the bound; beyond that only bit-reproducibility degrades, not the value.  The price is dynamic range:
+// an element keeps an absolute accuracy of ~sqrt(n) q / 2 after n contributions, i.e. elements below ~1e-10 of the bound
+// of their wavelength no longer meet 1e-5 relative (deeply shadowed cells of an optically thick model).
+void det_prepare(dre_engine* e, int rt_type, int mode) {
+  const DreDev& g = e->g;
+  const int L = g.L, Lq = dre_lq(L), nq = 3 * Lq + 2;
+  const bool src_pass = (rt_type == DRE_RTT_PRECALC_SRC || rt_type == DRE_RTT_DIR_SRC);
+  if ((int)e->det_e.size() != nq) e->det_e.assign(nq, INT_MIN);
+  e->red_d.ensure((size_t)2 * L);
+  std::vector<double> lt(L, 0.0);
+  if (!src_pass || e->S > 0) {
+    e->n_launch++;
+    if (src_pass) k_colsum<<<L, 256, 0, e->st>>>(e->lum_p_src.p, e->S, L, e->red_d.p);
+    else k_colsum<<<L, 256, 0, e->st>>>(e->lumcell.p, g.N, L, e->red_d.p);
+    CK(cudaMemcpyAsync(lt.data(), e->red_d.p, (size_t)L * 8, cudaMemcpyDeviceToHost, e->st));
+    CK(cudaStreamSynchronize(e->st));
+  }
+  const double csmin = g.csize_arr[g.max_lvl];
+  auto bump = [&](int idx, double bound) {
+    if (!(bound > 0) || !std::isfinite(bound)) return;
+    int ex; std::frexp(bound, &ex);          // bound = m 2^ex, m in [0.5, 1)
+    e->det_e[idx] = std::max(e->det_e[idx], ex);
+  };
+  for (int l = 0; l < L; l++) {
+    // scaspe is zero at the start of a scattering iteration (rt_routines.f90:747-756): its grid follows the
+    // luminosity of the iteration instead of the running maximum
+    if (rt_type == DRE_RTT_SCATT && lt[l] > 0) e->det_e[l] = INT_MIN;
+    bump(l, 2.0 * lt[l]);
+    bump(Lq + l, 2.0 * std::sqrt(3.0) * lt[l] / (g.par.cs * csmin * csmin));
+    bump(2 * Lq + l, 2.0 * lt[l]);
+  }
+  bump(3 * Lq, g.par.modelsize * 17179869184.0);   // psel_sum of a source: up to 2^34 rays of at most ~modelsize each
+  e->h_qc.assign(nq, 0.0);
+  for (int i = 0; i < nq; i++) if (e->det_e[i] != INT_MIN) e->h_qc[i] = std::ldexp(1.5, e->det_e[i]);
+  e->qc.upload(e->h_qc.data(), nq, e->st);
+  const size_t NL = (size_t)g.N * L;
+  if (mode == MODE_PRECALC) {
+    (e->n_launch++, k_quantize_cols)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->u_fest.p, NL, L, e->qc.p + Lq, nullptr);
+  } else {
+    const size_t n = e->rows_elems();
+    (e->n_launch++, k_quantize_rows)<<<cdiv(n, 256), 256, 0, e->st>>>(e->acc.p, n, g.ROW, L, g.lamof, e->qc.p);
+    (e->n_launch++, k_quantize_cols)<<<1, 256, 0, e->st>>>(e->lum_lost.p, (size_t)L, L, e->qc.p + 2 * Lq, nullptr);
+  }
+  CK(cudaGetLastError());
 }
 
 // returns the largest number of list entries + tasks alive in one step of the batch
@@ -726,6 +788,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   const int nsrc = build_source_list(e);
   const long long total_units = (long long)nsrc * 48;
   const long long mine = total_units > e->rank ? (total_units - e->rank + e->nranks - 1) / e->nranks : 0;
+  if (e->opt_det) det_prepare(e, rt_type, mode);
   DreAccum A = make_accum(e, e->prev.p);
   // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known
   // in advance.  Start from a quarter of the configured batch, measure list entries per unit, and size the
@@ -909,16 +972,31 @@ int dre_allreduce(dre_engine* e, int rt_type) {
       ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64); break;
     case DRE_RTT_SCATT: {
       // delta trick io_routines.f90:3743-3757 and lum_lost correction :3846-3848
-      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0);
+      const bool det = e->opt_det && e->qc.p && (int)e->h_qc.size() == 3 * dre_lq(g.L) + 2;
+      const double* qc_u = det ? e->qc.p + dre_lq(g.L) : nullptr;
+      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0, qc_u);
       ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64);
-      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1);
+      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1, qc_u);
       std::vector<double> ll(g.L), lp(g.L);
       CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
       CK(cudaMemcpyAsync(lp.data(), e->lum_lost_prev.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
       CK(cudaStreamSynchronize(e->st));
-      for (int l = 0; l < g.L; l++) ll[l] = ll[l] - (e->nranks - 1) / (double)e->nranks * lp[l];
+      std::vector<double> lpq(g.L, 0.0);
+      if (det) {   // exact form of the same correction: sum the per-rank increments over the grid value of lum_lost_prev
+        for (int l = 0; l < g.L; l++) {
+          volatile double c = e->h_qc[2 * dre_lq(g.L) + l], t = lp[l] + c;
+          lpq[l] = t - c;
+          ll[l] = ll[l] - lpq[l];
+        }
+      } else for (int l = 0; l < g.L; l++) ll[l] = ll[l] - (e->nranks - 1) / (double)e->nranks * lp[l];
       CK(cudaMemcpyAsync(e->lum_lost.p, ll.data(), g.L * 8, cudaMemcpyHostToDevice, e->st));
       ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
+      if (det) {
+        CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
+        CK(cudaStreamSynchronize(e->st));
+        for (int l = 0; l < g.L; l++) ll[l] = ll[l] + lpq[l];
+        CK(cudaMemcpyAsync(e->lum_lost.p, ll.data(), g.L * 8, cudaMemcpyHostToDevice, e->st));
+      }
       ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64);
       break;
     }
@@ -1338,10 +1416,21 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "scan_chained") e->opt_scan_chained = value ? 1 : 0;
   else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));
+  else if (s == "deterministic") e->opt_det = value != 0;
   else if (s == "dir_kmax") e->opt_dir_kmax = std::max(2, std::min(10, (int)value));
   else DRE_REQUIRE(false, "dre_set_option: unknown option");
   DRE_CATCH(e)
 }
+int dre_get_quanta(dre_engine* e, double* q_out) {
+  DRE_TRY(e)
+  DRE_REQUIRE(q_out != nullptr, "dre_get_quanta: null output");
+  const int L = e->g.L, Lq = dre_lq(L);
+  const bool have = (int)e->h_qc.size() == 3 * Lq + 2;
+  for (int k = 0; k < 3; k++)
+    for (int l = 0; l < L; l++) q_out[k * L + l] = have ? e->h_qc[k * Lq + l] / 6755399441055744.0 /* 1.5 * 2^52 */ : 0.0;
+  DRE_CATCH(e)
+}
+
 int dre_mark(dre_engine* e, int slot) {
   DRE_TRY(e)
   CK(cudaSetDevice(e->device));

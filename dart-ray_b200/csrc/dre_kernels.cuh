@@ -23,7 +23,11 @@ __host__ __device__ inline int dre_pkt_stride(int L) { return DRE_PKT_HDR + ((L 
 __host__ __device__ inline int dre_stage_len(int ROW, int split) {
   int n = (ROW + split - 1) / split; n += n & 1; return n < 2 ? 2 : n;
 }
-__device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split) {
+// qc != nullptr (deterministic build): the rounding constants are copied behind the per-warp regions.
+__device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* smem, int warp, int lane, WarpSmem& ws, bool need, int split,
+                                              const double* __restrict__ qc = nullptr) {
+  ws.cq = nullptr;
+  const int nwarps = blockDim.x >> 5, nq = 3 * dre_lq(g.L) + 2;
   ws.pending = 0; ws.stage_len = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.run_n = 0; ws.run_total = 0;
   ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   if (!need) {   // precalc: only the look-ahead buffer lives in (dynamic) shared memory
@@ -32,6 +36,11 @@ __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* sm
     ws.pmbar = (unsigned long long*)(ws.pre + 8 + 32 * g.KLn);
     ws.pkt = ws.pre + 8 + 32 * g.KLn + 2;
     if (lane == 0) mbar_init(ws.pmbar);
+    if (qc) {
+      double* cq = reinterpret_cast<double*>(smem) + (size_t)nwarps * (8 + 32 * g.KLn + 2 + dre_pkt_stride(g.L));
+      for (int j = threadIdx.x; j < nq; j += blockDim.x) cq[j] = qc[j];
+      ws.cq = cq;
+    }
     __syncthreads();
     return;
   }
@@ -50,8 +59,14 @@ __device__ __forceinline__ void dre_warp_smem(const DreDev& g, unsigned char* sm
   if (lane == 0) mbar_init(ws.pmbar);
   ws.fphase = 0; ws.fwait = 0;
   if (lane == 0) mbar_init(ws.mbar);
+  if (qc) {
+    double* cq = (double*)(smem + lam_bytes + per * nwarps);
+    for (int j = threadIdx.x; j < nq; j += blockDim.x) cq[j] = qc[j];
+    ws.cq = cq;
+  }
   __syncthreads();
 }
+static inline size_t dre_det_smem_bytes(int L) { return (size_t)(3 * dre_lq(L) + 2) * 8; }
 static inline size_t dre_trace_smem_bytes(int ROW, int L, int warps, int split) {
   const size_t lam_bytes = ((size_t)ROW * 2 + 15) & ~(size_t)15;
   const size_t per = (size_t)(ROW + dre_stage_len(ROW, split) + 2 * L + (L & 1 ? 2 : 0) + 8 + 8 + 32 * ((L + 31) / 32) + 2 + dre_pkt_stride(L)) * 8;
@@ -160,14 +175,14 @@ __global__ void __launch_bounds__(128) k_prep_rays(DreAccum A, DreUnits u, DreLi
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
-template <int MODE, int KL>
+template <int MODE, int KL, int DET>
 __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, const double* __restrict__ pkts, int pstride, int nt,
                         DreList out, int* __restrict__ counter, int chunk) {
   extern __shared__ __align__(128) unsigned char smem[];
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpSmem ws;
-  dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split);
+  dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split, DET ? A.qc : nullptr);
   WarpStats st; memset(&st, 0, sizeof(st));
 #ifdef DRE_TIMING
   st.tprev = clock64();
@@ -223,7 +238,7 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, cons
     DRE_TICK(9);    // setup: packet fields to registers, next packet requested
     RayOut o;
     st.psel = 0; st.npsel = 0;
-    trace_ray<MODE, KL>(g, A, ws, lane, r, I, lost, st, o, lk);
+    trace_ray<MODE, KL, DET>(g, A, ws, lane, r, I, lost, st, o, lk);
     if (MODE == MODE_DEP && lane == 0 && st.npsel > 0) {
       const int sid = (g.rt_type == DRE_RTT_DIR_SRC) ? g.N + g.src_cell[r.nc] : r.nc;
       atomicAdd(&A.psel_sum[sid], st.psel);
@@ -272,7 +287,7 @@ __global__ void k_iobs(DreAccum A, DreIobs q, int* __restrict__ counter) {
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31;
   __shared__ double s_pre[8][8 + 32 * KL];      // look-ahead buffers of the 8 warps of a CTA
-  WarpSmem ws; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
+  WarpSmem ws; ws.cq = nullptr; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.F = ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   ws.pre = s_pre[threadIdx.x >> 5];
   WarpStats st; memset(&st, 0, sizeof(st));
   double lost[KL];
@@ -338,7 +353,7 @@ __global__ void k_build_ftab(int k, double* __restrict__ rows) {
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long npix = 12ll << (2 * k);
   if (w >= npix) return;
-  WarpSmem ws; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
+  WarpSmem ws; ws.cq = nullptr; ws.pending = 0; ws.slot = 0; ws.spos = 0; ws.run_valid = 0; ws.stage = ws.en2 = nullptr; ws.lamof = nullptr; ws.mbar = nullptr; ws.fphase = 0; ws.fwait = 0; ws.runs = nullptr;
   ws.F = rows + (size_t)w * g.ROW;
   unsigned act[DRE_KL];
   for (int q = 0; q < DRE_KL; q++) { const int rem = g.L - 32 * q; act[q] = rem >= 32 ? 0xffffffffu : (rem > 0 ? ((1u << rem) - 1u) : 0u); }
@@ -531,11 +546,28 @@ __global__ void k_u_rows(double* __restrict__ rows, double* __restrict__ u, int 
   if (dir == 0) rows[j] = u[i]; else u[i] = rows[j];
 }
 // rt_mpi delta trick for the scattering u_final (io_routines.f90:3743-3757): rows.u = max(rows.u - u_fest, 0) / + u_fest
-__global__ void k_u_delta(double* __restrict__ rows, const double* __restrict__ u_fest, int N, int L, int ROW, int dir) {
+// qc_u != nullptr (deterministic mode): u_fest is taken on the rounding grid of the pass, as the accumulator rows were at
+// its start, so the difference, its sum over the ranks and the final sum are all exact.
+__global__ void k_u_delta(double* __restrict__ rows, const double* __restrict__ u_fest, int N, int L, int ROW, int dir,
+                          const double* __restrict__ qc_u) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (size_t)N * L) return;
   const size_t j = (i / L) * ROW + (i % L);
-  if (dir == 0) { const double v = rows[j] - u_fest[i]; rows[j] = v < 0 ? 0 : v; } else rows[j] = rows[j] + u_fest[i];
+  const double uf = qc_u ? dre_rq(u_fest[i], qc_u[i % L]) : u_fest[i];
+  if (dir == 0) { const double v = rows[j] - uf; rows[j] = v < 0 ? 0 : v; } else rows[j] = rows[j] + uf;
+}
+// Deterministic mode, start of a pass: what the accumulators already hold is put on the rounding grid of the pass.
+__global__ void k_quantize_rows(double* __restrict__ rows, size_t n, int ROW, int L, const unsigned short* __restrict__ lamof,
+                                const double* __restrict__ qc) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int j = (int)(i % ROW), Lq = dre_lq(L);
+  const double c = (j < Lq) ? qc[Lq + min(j, L - 1)] : qc[lamof[j] >> 3];
+  rows[i] = dre_rq(rows[i], c);
+}
+__global__ void k_quantize_cols(double* __restrict__ a, size_t n, int L, const double* __restrict__ qc_cols, const double* __restrict__ qc_one) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = dre_rq(a[i], qc_cols ? qc_cols[i % L] : qc_one[0]);
 }
 __global__ void k_psel_ratio(const double* __restrict__ s, const long long* __restrict__ n, int m, double* __restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

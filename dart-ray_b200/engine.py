@@ -22,7 +22,7 @@ SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
     "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
-    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
+    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_get_quanta", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
 
@@ -121,6 +121,13 @@ class Engine:
 
     def set_option(self, name, value):
         self._ck(self.l.dre_set_option(self.h, name.encode(), C.c_double(value)))
+
+    def quanta(self):
+        """Rounding grids of the last pass run with option "deterministic": (q_scaspe[L], q_u[L], q_lum_lost[L])."""
+        L = self.scene.lnum
+        q = np.zeros(3 * L)
+        self._ck(self.l.dre_get_quanta(self.h, abi.dptr(q)))
+        return q[:L].copy(), q[L:2 * L].copy(), q[2 * L:].copy()
 
     def mark(self, slot):
         self._ck(self.l.dre_mark(self.h, C.c_int(slot)))

@@ -182,7 +182,16 @@ int dre_pix2vec(dre_engine*, int32_t nside, int32_t npix, const int32_t* ipix,
 /* ---- parity / debug ------------------------------------------------------- */
 int dre_set_record(dre_engine*, int64_t max_records);   /* 0 disables */
 int dre_get_records(dre_engine*, dre_isect* out, int64_t cap, int64_t* n);
+/* Tuning options (none changes a result beyond the summation order) and one mode switch:
+ * "deterministic" = 1: order-independent accumulation.  The north star asks for deposits "written in a fixed order so the
+ * result is deterministic"; the reference itself is not (OpenMP dynamic schedule + atomic updates, rt_routines.f90:994,
+ * 2667-2684).  Instead of fixing the order, every contribution to u_fest / u_final / scaspe / lum_lost / psel_av is first
+ * rounded to a per-wavelength grid q(lambda) = 2^-52 x (a-priori bound of the sum), which makes every fp64 partial sum
+ * exact: the accumulators are bit-identical for any schedule, unit batching, reduction path and number of GPUs.  Cost:
+ * absolute accuracy ~sqrt(n) q / 2 per element after n contributions (dre_get_quanta returns q). */
 int dre_set_option(dre_engine*, const char* name, double value);
+/* quanta of the last deterministic pass: q_out[0..L) scaspe, [L..2L) u_final / u_fest, [2L..3L) lum_lost (0 = no grid) */
+int dre_get_quanta(dre_engine*, double* q_out /*(3L)*/);
 /* evaluates the ray-march kernel's exp() (attenuation, deposit rt_routines.f90:2380-2381) on n host values */
 int dre_eval_exp(dre_engine*, int32_t n, const double* x, double* y);
 /* timing hooks: CUDA events on the engine's stream (print_time io_routines.f90:4268 is wall clock) */

@@ -3,7 +3,10 @@ NCCL) must reproduce the one-GPU solve: event counters and the intersection chec
 bit, every rank ends with the same fields, and they match the one-GPU fields to summation order.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-        --master-port 29511 tests/multigpu_check.py [scene]
+        --master-port 29511 tests/multigpu_check.py [scene] [det]
+
+With `det` both solves run with option "deterministic" (order-independent accumulation) and the N-GPU fields must
+equal the one-GPU fields bit for bit.
 """
 import os
 import sys
@@ -62,6 +65,9 @@ def main():
     dist.broadcast_object_list(obj, src=0)
     eng = engine.Engine(sc, device=lr, rank=rank, nranks=world, nccl_id=obj[0])
     eng.set_option("hash", 1)
+    det = len(sys.argv) > 2 and sys.argv[2] == "det"
+    if det:
+        eng.set_option("deterministic", 1)
     tot = solve(eng, sc, abi)
     st = O.State(sc)
     eng.download_state(st)
@@ -79,6 +85,10 @@ def main():
     if rank == 0:
         one = engine.Engine(sc, device=lr)
         one.set_option("hash", 1)
+        if det:
+            one.set_option("deterministic", 1)
+            one.set_option("warps", 7)          # a different schedule as well
+            one.set_option("batch_units", 1000)
         tot1 = solve(one, sc, abi)
         s1 = O.State(sc)
         one.download_state(s1)
@@ -88,10 +98,11 @@ def main():
         assert sum(hashes) % (1 << 64) == tot1["isect_hash"]
         for name in ("u_fest", "u_final", "lum_lost", "lumcell"):
             a, b = getattr(st, name), getattr(s1, name)
-            assert np.allclose(a, b, rtol=1e-10, atol=1e-300), name
+            assert np.array_equal(a, b) if det else np.allclose(a, b, rtol=1e-10, atol=1e-300), name
         for a, b in zip(st.scaspe_tot + st.scaspe, s1.scaspe_tot + s1.scaspe):
-            assert np.allclose(a, b, rtol=1e-10, atol=1e-300)
-        print(f"multigpu_check ok: world={world} scene={kind} intersections={int(t[0])}")
+            assert np.array_equal(a, b) if det else np.allclose(a, b, rtol=1e-10, atol=1e-300)
+        assert st.u_final.max() > 0 and st.scaspe_tot[0].max() > 0
+        print(f"multigpu_check ok: world={world} scene={kind} det={int(det)} intersections={int(t[0])}")
     dist.barrier()
     dist.destroy_process_group()
 

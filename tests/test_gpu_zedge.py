@@ -136,3 +136,126 @@ def test_three_point_sources_and_walls_on_every_axis(tiny_galaxy):
     sc.wall_coord = (-0.3 * ms, 0.3 * ms, -0.25 * ms, 0.35 * ms, -0.2 * ms, 0.2 * ms)
     assert len(set(sc.cell_src.tolist())) == 3
     run_sequence(sc, record=0, iterations=1)
+
+
+# ---- order-independent accumulation (option "deterministic") ------------------------------------------------------------
+def _full_run(scene, options, iterations=2):
+    """precalc -> direct light -> scattering iterations on the device; returns every accumulator of the path."""
+    from dartray_b200 import abi
+    from oracle import oracle as O
+    eng = _engine(scene, options)
+    st = O.State(scene)
+    has_src = scene.nsrc > 0
+    has_cell = bool(np.any(scene.lumcell))
+    out = {}
+    for rt in ([abi.RTT_PRECALC_CELL] if has_cell else []) + ([abi.RTT_PRECALC_SRC] if has_src else []) + \
+              ([abi.RTT_DIR_CELL] if has_cell else []) + ([abi.RTT_DIR_SRC] if has_src else []):
+        eng.rt_loop(rt, 0)
+    psel = np.zeros(scene.grid.ncell + scene.nsrc)
+    out["psel_av_direct"] = eng.download(abi.ARR_PSEL_AV, psel).copy()
+    tot = np.zeros(scene.lnum)
+    for it in range(1, iterations + 1):
+        if eng.rt_prepare_scatt(it, tot):
+            break
+        eng.rt_loop(abi.RTT_SCATT, it)
+    eng.download_state(st)
+    out["psel_av_scatt"] = eng.download(abi.ARR_PSEL_AV, psel).copy()
+    out.update(u_fest=st.u_fest, u_final=st.u_final, lum_lost=st.lum_lost, lumcell=st.lumcell, tot_rad_en=tot)
+    for l in range(scene.lnum):
+        out[f"scaspe{l}"] = st.scaspe[l]; out[f"scaspe_tot{l}"] = st.scaspe_tot[l]
+    eng.close()
+    return out
+
+
+SCHEDULES = (
+    (("warps", 16), ("chunk", 8)),
+    (("warps", 5), ("chunk", 1), ("ctas_per_sm", 2), ("batch_units", 336)),
+    (("use_bulk", 0), ("warps", 9), ("chunk", 3), ("batch_units", 2000), ("stage_split", 3)),
+)
+
+
+@pytest.mark.parametrize("fixture", ["tiny_galaxy", "tiny_trusti"])
+def test_deterministic_mode_is_bit_reproducible(fixture, request):
+    """With option "deterministic" every contribution is rounded to a per-wavelength grid before it is added, so all
+    partial sums are exact and the accumulators cannot depend on the order of the reductions: three runs that schedule
+    the rays differently (warps per CTA, rays per chunk, unit batches, bulk reductions or per-lane atomics) give the same
+    bits in u_fest, u_final, every scaspe / scaspe_tot plane, lum_lost, lumcell, tot_rad_en and psel_av."""
+    scene = request.getfixturevalue(fixture)
+    runs = [_full_run(scene, (("deterministic", 1),) + s) for s in SCHEDULES]
+    assert runs[0]["u_final"].max() > 0 and runs[0]["scaspe0"].max() > 0
+    for other in runs[1:]:
+        for k, v in runs[0].items():
+            assert np.array_equal(v, other[k]), f"{k} differs between two deterministic runs"
+
+
+DET_K = 2048    # allowance in quanta: ~sqrt(n)/2 for up to n = 1.6e7 contributions per element
+
+
+@pytest.mark.parametrize("fixture", ["tiny_galaxy", "tiny_trusti", "small_magtar"])
+def test_deterministic_mode_parity(fixture, request):
+    """The rounding changes no decision of the ray trees (counters and the intersection checksum stay bit-exact) and every
+    accumulator stays within 1e-5 relative + DET_K quanta of the oracle, the quanta being those the engine reports
+    (2^-52 of the a-priori bound of each wavelength: dre_get_quanta)."""
+    from dartray_b200 import abi
+    from oracle import oracle as O
+    from test_gpu_parity import assert_fields_close
+    scene = request.getfixturevalue(fixture)
+    eng = _engine(scene, (("deterministic", 1),))
+    orc, st = _oracle(scene)
+    gst = O.State(scene)
+    has_src = scene.nsrc > 0
+    has_cell = bool(np.any(scene.lumcell))
+    L = scene.lnum
+    qs_max = np.zeros(L)
+
+    def compare(tag, scatt):
+        nonlocal qs_max
+        eng.download_state(gst)
+        qs, qu, ql = eng.quanta()
+        assert (qu > 0).all() and (qs > 0).all()
+        qs_max = np.maximum(qs_max, qs)
+        assert_fields_close(gst.u_fest, st.u_fest, f"u_fest {tag}", atol=DET_K * qu[None, :])
+        assert_fields_close(gst.u_final, st.u_final, f"u_final {tag}", atol=DET_K * qu[None, :])
+        assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost {tag}", atol=DET_K * ql)
+        for l in range(L):
+            assert_fields_close(gst.scaspe[l], st.scaspe[l], f"scaspe[{l}] {tag}", atol=DET_K * qs[l])
+            if scatt:
+                assert_fields_close(gst.scaspe_tot[l], st.scaspe_tot[l], f"scaspe_tot[{l}] {tag}", atol=DET_K * qs_max[l])
+
+    for rt in ([abi.RTT_PRECALC_CELL] if has_cell else []) + ([abi.RTT_PRECALC_SRC] if has_src else []) + \
+              ([abi.RTT_DIR_CELL] if has_cell else []) + ([abi.RTT_DIR_SRC] if has_src else []):
+        c_o = orc.run_pass(rt, 0, st)
+        c_g = eng.rt_loop(rt, 0)
+        assert_counters_equal(c_g, c_o)
+        compare(f"after pass {rt}", False)
+    tot_g = np.zeros(L)
+    for it in (1, 2):
+        f_o = orc.prepare_scatt(it, st)
+        f_g = eng.rt_prepare_scatt(it, tot_g)
+        assert f_o == f_g
+        # tot_rad_en(l) sums N x npix_hp(l) elements of the direct-light scaspe planes, each on the grid qs_max(l)
+        assert_fields_close(tot_g, st.tot_rad_en, "tot_rad_en",
+                            atol=DET_K * qs_max * np.sqrt(scene.grid.ncell * scene.npix_hp.astype(float)))
+        if f_o:
+            break
+        orc.set_sources(st.lumcell)
+        c_o = orc.run_pass(abi.RTT_SCATT, it, st)
+        c_g = eng.rt_loop(abi.RTT_SCATT, it)
+        assert_counters_equal(c_g, c_o)
+        compare(f"after scattering iteration {it}", True)
+    eng.close()
+
+
+@pytest.mark.parametrize("kind", ["galaxy", "trusti"])
+def test_two_gpus_bit_identical_in_deterministic_mode(kind):
+    """Sums of grid values are exact, so the NCCL all-reduce (rt_mpi) cannot change them either: two GPUs sharing the
+    units give the same bits as one GPU with another schedule."""
+    import os, subprocess, sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29519", os.path.join(root, "tests", "multigpu_check.py"), kind, "det"],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "multigpu_check ok" in r.stdout and "det=1" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
