@@ -259,3 +259,61 @@ def test_two_gpus_bit_identical_in_deterministic_mode(kind):
                         "127.0.0.1", "--master-port", "29519", os.path.join(root, "tests", "multigpu_check.py"), kind, "det"],
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "multigpu_check ok" in r.stdout and "det=1" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_trusti_full_size_properties():
+    """C1 at its full size (21 801 cells, 32 wavelengths, 181-MB accumulator rows), through properties that need no
+    oracle run:
+    (a) a checksum linking the two accumulators: the light scattered out of the rays, sum over cells and HEALPix
+        directions of the direct-light scaspe (= tot_rad_en, rt_routines.f90:690-698), equals ksca_norm x the energy
+        removed from the rays, sum_c u_final dens cs V (deposit :2499-2525, with sum_pix ffn = 1 :2258-2260);
+    (b) linearity, bit for bit: with order-independent accumulation a solve with twice the source luminosity gives
+        exactly twice every accumulator (all operations on the path are linear in the luminosity, x2 is exact in fp64,
+        the rounding grids scale with it) and the same ray trees."""
+    import copy
+    from dartray_b200 import abi, scenes
+    from oracle import oracle as O
+    sc = scenes.trusti_scene()
+    assert sc.grid.ncell == 21801 and sc.lnum == 32
+    sc2 = copy.copy(sc)
+    sc2.lum_p_src = 2.0 * sc.lum_p_src
+    res = []
+    for s in (sc, sc2):
+        eng = _engine(s, (("deterministic", 1),))
+        cnt = [eng.rt_loop(abi.RTT_PRECALC_SRC, 0), eng.rt_loop(abi.RTT_DIR_SRC, 0)]
+        st = O.State(s)
+        eng.download_state(st)
+        u_dir, lost_dir = st.u_final.copy(), st.lum_lost.copy()
+        tot = np.zeros(s.lnum)
+        assert not eng.rt_prepare_scatt(1, tot)
+        cnt.append(eng.rt_loop(abi.RTT_SCATT, 1))
+        eng.download_state(st)
+        res.append((cnt, u_dir, lost_dir, tot, st))
+        eng.close()
+    # (a) in the default mode (the grid of the deterministic mode is too coarse for the far infrared, where 1e-10 of
+    # the luminosity is scattered: DESIGN.md section 4)
+    eng = _engine(sc)
+    eng.rt_loop(abi.RTT_PRECALC_SRC, 0)
+    c_dir = eng.rt_loop(abi.RTT_DIR_SRC, 0)
+    sd = O.State(sc)
+    eng.download_state(sd)
+    tot_d = np.zeros(sc.lnum)
+    eng.rt_prepare_scatt(1, tot_d)
+    eng.close()
+    cs = abi.make_params(sc, abi.RTT_DIR_SRC).cs
+    removed = (sd.u_final * sc.dens_arr * (cs * sc.grid.csize ** 3)[:, None]).sum(axis=0)
+    assert tot_d.min() > 0
+    assert np.allclose(tot_d, sc.ksca_norm * removed, rtol=1e-9, atol=0.0), np.abs(tot_d / (sc.ksca_norm * removed) - 1).max()
+    assert np.all(tot_d + sd.lum_lost < sc.lum_p_src[0])      # scattered + lost light cannot exceed what was emitted
+    # (b)
+    cnt, u_dir, lost_dir, tot, st = res[0]
+    cnt2, u_dir2, lost_dir2, tot2, st2 = res[1]
+    assert_counters_equal(c_dir, cnt[1])                      # the rounding changes no ray tree
+    for a, b in zip(cnt, cnt2):
+        assert_counters_equal(a, b)
+    assert cnt[1].intersections > 500_000 and cnt[2].intersections > cnt[1].intersections
+    assert np.array_equal(u_dir2, 2.0 * u_dir) and np.array_equal(tot2, 2.0 * tot) and np.array_equal(lost_dir2, 2.0 * lost_dir)
+    assert np.array_equal(st2.u_final, 2.0 * st.u_final) and np.array_equal(st2.lumcell, 2.0 * st.lumcell)
+    assert np.array_equal(st2.lum_lost, 2.0 * st.lum_lost)
+    for l in range(sc.lnum):
+        assert np.array_equal(st2.scaspe[l], 2.0 * st.scaspe[l]) and np.array_equal(st2.scaspe_tot[l], 2.0 * st.scaspe_tot[l])
