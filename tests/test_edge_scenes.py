@@ -52,3 +52,28 @@ def test_point_source_host_cell_is_dusty(tiny_galaxy):
     assert sc.nsrc == 1 and sc.src_cell[j] == 0 and sc.grid.cchild[j] == -1
     assert sc.dens_arr[j].min() > 0 and sc.lumcell[j].max() > 0     # Q4 / Q10 run with tau > 0, and the cell emits too
     assert np.all(np.abs(sc.ccoord_p_src[0] - sc.grid.ccoord[j]) < sc.grid.csize[j] / 2)
+
+
+def test_rounding_grid_makes_sums_order_independent():
+    """The arithmetic behind the engine's option "deterministic" (DESIGN.md section 4), in numpy: values rounded to the
+    grid q = 2^(e-52) with rq(v) = (v + C) - C, C = 1.5 * 2^e, add up exactly in fp64 as long as the sum stays below
+    2^53 q, so any order of summation gives the same bits; without the rounding the orders disagree."""
+    rng = np.random.default_rng(5)
+    v = rng.random(200_000) * 10.0 ** rng.uniform(-9, 0, 200_000)        # 9 decades of dynamic range, sum ~ 2e4
+    bound = 2.0 * v.sum()
+    e = int(np.ceil(np.log2(bound)))
+    C = 1.5 * 2.0 ** e
+    q = 2.0 ** (e - 52)
+    r = (v + C) - C
+    assert np.all(np.abs(r - v) <= q / 2) and np.all(r / q == np.round(r / q))      # nearest grid point
+    sums, raw = set(), set()
+    for _ in range(6):
+        p = rng.permutation(len(v))
+        sums.add(float(np.add.reduce(r[p])))          # pairwise
+        sums.add(float(np.cumsum(r[p])[-1]))          # sequential
+        raw.add(float(np.cumsum(v[p])[-1]))
+    assert len(sums) == 1 and len(raw) > 1
+    assert abs(sums.pop() - v.sum()) <= q * np.sqrt(len(v))
+    # scaling the inputs and the bound by a power of two scales the result exactly (the full-size linearity test)
+    r2 = (2.0 * v + 2.0 * C) - 2.0 * C
+    assert np.array_equal(r2, 2.0 * r)
