@@ -243,6 +243,7 @@ int dre_set_grid(dre_engine* e, int32_t N, int32_t max_lvl, const int32_t base[2
   CK(cudaStreamSynchronize(e->st));
   g.cell = e->cells.p;
   e->have_grid = true; e->have_opacity = false; e->have_sources = false;
+  e->det_e.clear(); e->h_qc.clear();   // rounding grids of the deterministic mode belong to one model
   DRE_CATCH(e)
 }
 
@@ -310,6 +311,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   for (double& x : e->per_unit_est) x = 0;
   e->list_budget = 0;
   e->have_opacity = true; e->have_sources = false;
+  e->det_e.clear(); e->h_qc.clear();
   DRE_CATCH(e)
 }
 

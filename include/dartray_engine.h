@@ -188,7 +188,9 @@ int dre_get_records(dre_engine*, dre_isect* out, int64_t cap, int64_t* n);
  * 2667-2684).  Instead of fixing the order, every contribution to u_fest / u_final / scaspe / lum_lost / psel_av is first
  * rounded to a per-wavelength grid q(lambda) = 2^-52 x (a-priori bound of the sum), which makes every fp64 partial sum
  * exact: the accumulators are bit-identical for any schedule, unit batching, reduction path and number of GPUs.  Cost:
- * absolute accuracy ~sqrt(n) q / 2 per element after n contributions (dre_get_quanta returns q). */
+ * absolute accuracy ~sqrt(n) q / 2 per element after n contributions (dre_get_quanta returns q).  The grids are running
+ * maxima over the passes made since dre_set_grid / dre_set_opacity, so the bits are reproducible between runs that make the
+ * same sequence of calls (any schedule, any number of ranks), not between the first and a repeated solve on one engine. */
 int dre_set_option(dre_engine*, const char* name, double value);
 /* quanta of the last deterministic pass: q_out[0..L) scaspe, [L..2L) u_final / u_fest, [2L..3L) lum_lost (0 = no grid) */
 int dre_get_quanta(dre_engine*, double* q_out /*(3L)*/);
