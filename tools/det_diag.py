@@ -1,5 +1,10 @@
+"""Diagnostic (GPU): per accumulator, the largest difference between a solve with option "deterministic" and a default
+solve, relative to the plane maximum and per element — the numbers behind the dynamic-range limit stated in DESIGN.md
+section 4.  Run on the GPU box from the repo root: python tools/det_diag.py"""
 import sys
-sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np
 from dartray_b200 import scenes, abi
 from oracle import oracle as O
