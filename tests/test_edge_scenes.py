@@ -77,3 +77,38 @@ def test_rounding_grid_makes_sums_order_independent():
     # scaling the inputs and the bound by a power of two scales the result exactly (the full-size linearity test)
     r2 = (2.0 * v + 2.0 * C) - 2.0 * C
     assert np.array_equal(r2, 2.0 * r)
+
+
+@pytest.mark.parametrize("fixture", ["tiny_trusti", "small_magtar"])
+def test_oracle_scattered_light_checksum_and_linearity(fixture, request):
+    """Two pins of the oracle that need no second implementation (the same properties are checked on the GPU at the full
+    C1 size, test_gpu_zedge.py::test_trusti_full_size_properties):
+    - cross-formula checksum: the direct light scattered out of the rays (sum over cells and HEALPix directions of scaspe,
+      process_scatt_rad rt_routines.f90:2638-2726 with sum_pix ffn = 1 :2258-2260) equals ksca_norm x the energy removed
+      from them, sum_c u_final dens cs V (deposit :2499-2525) — valid for point sources in dust-free host cells;
+    - linearity: twice the luminosity gives exactly twice the accumulators (one thread: fixed summation order)."""
+    import copy
+    from dartray_b200 import abi
+    from oracle import oracle as O
+    sc = request.getfixturevalue(fixture)
+    assert sc.dens_arr[sc.cell_src[0]].max() == 0
+    out = []
+    for s in (sc, copy.copy(sc)):
+        if out:
+            s.lum_p_src = 2.0 * sc.lum_p_src
+        orc = O.Oracle(s, nthreads=1)
+        st = O.State(s)
+        orc.run_pass(abi.RTT_PRECALC_SRC, 0, st)
+        c = orc.run_pass(abi.RTT_DIR_SRC, 0, st)
+        out.append((c, st))
+    c, st = out[0]
+    cs = abi.make_params(sc, abi.RTT_DIR_SRC).cs
+    removed = (st.u_final * sc.dens_arr * (cs * sc.grid.csize ** 3)[:, None]).sum(axis=0)
+    scattered = np.array([st.scaspe[l][:, :sc.npix_hp[l]].sum() for l in range(sc.lnum)])
+    assert scattered.min() > 0
+    assert np.allclose(scattered, sc.ksca_norm * removed, rtol=1e-10, atol=0.0)
+    c2, st2 = out[1]
+    assert c2.intersections == c.intersections and c2.isect_hash == c.isect_hash
+    assert np.array_equal(st2.u_final, 2.0 * st.u_final) and np.array_equal(st2.lum_lost, 2.0 * st.lum_lost)
+    for l in range(sc.lnum):
+        assert np.array_equal(st2.scaspe[l], 2.0 * st.scaspe[l])
