@@ -11,9 +11,10 @@ dartray_hub.f90:12-67), on synthetic inputs shaped like the reference's example
           u_fest/u_final/scaspe/scaspe_prev/lum_lost and downloads the results
   roofline  algorithmic bytes of the deposit passes / device time of the ray-march kernel launches
   cpu_baseline  the CPU oracle (C++ restatement of the reference path, OpenMP over sources like
-          rt_routines.f90:994) on all host cores, on a bounded sample of scattering iteration 1
+          rt_routines.f90:994) on all host cores: ONE WHOLE SOLVE of the same workload (no sampling)
 
-`--impl reference` times that CPU path alone (the Fortran reference cannot be built in this image).
+`--impl reference` times that CPU path alone, whole solves of the same workload (the Fortran reference
+cannot be built in this image: no Fortran compiler, MPI or HDF5).
 """
 import argparse
 import json
@@ -226,85 +227,32 @@ def solve_host(eng, scene, abi, hs, max_iterations=30):
     return isect, up, down, t_call
 
 
-def sample_pass(scene, abi):
-    """The pass the CPU baseline samples: the one that dominates the solve (direct light of the emitting
-    cells when every leaf emits, else scattering iteration 1)."""
-    if bool(np.any(scene.lumcell)):
-        return abi.RTT_DIR_CELL, 0, "direct light of the emitting cells (rtt_dir_cell)"
-    return abi.RTT_SCATT, 1, "scattering iteration 1 (rtt_scatt)"
-
-
-def cpu_sample(scene, abi, st, target_s=15.0, nthreads=None, K_fixed=None):
-    """Oracle on all host cores: the sampled pass restricted to units with gid % K == 0."""
+def cpu_solve(scene, abi, nthreads=None, max_iterations=30):
+    """The whole solve on the host cores with the CPU oracle: the same call sequence as solve_resident
+    (dartray_main, dartray_hub.f90:12-67).  Returns (intersections, seconds, per-pass list)."""
     from oracle import oracle as O
     nthreads = nthreads or os.cpu_count() or 1
     orc = O.Oracle(scene, nthreads=nthreads)
-    rt, it, what = sample_pass(scene, abi)
-    orc.set_sources(st.lumcell if rt == abi.RTT_SCATT else scene.lumcell)
-
-    def run(K):
-        s2 = O.State(scene)
-        s2.u_fest[...] = st.u_fest; s2.u_final[...] = st.u_final
-        for l in range(scene.lnum):
-            s2.scaspe_prev[l][...] = st.scaspe_prev[l]
-        t0 = time.perf_counter()
-        c = orc.run_pass(rt, it, s2, rank=0, nranks=K)
-        return c, time.perf_counter() - t0
-
-    if K_fixed is not None:
-        c, dt = run(K_fixed)
-        return c, dt, K_fixed, nthreads, what
-    K = 256
-    c, dt = run(K)
-    full_est = dt * K
-    K2 = max(1, int(round(full_est / target_s)))
-    if K2 < K:
-        c, dt = run(K2)
-        K = K2
-    return c, dt, K, nthreads, what
-
-
-def cpu_state_oracle(scene, abi):
-    """State in front of the sampled pass, produced by the oracle itself (reference arm: no GPU)."""
-    from oracle import oracle as O
-    orc = O.Oracle(scene, nthreads=os.cpu_count() or 1)
+    orc.set_option("lock_cell", 1)    # the reference's own update scheme (vectorised when one ray is in the cell)
     st = O.State(scene)
-    rt, it, _ = sample_pass(scene, abi)
     has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
-    if has_cell:
-        orc.run_pass(abi.RTT_PRECALC_CELL, 0, st)
-    if has_src:
-        orc.run_pass(abi.RTT_PRECALC_SRC, 0, st)
-    if rt == abi.RTT_SCATT:
-        if has_cell:
-            orc.run_pass(abi.RTT_DIR_CELL, 0, st)
-        if has_src:
-            orc.run_pass(abi.RTT_DIR_SRC, 0, st)
-        orc.prepare_scatt(1, st)
-    return st
-
-
-def cpu_state_engine(eng, scene, abi):
-    """The same state produced by the engine (our arm: untimed setup of the CPU sample)."""
-    from oracle import oracle as O
-    st = O.State(scene)
-    for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST):
-        eng.zero(a)
-    eng.set_sources(scene.lumcell)
-    rt, it, _ = sample_pass(scene, abi)
-    has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
-    if has_cell:
-        eng.rt_loop(abi.RTT_PRECALC_CELL)
-    if has_src:
-        eng.rt_loop(abi.RTT_PRECALC_SRC)
-    if rt == abi.RTT_SCATT:
-        if has_cell:
-            eng.rt_loop(abi.RTT_DIR_CELL)
-        if has_src:
-            eng.rt_loop(abi.RTT_DIR_SRC)
-        eng.rt_prepare_scatt(1, np.zeros(scene.lnum))
-    eng.download_state(st)
-    return st
+    passes = []
+    t0 = time.perf_counter()
+    seq = ([abi.RTT_PRECALC_CELL] if has_cell else []) + ([abi.RTT_PRECALC_SRC] if has_src else []) + \
+          ([abi.RTT_DIR_CELL] if has_cell else []) + ([abi.RTT_DIR_SRC] if has_src else [])
+    for rt in seq:
+        t1 = time.perf_counter()
+        c = orc.run_pass(rt, 0, st)
+        passes.append((rt, 0, c.intersections, time.perf_counter() - t1))
+    for it in range(1, max_iterations + 1):
+        if orc.prepare_scatt(it, st):
+            break
+        orc.set_sources(st.lumcell)
+        t1 = time.perf_counter()
+        c = orc.run_pass(abi.RTT_SCATT, it, st)
+        passes.append((abi.RTT_SCATT, it, c.intersections, time.perf_counter() - t1))
+    dt = time.perf_counter() - t0
+    return sum(p[2] for p in passes), dt, passes
 
 
 def main():
@@ -313,14 +261,19 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="galaxy")
-    ap.add_argument("--no-also", action="store_true", help="skip the secondary workloads (TRUST-I, MAGTAR)")
+    ap.add_argument("--workload", default="trustI")
+    ap.add_argument("--no-also", action="store_true", help="skip the secondary workloads (galaxy-shaped grid, MAGTAR)")
+    ap.add_argument("--also", default="galaxy,magtar", help="comma-separated secondary workloads")
+    ap.add_argument("--ref-budget-s", type=float, default=150.0, help="reference arm: stop starting new solves after this many seconds")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--option", action="append", default=[], help="engine option name=value")
     args = ap.parse_args()
 
-    os.environ["NCCL_DEBUG"] = os.environ.get("DRE_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout (one JSON line)
+    # NCCL's log goes to stderr so that stdout stays ONE JSON line; the level is left to the caller (the driver counts the
+    # communicator's ranks from the INFO lines)
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -336,22 +289,27 @@ def main():
         if rank != 0:
             return
         ncores = os.cpu_count() or 1
-        t0 = time.perf_counter()
-        st = cpu_state_oracle(scene, abi)
-        setup_s = time.perf_counter() - t0
+        # One step = one WHOLE solve of the same workload on all host cores (no sampling).  The run is bounded in time, not
+        # in work per step: at most `warmup` (capped at 1) untimed and `steps` timed solves, and no new solve is started
+        # once --ref-budget-s seconds have gone by (C1: ~13 s per solve on 16 cores).
+        t_start = time.perf_counter()
+        n_warm = min(1, args.warmup)
+        for _ in range(n_warm):
+            cpu_solve(scene, abi, ncores)
         vals = []
-        K = None
-        for i in range(max(1, args.warmup) + args.steps):   # the first (warm-up) call also calibrates the sample size
-            c, dt, K, nth, what = cpu_sample(scene, abi, st, target_s=10.0, nthreads=ncores, K_fixed=K)
-            if i >= max(1, args.warmup):
-                vals.append((c.intersections, dt))
+        for i in range(max(1, args.steps)):
+            if vals and time.perf_counter() - t_start > args.ref_budget_s:
+                break
+            n, dt, passes = cpu_solve(scene, abi, ncores)
+            vals.append((n, dt))
         n = sum(v[0] for v in vals); t = sum(v[1] for v in vals)
         v = n / t
-        sample = f"{what}, units with id % {K} == 0 ({vals[-1][0]} intersections per step); untimed setup {setup_s:.1f} s"
+        sample = (f"whole solve (precalc + direct + {sum(1 for p in passes if p[0] == abi.RTT_SCATT)} scattering iterations), "
+                  f"{vals[-1][0]} intersections per solve, {len(vals)} timed solves of {t / len(vals):.1f} s after {n_warm} warm-up")
         print(json.dumps({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
-                          "warmup": args.warmup, "ms_per_step": 1e3 * t / max(1, len(vals)), "higher_is_better": True,
+                          "steps_timed": len(vals), "warmup": args.warmup, "ms_per_step": 1e3 * t / len(vals), "higher_is_better": True,
                           "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-                          "cpu_baseline": {"value": v, "unit": unit, "cores": nth, "kind": "port", "sample": sample},
+                          "cpu_baseline": {"value": v, "unit": unit, "cores": ncores, "kind": "port", "sample": sample},
                           "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
@@ -447,17 +405,29 @@ def main():
         return ach
 
     ach = roofline(m)
-    traffic = None
-    try:   # dram__bytes_read.sum + dram__bytes_write.sum of the captured launch (profiles/, ncu --set full)
-        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj["bytes_per_launch"] if args.workload == "galaxy" else None
-    except Exception:
-        tj = None
-    roof = {"bound": "hbm", "kernel": "k_trace<MODE_DEP>", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
-            "algorithmic_bytes_per_step": m["abytes"], "kernel_ms_per_step": m["kms"], "launches_per_step": m["trace_launches"],
-            "per": "GPU (algorithmic bytes of the whole job / n_gpus / slowest rank's kernel time)",
-            "traffic_note": (tj or {}).get("launch") if traffic is not None else None}
+    def traffic_of(workload):
+        """dram__bytes_read.sum + dram__bytes_write.sum of the captured k_trace launch of this workload
+        (profiles/traffic.json, from an `ncu --set full` capture; per launch, like `achieved`)."""
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            ent = tj.get("workloads", {}).get(workload)
+            return (ent["dram_bytes_per_launch"], ent) if ent else (None, None)
+        except Exception:
+            return None, None
+
+    def roof_block(mm, workload):
+        ach_ = roofline(mm)
+        traffic, ent = traffic_of(workload)
+        return {"bound": "hbm", "kernel": "k_trace<MODE_DEP>", "achieved": ach_, "peak": peak, "unit": "GB/s", "frac": ach_ / peak,
+                "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
+                "algorithmic_bytes_per_step": mm["abytes"], "kernel_ms_per_step": mm["kms"], "launches_per_step": mm["trace_launches"],
+                "per": "GPU (algorithmic bytes of the whole job / n_gpus / slowest rank's kernel time)",
+                "traffic_note": (ent or {}).get("launch"),
+                "note": "achieved = ALGORITHMIC bytes (SURVEY 8d: reductions into the accumulator rows count 16 B per element) / device time of "
+                        "the k_trace launches; the rows are reduced in L2 (cp.reduce.async.bulk), so DRAM `traffic` is far below it when "
+                        "the rows fit the 126-MB L2"}
+
+    roof = roof_block(m, args.workload)
     line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(m["launches"]),
@@ -466,20 +436,19 @@ def main():
                            "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
             "rt_mpi_ms_per_step": m["mpi_ms"], "rank_pass_ms_min_max": m["pass_minmax"], "roofline": roof}
 
-    # the other workloads the metric is quoted on (north star: TRUST-I slab and the MAGTAR shell), same engine options
+    # the other workloads the metric is quoted on (north star: galaxy-shaped grid, MAGTAR shell), same engine options
     if not args.no_also:
         also = {}
-        for w in [x for x in ("trustI", "magtar") if x != args.workload]:
+        for w in [x for x in args.also.split(",") if x and x != args.workload]:
             sc2, desc2 = load_scene(w)
             e2 = engine.Engine(sc2, device=local_rank, rank=rank, nranks=world, nccl_id=None if world == 1 else new_id())
             for o in args.option:
                 k, v = o.split("=")
                 e2.set_option(k, float(v))
             m2 = measure(e2, sc2, 2, 1)
-            a2 = roofline(m2)
             also[w] = {"workload": desc2, "value": m2["isect"] / (m2["ms"] * 1e-3), "ms_per_step": m2["ms"],
                        "s_per_wavelength": m2["ms"] * 1e-3 / sc2.lnum, "intersections_per_step": m2["isect"],
-                       "roofline_frac": a2 / peak, "roofline_achieved_gbs": a2, "steps": 2, "warmup": 1}
+                       "rt_mpi_ms_per_step": m2["mpi_ms"], "roofline": roof_block(m2, w), "steps": 2, "warmup": 1}
             e2.close()
         line["also"] = also
 
@@ -488,20 +457,22 @@ def main():
         solve_host(eng, scene, abi, hs)  # warm-up
         barrier()
         t0 = time.perf_counter()
-        n_e2e = 1
+        n_e2e = max(3, min(args.steps, 5))
         for _ in range(n_e2e):
             isect_h, up, down, t_call = solve_host(eng, scene, abi, hs)
         barrier()
         dt = maxr(time.perf_counter() - t0) / n_e2e
         line["e2e"] = {"value": sumr(float(isect_h)) / dt, "unit": unit, "h2d_bytes_per_step": int(up), "d2h_bytes_per_step": int(down),
                        "ms_per_step": dt * 1e3, "ms_in_dre_run_pass": t_call * 1e3,
-                       "ms_host_rt_prepare": (dt - t_call) * 1e3, "timing": "host wall clock around dre_run_pass calls (uploads and downloads inside)"}
+                       "ms_host_rt_prepare": (dt - t_call) * 1e3, "solves_timed": n_e2e,
+                       "timing": "host wall clock around dre_run_pass calls (uploads and downloads inside), mean of the timed solves"}
 
     if rank == 0 and world == 1 and not args.no_cpu:
-        st = cpu_state_engine(eng, scene, abi)      # untimed setup on the GPU; the timed part below is CPU only
-        c, dt, K, nth, what = cpu_sample(scene, abi, st)
-        line["cpu_baseline"] = {"value": c.intersections / dt, "unit": unit, "cores": nth, "kind": "port",
-                                "sample": f"{what}, units with id % {K} == 0: {c.intersections} intersections in {dt:.1f} s"}
+        ncores = os.cpu_count() or 1
+        n_cpu, dt_cpu, passes_cpu = cpu_solve(scene, abi, ncores)     # one whole solve on the host cores, CPU only
+        line["cpu_baseline"] = {"value": n_cpu / dt_cpu, "unit": unit, "cores": ncores, "kind": "port",
+                                "sample": f"one whole solve of the same workload: {n_cpu} intersections in {dt_cpu:.1f} s",
+                                "ms_per_step": dt_cpu * 1e3}
     if rank == 0:
         print(json.dumps(line))
     eng.close()

@@ -783,8 +783,17 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   e->g.rt_type = rt_type;
   ensure_dir_tables(e);
   e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->rec_n.zero(1, e->st);
-  // psel_av_arr(i0, iterations, :) is a fresh slice in every pass (rt_routines.f90:1446, io_routines.f90:3874)
-  { const size_t NS = (size_t)e->g.N + e->S; e->psel_sum.zero(NS, e->st); e->ipsel.zero(NS, e->st); }
+  // psel_av_arr(i0, iterations, :) is ONE slice for the direct-light phase -- rtt_dir_cell writes sid = cell, rtt_dir_src writes
+  // sid = N + src, rt_mpi reduces once after both (rt_routines.f90:1456-1463, dartray_hub.f90:31-34) -- and a fresh slice in
+  // every scattering iteration (expand_psel_av_arr, dartray_hub.f90:453).  A pass therefore clears only the sid range it writes.
+  if (mode == MODE_DEP) {
+    const size_t N0 = (size_t)e->g.N, NS = N0 + e->S;
+    const size_t lo = (rt_type == DRE_RTT_DIR_SRC) ? N0 : 0, hi = (rt_type == DRE_RTT_DIR_CELL) ? N0 : NS;
+    if (hi > lo) {
+      CK(cudaMemsetAsync(e->psel_sum.p + lo, 0, (hi - lo) * sizeof(double), e->st));
+      CK(cudaMemsetAsync(e->ipsel.p + lo, 0, (hi - lo) * sizeof(long long), e->st));
+    }
+  }
   e->last_kernel_ms = 0; e->last_launches = 0; e->launch_mark = e->n_launch;
   CK(cudaEventRecord(e->ev[0], e->st));
   const int nsrc = build_source_list(e);
@@ -845,7 +854,6 @@ int dre_run_pass(dre_engine* e, int rt_type, int iterations, const double* u_fes
     if (scaspe && (rc = dre_upload(e, DRE_ARR_SCASPE, scaspe))) return rc;
     if (scaspe_prev && rt_type == DRE_RTT_SCATT && (rc = dre_upload(e, DRE_ARR_SCASPE_PREV, scaspe_prev))) return rc;
     if (lum_lost && (rc = dre_upload(e, DRE_ARR_LUM_LOST, lum_lost))) return rc;
-    if ((rc = dre_zero(e, DRE_ARR_PSEL_AV))) return rc;
   }
   if ((rc = dre_run_pass_resident(e, rt_type, iterations, out))) return rc;
   if (precalc) {
@@ -854,7 +862,17 @@ int dre_run_pass(dre_engine* e, int rt_type, int iterations, const double* u_fes
     if (u_accum && (rc = dre_download(e, DRE_ARR_U_FINAL, u_accum))) return rc;
     if (scaspe && (rc = dre_download(e, DRE_ARR_SCASPE, (void*)scaspe))) return rc;
     if (lum_lost && (rc = dre_download(e, DRE_ARR_LUM_LOST, lum_lost))) return rc;
-    if (psel_av && (rc = dre_download(e, DRE_ARR_PSEL_AV, psel_av))) return rc;
+    if (psel_av) {   // only the sid range of the pass just run: the other half of the slice belongs to the other direct pass
+      DRE_TRY(e)
+      const size_t N0 = (size_t)e->g.N, NS = N0 + e->S;
+      const size_t lo = (rt_type == DRE_RTT_DIR_SRC) ? N0 : 0, hi = (rt_type == DRE_RTT_DIR_CELL) ? N0 : NS;
+      if (hi > lo) {
+        (e->n_launch++, k_psel_ratio)<<<cdiv(NS, 256), 256, 0, e->st>>>(e->psel_sum.p, e->ipsel.p, (int)NS, e->psel_av.p);
+        CK(cudaMemcpyAsync(psel_av + lo, e->psel_av.p + lo, (hi - lo) * 8, cudaMemcpyDeviceToHost, e->st));
+        CK(cudaStreamSynchronize(e->st));
+      }
+      DRE_CATCH(e)
+    }
   }
   return 0;
 }

@@ -178,6 +178,13 @@ struct Ctx {
   int64_t max_records = 0;
   std::vector<dre_isect> records;
   std::string err;
+  // lock_cell rt_routines.f90:1692-1693 (smooth_grid_routines.f90:191): occupancy counter per cell that selects the
+  // reference's vectorised, non-atomic update when a single ray is inside the cell (:2444, :2497, :2649).  That path can lose
+  // an update when a second ray enters the cell in the middle of it (the reference accepts this), so it is OFF for the parity
+  // checks (every update atomic, exact) and switched ON by the timing legs of bench.py only, so that the CPU baseline runs
+  // the reference's fast path (orc_set_option "lock_cell").
+  int use_lock_cell = 0;
+  mutable std::vector<int> lock_cell;
 };
 
 // set_base smooth_grid_routines.f90:622-649
@@ -235,6 +242,7 @@ struct Th {
   const Ctx* c;
   int rt_type, iterations;
   bool multi;                      // >1 thread: shared accumulators use atomics (lock_cell>1 branch)
+  bool lock1 = false;              // lock_cell(cc) == 1 for the current intersection (only with Ctx::use_lock_cell)
   // accumulators (shared between threads)
   const double* u_fest; double* u_accum; double* const* scaspe; const double* const* scaspe_prev;
   const double* const* scaspe_tot;
@@ -249,6 +257,8 @@ struct Th {
   std::vector<char> iq_a;
   std::vector<int> iq;
   std::vector<double> ray_intensity_dep;
+  // per-thread scratch of deposit / ray_tracing (automatic arrays in the Fortran: no heap traffic in the hot loop)
+  std::vector<double> s_tau, s_exp, s_iav, s_en, s_ri, s_sl;
   int lnum_a, lnum_a_old;
   std::vector<std::vector<double>> ffn_arr_mw, ffn_arr, ads_arr, scaspe_temp_arr;
   std::vector<Ray> high, low, ext;
@@ -260,6 +270,28 @@ struct Th {
   int unit, step, ray_ord;
 };
 
+struct LockGuard {   // lock_cell(cc) += 1 at the top of an intersection (:1692), -= 1 on every way out (:1743-1845)
+  int* p;
+  explicit LockGuard(int* q) : p(q) {
+    if (p) {
+#pragma omp atomic
+      *p += 1;
+    }
+  }
+  ~LockGuard() {
+    if (p) {
+#pragma omp atomic
+      *p -= 1;
+    }
+  }
+};
+inline bool lock_is_one(const Ctx& c, int cc) {   // the test `lock_cell(cc) == 1` at the moment of the update
+  if (!c.use_lock_cell) return false;
+  int lc;
+#pragma omp atomic read
+  lc = c.lock_cell[cc];
+  return lc == 1;
+}
 inline void atomic_add(bool multi, double* p, double v) {
   if (multi) {
 #pragma omp atomic
@@ -413,13 +445,15 @@ void process_scatt_rad(Th& t, int cc, const std::vector<double>& en_sca) {
   double s = 0;
   for (int iw = 0; iw < t.lnum_a; iw++) s += en_sca[iw];
   if (s == 0.) return;
+  t.lock1 = lock_is_one(c, cc);
   for (int iw = 0; iw < t.lnum_a; iw++) {
     int il = t.iq[iw];
     double en_sca_out = en_sca[iw];
     int np = c.npix_arr[il];
     double* row = t.scaspe[il] + (size_t)np * cc;
     const std::vector<double>& f = t.ffn_arr_mw[il];
-    for (int p = 0; p < np; p++) atomic_add(t.multi, &row[p], en_sca_out * f[p]);
+    if (t.lock1) for (int p = 0; p < np; p++) row[p] += en_sca_out * f[p];      // :2649-2656, vectorised
+    else for (int p = 0; p < np; p++) atomic_add(t.multi, &row[p], en_sca_out * f[p]);
     t.cnt.sca_elems += np;
   }
 }
@@ -432,7 +466,7 @@ void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, i
   const int La = t.lnum_a;
   const int L = c.L;
   int npix_beam = 12 * (t.nside * t.nside);
-  std::vector<double> tau_c(La), exp_tau_c(La), i_av(La);
+  double* tau_c = t.s_tau.data(); double* exp_tau_c = t.s_exp.data(); double* i_av = t.s_iav.data();
   for (int k = 0; k < La; k++) tau_c[k] = c.dens_arr[t.iq[k] + (size_t)L * cc] * length;
   for (int k = 0; k < La; k++) exp_tau_c[k] = exp(-tau_c[k]);
   int clvl = c.lvl[nc];
@@ -467,7 +501,8 @@ void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, i
       if (psel > P.rad_lim * P.modelsize) { ray_status = RAS_GONE; return; }
       if ((beam_f / P.bm_par <= beam_i) && !flag_beam) { ray_status = RAS_GO_HIGH; return; }
       if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
-        for (int k = 0; k < La; k++)
+        if (lock_is_one(c, cc)) for (int k = 0; k < La; k++) t.u_accum[t.iq[k] + (size_t)L * cc] += i_av[k] * length / P.cs / vol_f * area_i * beam_i;   // :2444
+        else for (int k = 0; k < La; k++)
           atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
         t.cnt.deposits++; t.cnt.active_lambda += La; t.cnt.active_lambda_dep += La;
       } else { ray_status = RAS_GO_LOW; return; }
@@ -491,10 +526,12 @@ void deposit(Th& t, int cc, std::vector<double>& ray_intensity, double length, i
         ray_status = RAS_GONE;
         return;
       } else if ((beam_f / P.bm_par_max < beam_i) || (t.nside <= 2 * NSIDE_MIN) || flag_beam) {
-        for (int k = 0; k < La; k++)
+        if (lock_is_one(c, cc)) for (int k = 0; k < La; k++) t.u_accum[t.iq[k] + (size_t)L * cc] += i_av[k] * length / P.cs / vol_f * area_i * beam_i;   // :2497
+        else for (int k = 0; k < La; k++)
           atomic_add(t.multi, &t.u_accum[t.iq[k] + (size_t)L * cc], i_av[k] * length / P.cs / vol_f * area_i * beam_i);
         t.cnt.deposits++; t.cnt.active_lambda += La; t.cnt.active_lambda_dep += La;
-        std::vector<double> en_sca(La, 0.0);
+        std::vector<double>& en_sca = t.s_en;
+        for (int k = 0; k < La; k++) en_sca[k] = 0.0;
         if (cc != nc) {
           for (int k = 0; k < La; k++) {
             if (tau_c[k] > TINY) en_sca[k] = ray_intensity[k] * (1.0 - exp_tau_c[k]) * c.ksca_norm[t.iq[k]] * area_i * beam_i;
@@ -577,7 +614,7 @@ bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vecto
   int incvec[3];
   for (int i = 0; i < 3; i++) incvec[i] = std::max(std::min((int)(cproj[i] / GLEPSILON), 1), -1);
   for (int i = 0; i < 3; i++) cproj[i] = 1 / cproj[i];
-  std::vector<double> ray_intensity(L);
+  std::vector<double>& ray_intensity = t.s_ri;
   for (int i = 0; i < L; i++) ray_intensity[i] = src_lum[i] / (4 * PI * c.csize[nc] * c.csize[nc]);
   std::fill(t.iq_a.begin(), t.iq_a.end(), 0);
   set_iq_list(t, ray_intensity, flag_beam);
@@ -587,6 +624,7 @@ bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vecto
   int kint = 0;
   bool ok = true;
   for (;;) {
+    LockGuard lg(c.use_lock_cell ? &c.lock_cell[cc] : nullptr);
     if (dep_pass) set_iq_list(t, ray_intensity, flag_beam);
     double psel, pabs[3];
     calc_psel(t, incvec, psel, pabs, isel, clvl, cc, cproj);
@@ -601,7 +639,7 @@ bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vecto
       for (int k = 0; k < t.lnum_a; k++) ray_intensity[t.iq[k]] = t.ray_intensity_dep[k];
     }
     if (ray_status == RAS_GO_HIGH) {
-      std::vector<double> sl(L);
+      std::vector<double>& sl = t.s_sl;
       for (int i = 0; i < L; i++) sl[i] = ray_intensity[i] * (4 * PI * c.csize[nc] * c.csize[nc]);
       double dpl = (isel_old != 0) ? prev / cproj[isel_old - 1] : 0.;  // Q11: guard cproj(0)
       add_to_high_ray_list(t, dl, al, t.nside, prev, isel_old, dpl, sl, cc, RT_HIGH);
@@ -611,7 +649,7 @@ bool ray_tracing(Th& t, int nc, double al, double dl, int clvl, const std::vecto
       t.ipsel_av++; t.psel_av += psel;
       break;
     } else if (ray_status == RAS_GO_LOW) {
-      std::vector<double> sl(L);
+      std::vector<double>& sl = t.s_sl;
       for (int i = 0; i < L; i++) sl[i] = ray_intensity[i] * (4 * PI * c.csize[nc] * c.csize[nc]);
       add_to_low_ray_list(t, dl, al, t.nside, prev, isel_old, cproj, sl, cc);
       t.cnt.merges++;
@@ -836,6 +874,7 @@ void th_init(Th& t, const Ctx& c, int rt_type, int iterations, bool multi) {
   const int L = c.L;
   t.lum_lost_temp.assign(L, 0.0); t.i_obs_temp.assign(L, 0.0);
   t.iq_a.assign(L, 0); t.iq.clear(); t.ray_intensity_dep.clear();
+  t.s_tau.assign(L, 0.0); t.s_exp.assign(L, 0.0); t.s_iav.assign(L, 0.0); t.s_en.assign(L, 0.0); t.s_ri.assign(L, 0.0); t.s_sl.assign(L, 0.0);
   t.lnum_a = t.lnum_a_old = 0;
   t.ffn_arr_mw.resize(L); t.scaspe_temp_arr.resize(L);
   for (int l = 0; l < L; l++) { t.ffn_arr_mw[l].assign(c.npix_arr[l], 0.0); t.scaspe_temp_arr[l].assign(c.npix_arr[l], 0.0); }
@@ -936,6 +975,10 @@ int orc_set_sources(orc_ctx* o, const double* lumcell, int32_t S, const double* 
 
 int orc_set_params(orc_ctx* o, const dre_params* p) { o->c.par = *p; return 0; }
 int orc_set_record(orc_ctx* o, int64_t n) { o->c.max_records = n; return 0; }
+int orc_set_option(orc_ctx* o, const char* name, double value) {
+  if (!strcmp(name, "lock_cell")) { o->c.use_lock_cell = value != 0; o->c.lock_cell.assign(o->c.N, 0); return 0; }
+  return 1;
+}
 int orc_get_records(orc_ctx* o, dre_isect* out, int64_t cap, int64_t* n) {
   int64_t m = std::min<int64_t>(cap, (int64_t)o->c.records.size());
   if (out && m > 0) memcpy(out, o->c.records.data(), m * sizeof(dre_isect));

@@ -93,6 +93,12 @@ class Oracle:
     def set_record(self, n):
         self.l.orc_set_record(self.h, C.c_int64(n))
 
+    def set_option(self, name, value):
+        """"lock_cell" = 1: the reference's non-atomic vectorised update when one ray is in the cell (rt_routines.f90:2444,
+        2497, 2649).  Timing legs only: it can lose an update, so the parity checks keep it off."""
+        if self.l.orc_set_option(self.h, name.encode(), C.c_double(value)) != 0:
+            raise ValueError(name)
+
     def records(self):
         n = C.c_int64(0)
         self.l.orc_get_records(self.h, None, C.c_int64(0), C.byref(n))

@@ -47,11 +47,22 @@ def assert_counters_equal(c1, c2, keys=("sources", "rays", "intersections", "dep
         assert d1[k] == d2[k], f"counter {k}: engine {d1[k]} oracle {d2[k]}"
 
 
-def run_sequence(scene, record=0, iterations=2, options=()):
+def assert_psel_av(eng, st, scene, where):
+    """psel_av_arr(i0, iterations, :) (rt_routines.f90:1456-1463): the oracle keeps the per-source sums psel_sum / ipsel of the
+    slice, the engine returns the averages; sources without a terminated ray stay 0 on both sides."""
+    from dartray_b200 import abi
+    got = np.zeros(scene.grid.ncell + scene.nsrc)
+    eng.download(abi.ARR_PSEL_AV, got)
+    want = np.where(st.ipsel > 0, st.psel_sum / np.maximum(st.ipsel, 1), 0.0)
+    assert np.array_equal(got != 0, want != 0), f"psel_av {where}: different sources have an average path"
+    assert_fields_close(got, want, f"psel_av {where}")
+
+
+def run_sequence(scene, record=0, iterations=2, options=(), nthreads=8, maps=True):
     """precalc_src -> dir_src -> i_obs_dir_src -> scatt x iterations -> i_obs on both sides, comparing after each pass."""
     from dartray_b200 import abi
     eng = _engine(scene, options)
-    orc, st = _oracle(scene)
+    orc, st = _oracle(scene, nthreads)
     from oracle import oracle as O
     gst = O.State(scene)
     has_src = scene.nsrc > 0
@@ -81,6 +92,8 @@ def run_sequence(scene, record=0, iterations=2, options=()):
         for l in range(scene.lnum):
             assert_fields_close(gst.scaspe[l], st.scaspe[l], f"scaspe[{l}] after pass {rt}")
         assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost after pass {rt}")
+    # one psel_av slice for the direct-light phase: cells from rtt_dir_cell, point sources from rtt_dir_src
+    assert_psel_av(eng, st, scene, "after the direct-light passes")
     # direct-light i_obs
     for rt in ([abi.RTT_I_OBS_DIR_CELL] if has_cell else []) + ([abi.RTT_I_OBS_DIR_SRC] if has_src else []):
         c_o = orc.run_iobs(rt, st)
@@ -88,7 +101,8 @@ def run_sequence(scene, record=0, iterations=2, options=()):
         assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
         assert_fields_close(gst.i_obs, st.i_obs, f"i_obs after pass {rt}")
         assert_fields_close(eng.calc_sed(1.0e4, 0), orc.calc_sed(st, 1.0e4, 0), f"SED (direct light) after pass {rt}")
-        assert_fields_close(eng.make_maps(32, 1.5, 1), orc.make_maps(st, 32, 1.5, 1), f"maps (direct light) after pass {rt}")
+        if maps:
+            assert_fields_close(eng.make_maps(32, 1.5, 1), orc.make_maps(st, 32, 1.5, 1), f"maps (direct light) after pass {rt}")
         if len(scene.ccoord_obs):
             assert_fields_close(gst.i_obs_in, st.i_obs_in, f"i_obs_in after pass {rt}")
     # scattering iterations
@@ -101,6 +115,7 @@ def run_sequence(scene, record=0, iterations=2, options=()):
         if f_o:
             break
         orc.set_sources(st.lumcell)
+        st.psel_sum[...] = 0; st.ipsel[...] = 0      # expand_psel_av_arr (dartray_hub.f90:453): a fresh slice per iteration
         if record:
             eng.set_record(record); orc.set_record(record)
         c_o = orc.run_pass(abi.RTT_SCATT, it, st)
@@ -116,6 +131,7 @@ def run_sequence(scene, record=0, iterations=2, options=()):
             assert_fields_close(gst.scaspe_tot[l], st.scaspe_tot[l], f"scaspe_tot[{l}] after scatt {it}")
         assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost after scatt {it}")
         assert_fields_close(gst.lumcell, st.lumcell, f"lumcell after scatt {it}")
+        assert_psel_av(eng, st, scene, f"after scatt {it}")
     # scattered-light i_obs from scaspe_tot
     it += 1
     orc.prepare_scatt(it, st); eng.rt_prepare_scatt(it, tot_g)
@@ -127,13 +143,13 @@ def run_sequence(scene, record=0, iterations=2, options=()):
     for units in (0, 1, 2):     # N1: calc_sed / sum_i_obs (sed_routines.f90:90-246) in the three i_obs unit systems
         assert_fields_close(eng.calc_sed(1.0e6, units, lam_si), orc.calc_sed(st, 1.0e6, units, lam_si), f"SED units {units}")
     # N2: make_maps / map_projection (visual_routines.f90:59-177, 570-772): external-observer maps of every direction
-    for npx, fac, units in ((40, 1.0, 0), (24, 2.0, 2)):
+    for npx, fac, units in (((40, 1.0, 0), (24, 2.0, 2)) if maps else ()):
         assert_fields_close(eng.make_maps(npx, fac, units, lam_si), orc.make_maps(st, npx, fac, units, lam_si),
                             f"maps {npx} px, size factor {fac}, units {units}")
     if len(scene.ccoord_obs):
         assert_fields_close(gst.i_obs_in, st.i_obs_in, "i_obs_in after rtt_i_obs")
         # N2, internal observers: map_in_projection (visual_routines.f90:917-1182) on HEALPix spheres of nside 8 and 64
-        for kp, units in ((3, 0), (6, 2)):
+        for kp, units in (((3, 0), (6, 2)) if maps else ()):
             assert_fields_close(eng.make_maps_in(kp, units, lam_si), orc.make_maps_in(st, kp, units, lam_si),
                                 f"internal-observer maps kp_maps {kp}, units {units}")
     eng.close()
