@@ -213,7 +213,6 @@ struct DreUnits {
   int* nc;        // [U] source cell
   int* gid;       // [U] global unit id = source_ordinal*48 + sector (record/hash key)
   int* nk;        // [U] log2 of the current nside
-  int* nk_prev;   // [U] nk of the step just executed (k_next runs before the list rebuild)
   int* step;      // [U]
   int* mode;      // [U] 0 done, 1 extract from HIGH, 2 extract from LOW
   int* task_seg;  // [U+1]

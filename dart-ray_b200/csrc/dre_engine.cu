@@ -3,10 +3,12 @@
 // Replaces rt_loop / rt_loop_iobs / rt_mpi of DART-Ray (rt_routines.f90:985-1058, :1470-1603,
 // io_routines.f90:3667-3881).  No CPU fallback: every entry point that computes runs CUDA kernels.
 #include <algorithm>
+#include <chrono>
 #include <dlfcn.h>
 #include "dre_host.h"
 #include "dre_lists.cuh"
 #include "dre_kernels.cuh"
+#include "dre_split.cuh"
 #include "dre_maps.cuh"
 
 namespace {
@@ -71,21 +73,28 @@ struct dre_engine {
   int nsrc_list = 0;
   // record
   long long rec_cap = 0; DBuf<dre_isect> rec; DBuf<unsigned long long> rec_n;
-  // wavefront scratch
+  // wavefront scratch (device-driven resolution step, dre_lists.cuh)
   ListStore H[2], W[2], OUT;
-  DBuf<int> u_nc, u_gid, u_nk, u_nk_prev, u_step, u_mode, u_task_seg;
-  DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, leader, unit_of_ext, ntask, nreco,
-      task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, scan_tmp[3];
+  DBuf<int> u_nc, u_gid, u_nk, u_step, u_mode, u_task_seg;
+  DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, unit_of_ext, ntask, nreco,
+      task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt;
   DBuf<DreTask> tasks;
   DBuf<double> pkts;     // ray packets of the current step
-  DBuf<unsigned long long> scan_desc; unsigned scan_epoch = 0;   // tile descriptors of the chained scan
+  DBuf<DreCtl> ctl; DreCtl* h_ctl = nullptr; int* h_err = nullptr;   // control block of the step and its pinned host mirror
+  DBuf<unsigned long long> scan_desc; int desc_stride = 0;          // tile descriptors of the chained scans (10 job slots)
+  int capH = 0, capW = 0, capT = 0, capU = 0;
+  DBuf<DreEvt> evt; DBuf<int> nev, evoff; int capE = 0;     // events of the rays of a step (dre_split.cuh)
+  // replayable launch sequences of one resolution step (before / after the ray-march kernel), per list parity
+  struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
+  StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_scan_chained = 1, opt_det = 0;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_det = 0;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
+  double est_H[16] = {0}, est_W[16] = {0}, est_T[16] = {0};   // list entries / tasks per unit seen so far, by rt_type
   size_t list_budget = 0;          // bytes the ray lists of a batch may take (half of the memory free after configuration)
   double per_unit_est[16] = {0};   // list entries per unit of the last pass, by rt_type
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
@@ -96,30 +105,29 @@ struct dre_engine {
 
 namespace {
 
-// exclusive scan of n ints into out[0..n] (out[n] = total); recursion over tile sums
-__global__ void k_scan_top(const int* sums, int* scanned) { scanned[0] = 0; scanned[1] = sums[0]; }
-void scan_level(dre_engine* e, const int* in, int* out, int n, int level) {
-  DRE_REQUIRE(level < 3, "scan: input too large");
-  const int nb = cdiv(n, SCAN_TILE);
-  e->scan_tmp[level].ensure((size_t)2 * nb + 8);
-  int* sums = e->scan_tmp[level].p;
-  int* scanned = sums + nb;
-  (e->n_launch++, k_scan_tile)<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, sums, n);
-  if (nb == 1) (e->n_launch++, k_scan_top)<<<1, 1, 0, e->st>>>(sums, scanned);
-  else scan_level(e, sums, scanned, nb, level + 1);
-  (e->n_launch++, k_scan_add)<<<cdiv((size_t)n + 1, 256), 256, 0, e->st>>>(out, scanned, n, nb);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (function, device), shared by every engine of the process
+int g_smem_set[64][3][3][2];
+
+__global__ void k_bump_epoch(DreCtl* c) { c->scan_epoch += 16u; }
+// descriptor regions of the chained scans: 12 job slots x (tiles of the largest input + 1) words; never cleared after
+// the first allocation (epoch-tagged), re-created (zeroed) when they grow
+void ensure_scan_desc(dre_engine* e, int tiles) {
+  if (tiles + 1 <= e->desc_stride) return;
+  const int stride = std::max(64, (int)((tiles + 1) * 1.5));
+  e->scan_desc.release();
+  e->scan_desc.zero((size_t)12 * stride, e->st);
+  e->desc_stride = stride;
 }
-void scan(dre_engine* e, const int* in, int* out, int n) {
-  if (n <= 0) { (e->n_launch++, k_set_int)<<<1, 1, 0, e->st>>>(out, 0); return; }
-  if (n <= SCAN_TILE) { (e->n_launch++, k_scan_small)<<<1, SCAN_THREADS, 0, e->st>>>(in, out, n); return; }
-  if (e->opt_scan_chained) {
-    const int nb = cdiv(n, SCAN_TILE);
-    if ((size_t)nb > e->scan_desc.cap) { e->scan_desc.ensure(nb, 2.0); CK(cudaMemsetAsync(e->scan_desc.p, 0, e->scan_desc.cap * 8, e->st)); }
-    e->scan_epoch = (e->scan_epoch % 0x3fffffffu) + 1u;      // never 0: a cleared word reads as unpublished
-    (e->n_launch++, k_scan_chained)<<<nb, SCAN_THREADS, 0, e->st>>>(in, out, n, e->scan_desc.p, e->scan_epoch);
-    return;
-  }
-  scan_level(e, in, out, n, 0);
+
+// exclusive scan of n ints (n known to the host) into out[0..n] (out[n] = total): job slot 9 of the chained scan
+void scan_host_n(dre_engine* e, const int* in, int* out, int n) {
+  const int nb = std::max(1, cdiv(std::max(n, 1), SCAN_TILE));
+  ensure_scan_desc(e, nb);
+  ScanJobs J; memset(&J, 0, sizeof(J));
+  J.j[0].in = in; J.j[0].out = out; J.j[0].n_ptr = nullptr; J.j[0].n_const = n; J.j[0].slot = 9;
+  CK(cudaMemsetAsync(&e->ctl.p->tickets[9], 0, sizeof(int), e->st));
+  (e->n_launch++, k_scan_jobs)<<<dim3(std::min(nb, 2 * e->sm_count), 1), SCAN_THREADS, 0, e->st>>>(J, e->ctl.p, e->scan_desc.p, e->desc_stride, 9u, 0);
+  (e->n_launch++, k_bump_epoch)<<<1, 1, 0, e->st>>>(e->ctl.p);
 }
 
 // publish the static inputs to the constant bank the kernels read
@@ -180,6 +188,9 @@ int dre_create(dre_engine** out, int device, int rank, int nranks, const void* n
     CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CK(cudaEventCreate(&e->ev[i]));
     e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->counter.zero(4, e->st); e->active.zero(2, e->st);
+    e->ctl.zero(1, e->st);
+    CK(cudaMallocHost((void**)&e->h_ctl, sizeof(DreCtl))); CK(cudaMallocHost((void**)&e->h_err, sizeof(int)));
+    memset(e->h_ctl, 0, sizeof(DreCtl)); *e->h_err = 0;
     e->rec_n.zero(1, e->st);
     if (e->nranks > 1) {
       DRE_REQUIRE(nccl_id128 != nullptr, "dre_create: nranks > 1 needs an NCCL unique id");
@@ -203,6 +214,9 @@ void dre_destroy(dre_engine* e) {
   cudaSetDevice(e->device);
   cudaDeviceSynchronize();
   if (e->comm) g_nccl.CommDestroy(e->comm);
+  for (auto& sm : e->sgraph) for (auto& sg : sm) { if (sg.pre) cudaGraphExecDestroy(sg.pre); if (sg.post) cudaGraphExecDestroy(sg.post); }
+  if (e->h_ctl) cudaFreeHost(e->h_ctl);
+  if (e->h_err) cudaFreeHost(e->h_err);
   for (int i = 0; i < 4; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
   for (int i = 0; i < 8; i++) if (e->marks[i]) cudaEventDestroy(e->marks[i]);
   if (e->st) cudaStreamDestroy(e->st);
@@ -310,6 +324,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   CK(cudaStreamSynchronize(e->st));
   for (double& x : e->per_unit_est) x = 0;
   e->list_budget = 0;
+  e->capH = e->capW = e->capT = 0;     // the luminosity rows of the lists are lnum wide: re-sized by the next pass
   e->have_opacity = true; e->have_sources = false;
   e->det_e.clear(); e->h_qc.clear();
   DRE_CATCH(e)
@@ -480,7 +495,7 @@ int dre_zero(dre_engine* e, int which) {
 namespace {
 
 DreAccum make_accum(dre_engine* e, const double* prev_rows) {
-  DreAccum A;
+  DreAccum A; memset(&A, 0, sizeof(A));
   A.acc = e->acc.p; A.u_fest = e->u_fest.p; A.prev = prev_rows; A.lum_lost = e->lum_lost.p;
   A.psel_sum = e->psel_sum.p; A.ipsel = e->ipsel.p; A.counters = e->counters.p;
   A.rec = e->rec.p; A.rec_cap = e->rec_cap; A.rec_n = e->rec_n.p; A.err = e->errflag.p; A.use_bulk = e->opt_use_bulk; A.want_hash = e->opt_hash; A.stage_split = e->opt_stage_split; A.ring_slots = e->opt_ring_slots;
@@ -510,7 +525,7 @@ int build_source_list(dre_engine* e) {
   e->srcflag.ensure(g.N); e->srcpos.ensure((size_t)g.N + 1); e->srclist.ensure(g.N);
   sync_g(e);
   (e->n_launch++, k_src_flags)<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p);
-  scan(e, e->srcflag.p, e->srcpos.p, g.N);
+  scan_host_n(e, e->srcflag.p, e->srcpos.p, g.N);
   (e->n_launch++, k_src_compact)<<<cdiv(g.N, 256), 256, 0, e->st>>>(e->srcflag.p, e->srcpos.p, g.N, e->srclist.p);
   e->nsrc_list = read_int(e, e->srcpos.p + g.N);
   return e->nsrc_list;
@@ -544,44 +559,71 @@ void ensure_ftab(dre_engine* e, unsigned nkmask) {
   }
 }
 
+// ---- one resolution step of the wavefront = [pre] list extraction, merge, tasks, ray packets -> [trace] the ray-march
+// kernel -> [post] outcome flags, rebuilt lists, define_next_level.  Every kernel reads its counts from device memory
+// (dre_lists.cuh), so the launch sequence is a constant: pre and post are replayed from CUDA graphs, the ray-march kernel
+// is launched between them with CUDA events around it (its device time is the roofline denominator).
 template <int MODE, int KL, int DET>
-void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
+void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreStep& S) {
   size_t smem = 0; int warps = 8;
   if (MODE == MODE_DEP) {
     warps = trace_warps(e, &smem);
-    CK(cudaFuncSetAttribute(k_trace<MODE, KL, DET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int& set = g_smem_set[e->device & 63][MODE][KL == 4 ? 2 : KL - 1][DET];
+    if (set != (int)smem) { CK(cudaFuncSetAttribute(k_trace<MODE, KL, DET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = (int)smem; }
   } else smem = (size_t)warps * (8 + 32 * e->g.KLn + 2 + dre_pkt_stride(e->g.L)) * 8 + (DET ? dre_det_smem_bytes(e->g.L) : 0);
-  const int ctas_max = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
-  const int ctas = std::max(1, std::min(ctas_max, cdiv(nT, warps)));
-  // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance
-  const int chunk = std::max(1, std::min(e->opt_chunk, nT / (ctas * warps * 8)));
-  const int pstride = dre_pkt_stride(e->g.L);
-  e->pkts.ensure((size_t)nT * pstride);
-  e->n_launch++;
-  k_prep_rays<MODE><<<cdiv(nT, 128), 128, 0, e->st>>>(A, u, H, W, e->tasks.p, nT, e->pkts.p, pstride);
-  CK(cudaMemsetAsync(e->counter.p, 0, sizeof(int), e->st));
+  const int ctas = e->sm_count * (MODE == MODE_DEP ? e->opt_ctas_per_sm : 4);
   CK(cudaEventRecord(e->ev[2], e->st));
   e->n_launch++;
-  k_trace<MODE, KL, DET><<<ctas, warps * 32, smem, e->st>>>(A, e->pkts.p, pstride, nT, out, e->counter.p, chunk);
+  k_trace<MODE, KL, DET><<<ctas, warps * 32, smem, e->st>>>(A, S, e->opt_chunk);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
-  e->last_launches++;
+}
+
+// deposit passes as geometry (thread per ray, two passes around a prefix sum) + deposit (warp per ray): dre_split.cuh
+template <int KL, int DET>
+void launch_split_kl(dre_engine* e, const DreAccum& A, const DreStep& S) {
+  size_t smem = 0;
+  const int warps = trace_warps(e, &smem);
+  static_assert(KL == 1 || KL == 2 || KL == 4, "wavelengths per lane");
+  int& set = g_smem_set[e->device & 63][2][KL == 4 ? 2 : KL - 1][DET];   // slot [2]: k_deposit
+  if (set != (int)smem) { CK(cudaFuncSetAttribute(k_deposit<KL, DET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = (int)smem; }
+  ScanJobs J; memset(&J, 0, sizeof(J));
+  J.j[0].in = e->nev.p; J.j[0].out = e->evoff.p; J.j[0].n_ptr = &S.ctl->nT; J.j[0].slot = 10;
+  CK(cudaEventRecord(e->ev[2], e->st));
+  k_geom<0><<<e->sm_count * 8, 128, 0, e->st>>>(A, S, nullptr, e->nev.p, nullptr, 0);
+  k_scan_jobs<<<dim3(e->sm_count, 1), SCAN_THREADS, 0, e->st>>>(J, S.ctl, S.scan_desc, S.desc_stride, 10u, 1);
+  k_geom<1><<<e->sm_count * 8, 128, 0, e->st>>>(A, S, e->evt.p, e->nev.p, e->evoff.p, e->capE);
+  k_deposit<KL, DET><<<e->sm_count * e->opt_ctas_per_sm, warps * 32, smem, e->st>>>(A, S, e->evt.p, e->opt_chunk);
+  CK(cudaEventRecord(e->ev[3], e->st));
+  CK(cudaGetLastError());
+  e->n_launch += 4;
 }
 
 template <int MODE>
-void launch_trace(dre_engine* e, const DreAccum& A, const DreUnits& u, const DreList& H, const DreList& W, int nT, const DreList& out) {
+void launch_trace(dre_engine* e, const DreAccum& A, const DreStep& S) {
+  if (MODE == MODE_DEP && e->opt_split) {
+    const int det = A.det ? 1 : 0;
+    switch (e->g.KLn * 2 + det) {
+      case 2: launch_split_kl<1, 0>(e, A, S); break;
+      case 3: launch_split_kl<1, 1>(e, A, S); break;
+      case 4: launch_split_kl<2, 0>(e, A, S); break;
+      case 5: launch_split_kl<2, 1>(e, A, S); break;
+      default: if (det) launch_split_kl<4, 1>(e, A, S); else launch_split_kl<4, 0>(e, A, S); break;
+    }
+    return;
+  }
   if (A.det) {
     switch (e->g.KLn) {
-      case 1: launch_trace_kl<MODE, 1, 1>(e, A, u, H, W, nT, out); break;
-      case 2: launch_trace_kl<MODE, 2, 1>(e, A, u, H, W, nT, out); break;
-      default: launch_trace_kl<MODE, 4, 1>(e, A, u, H, W, nT, out); break;
+      case 1: launch_trace_kl<MODE, 1, 1>(e, A, S); break;
+      case 2: launch_trace_kl<MODE, 2, 1>(e, A, S); break;
+      default: launch_trace_kl<MODE, 4, 1>(e, A, S); break;
     }
     return;
   }
   switch (e->g.KLn) {
-    case 1: launch_trace_kl<MODE, 1, 0>(e, A, u, H, W, nT, out); break;
-    case 2: launch_trace_kl<MODE, 2, 0>(e, A, u, H, W, nT, out); break;
-    default: launch_trace_kl<MODE, 4, 0>(e, A, u, H, W, nT, out); break;
+    case 1: launch_trace_kl<MODE, 1, 0>(e, A, S); break;
+    case 2: launch_trace_kl<MODE, 2, 0>(e, A, S); break;
+    default: launch_trace_kl<MODE, 4, 0>(e, A, S); break;
   }
 }
 
@@ -635,105 +677,192 @@ void det_prepare(dre_engine* e, int rt_type, int mode) {
   CK(cudaGetLastError());
 }
 
-// returns the largest number of list entries + tasks alive in one step of the batch
-long long run_batch(dre_engine* e, int mode, const DreAccum& A, int unit0, int U) {
-  long long peak = U;
+// Buffers of the wavefront for U units and the given list / task capacities.  `keep_cur` >= 0: the contents of the
+// lists H[keep_cur] / W[keep_cur] (nH / nW entries) survive the growth (a refused step is repeated after it).
+void ensure_step(dre_engine* e, int U, int capH, int capW, int capT, int keep_cur, int nH, int nW) {
+  const int L = e->g.L;
+  if (U > e->capU) {
+    e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
+    e->extcnt.ensure(U); e->ext_seg.ensure((size_t)U + 1); e->reco_cnt.ensure(U);
+    e->keptH.ensure(U); e->keptW.ensure(U); e->newHcnt.ensure(U); e->newWcnt.ensure(U);
+    for (int i = 0; i < 2; i++) { e->H[i].seg.ensure((size_t)U + 1); e->W[i].seg.ensure((size_t)U + 1); }
+    e->capU = (int)std::min<size_t>(e->u_nc.cap, e->reco_cnt.cap);
+  }
+  capH = std::max(capH, e->capH); capW = std::max(capW, e->capW); capT = std::max(capT, e->capT);
+  if (capH > e->capH || capW > e->capW) {
+    for (int i = 0; i < 2; i++) {
+      if (i == keep_cur) { e->H[i].grow_keep(capH, nH, L, e->st); e->W[i].grow_keep(capW, nW, L, e->st); }
+      else { e->H[i].grow_keep(capH, 0, L, e->st); e->W[i].grow_keep(capW, 0, L, e->st); }
+    }
+    e->selH.ensure(capH); e->posH.ensure((size_t)capH + 1); e->selW.ensure(capW); e->posW.ensure((size_t)capW + 1);
+    const size_t nx = (size_t)capH + capW;
+    e->ext.ensure(nx); e->ipx.ensure(nx); e->gone.ensure(nx); e->cand.ensure(3 * nx); e->ncand.ensure(nx); e->nxt.ensure(nx); e->hasprev.ensure(nx);
+    e->unit_of_ext.ensure(nx); e->ntask.ensure(nx); e->nreco.ensure(nx); e->task_off.ensure(nx + 1); e->reco_off.ensure(nx + 1);
+    e->capH = capH; e->capW = capW;
+  }
+  if (capT > e->capT) {
+    e->tasks.ensure(capT); e->OUT.grow_keep(capT, 0, L, e->st);
+    e->fH.ensure(capT); e->fW.ensure(capT); e->posOH.ensure((size_t)capT + 1); e->posOW.ensure((size_t)capT + 1);
+    e->pkts.ensure((size_t)capT * dre_pkt_stride(L));
+    e->nev.ensure(capT); e->evoff.ensure((size_t)capT + 1);
+    e->capT = capT;
+  }
+  if (e->capE < 1024) { e->evt.ensure(1 << 20); e->capE = 1 << 20; }
+  ensure_scan_desc(e, cdiv((size_t)std::max(std::max(e->capH + e->capW, e->capT), std::max(U, e->g.N)) + 1, SCAN_TILE));
+}
+
+DreStep make_step(dre_engine* e, int U) {
+  DreStep S; memset(&S, 0, sizeof(S));
+  for (int i = 0; i < 2; i++) { S.H[i] = e->H[i].view(); S.W[i] = e->W[i].view(); S.H[i].n = S.W[i].n = 0; S.H[i].cap = e->capH; S.W[i].cap = e->capW; }
+  S.OUT = e->OUT.view(); S.OUT.n = 0; S.OUT.cap = e->capT; S.OUT.seg = nullptr;
+  S.u.nc = e->u_nc.p; S.u.gid = e->u_gid.p; S.u.nk = e->u_nk.p; S.u.step = e->u_step.p; S.u.mode = e->u_mode.p; S.u.task_seg = e->u_task_seg.p; S.u.U = 0;   // the unit count lives in DreCtl::U (set by k_seed): a graph serves every batch size
+  (void)U;
+  S.selH = e->selH.p; S.posH = e->posH.p; S.selW = e->selW.p; S.posW = e->posW.p; S.extcnt = e->extcnt.p; S.ext_seg = e->ext_seg.p;
+  S.ext = e->ext.p; S.ipx = e->ipx.p; S.gone = e->gone.p; S.cand = e->cand.p; S.ncand = e->ncand.p; S.nxt = e->nxt.p; S.hasprev = e->hasprev.p;
+  S.unit_of_ext = e->unit_of_ext.p; S.ntask = e->ntask.p; S.nreco = e->nreco.p; S.task_off = e->task_off.p; S.reco_off = e->reco_off.p;
+  S.reco_cnt = e->reco_cnt.p; S.keptH = e->keptH.p; S.keptW = e->keptW.p; S.newHcnt = e->newHcnt.p; S.newWcnt = e->newWcnt.p;
+  S.fH = e->fH.p; S.fW = e->fW.p; S.posOH = e->posOH.p; S.posOW = e->posOW.p; S.tasks = e->tasks.p; S.pkts = e->pkts.p;
+  S.pstride = dre_pkt_stride(e->g.L); S.capH = e->capH; S.capW = e->capW; S.capT = e->capT; S.ctl = e->ctl.p;
+  S.scan_desc = e->scan_desc.p; S.desc_stride = e->desc_stride; S.err = e->errflag.p; S.steps = e->counters.p + CNT_N; S.kmax = e->g.dir_kmax;
+  return S;
+}
+
+ScanJobs scan_jobs(const int* in0, int* out0, const int* n0, int nc0, int slot0, const int* in1, int* out1, const int* n1, int nc1, int slot1,
+                   int* total0 = nullptr) {
+  ScanJobs J; memset(&J, 0, sizeof(J));
+  J.j[0].total_out = total0;
+  J.j[0].in = in0; J.j[0].out = out0; J.j[0].n_ptr = n0; J.j[0].n_const = nc0; J.j[0].slot = slot0;
+  J.j[1].in = in1; J.j[1].out = out1; J.j[1].n_ptr = n1; J.j[1].n_const = nc1; J.j[1].slot = slot1;
+  return J;
+}
+
+// launches of a step in front of the ray-march kernel; returns their number
+template <int MODE>
+int enqueue_pre(dre_engine* e, const DreAccum& A, const DreStep& S, int cur, cudaStream_t st) {
+  const int G = e->sm_count * 2, Gs = e->sm_count;
+  const int* Un = &S.ctl->U;
+  k_step_select<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.selH, S.posH, &S.ctl->nH, 0, 0, S.selW, S.posW, &S.ctl->nW, 0, 1), S.ctl, S.scan_desc, S.desc_stride, 0u, 0);
+  k_step_unit_ext<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_scan_jobs<<<dim3(Gs, 1), SCAN_THREADS, 0, st>>>(scan_jobs(S.extcnt, S.ext_seg, Un, 0, 2, nullptr, nullptr, nullptr, 0, 0, &S.ctl->nExt), S.ctl, S.scan_desc, S.desc_stride, 2u, 0);
+  k_step_fill_ext<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_step_cand<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_step_resolve<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.ntask, S.task_off, &S.ctl->nExt, 0, 3, S.nreco, S.reco_off, &S.ctl->nExt, 0, 4), S.ctl, S.scan_desc, S.desc_stride, 3u, 0);
+  k_step_tasks<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_prep_rays<MODE><<<e->sm_count * 8, 128, 0, st>>>(A, S, cur);
+  return 10;
+}
+// launches of a step behind the ray-march kernel, ending with the copy of the control block to the host
+int enqueue_post(dre_engine* e, const DreStep& S, int cur, cudaStream_t st) {
+  const int G = e->sm_count * 2, Gs = e->sm_count;
+  const int* Un = &S.ctl->U;
+  k_step_out_flags<<<G, STEP_THREADS, 0, st>>>(S);
+  k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.fH, S.posOH, &S.ctl->nT, 0, 5, S.fW, S.posOW, &S.ctl->nT, 0, 6), S.ctl, S.scan_desc, S.desc_stride, 5u, 1);
+  k_step_unit_new<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.newHcnt, S.H[1 - cur].seg, Un, 0, 7, S.newWcnt, S.W[1 - cur].seg, Un, 0, 8), S.ctl, S.scan_desc, S.desc_stride, 7u, 1);
+  k_step_build<<<e->sm_count * 4, STEP_THREADS, 0, st>>>(S, cur, e->g.L);
+  k_step_next<<<G, STEP_THREADS, 0, st>>>(S, cur);
+  CK(cudaMemcpyAsync(e->h_ctl, S.ctl, sizeof(DreCtl), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(e->h_err, S.err, sizeof(int), cudaMemcpyDeviceToHost, st));
+  return 6;
+}
+
+// the two replayable halves of a step for list parity `cur`; re-captured when a pointer, a capacity or an option changed
+template <int MODE>
+void step_graphs(dre_engine* e, const DreAccum& A, const DreStep& S, int cur) {
+  dre_engine::StepGraph& sg = e->sgraph[MODE == MODE_DEP ? 1 : 0][cur];
+  // the key lists every value a captured launch freezes (field by field: struct padding is not comparable)
+  std::vector<unsigned char> key;
+  auto kp = [&key](const auto& v) { const unsigned char* q = reinterpret_cast<const unsigned char*>(&v); key.insert(key.end(), q, q + sizeof(v)); };
+  auto kl = [&kp](const DreList& l) { kp(l.unit); kp(l.dir_ipix); kp(l.meta); kp(l.cc_old); kp(l.dplane); kp(l.prev); kp(l.lum); kp(l.seg); kp(l.cap); };
+  kp(A.acc); kp(A.u_fest); kp(A.prev); kp(A.lum_lost); kp(A.psel_sum); kp(A.ipsel); kp(A.counters); kp(A.rec); kp(A.rec_cap); kp(A.rec_n);
+  kp(A.err); kp(A.stage_split); kp(A.want_hash); kp(A.ring_slots); kp(A.use_bulk); kp(A.det); kp(A.qc);
+  for (int i = 0; i < 2; i++) { kl(S.H[i]); kl(S.W[i]); }
+  kl(S.OUT);
+  kp(S.u.nc); kp(S.u.gid); kp(S.u.nk); kp(S.u.step); kp(S.u.mode); kp(S.u.task_seg);
+  kp(S.selH); kp(S.posH); kp(S.selW); kp(S.posW); kp(S.extcnt); kp(S.ext_seg); kp(S.ext); kp(S.ipx); kp(S.gone); kp(S.cand); kp(S.ncand);
+  kp(S.nxt); kp(S.hasprev); kp(S.unit_of_ext); kp(S.ntask); kp(S.nreco); kp(S.task_off); kp(S.reco_off); kp(S.reco_cnt); kp(S.keptH);
+  kp(S.keptW); kp(S.newHcnt); kp(S.newWcnt); kp(S.fH); kp(S.fW); kp(S.posOH); kp(S.posOW); kp(S.tasks); kp(S.pkts); kp(S.pstride);
+  kp(S.capH); kp(S.capW); kp(S.capT); kp(S.ctl); kp(S.scan_desc); kp(S.desc_stride); kp(S.err); kp(S.steps); kp(S.kmax);
+  const int mode = MODE, L = e->g.L, smc = e->sm_count;
+  kp(mode); kp(L); kp(smc);
+  if (sg.pre && sg.key == key) return;
+  if (sg.pre) { cudaGraphExecDestroy(sg.pre); sg.pre = nullptr; }
+  if (sg.post) { cudaGraphExecDestroy(sg.post); sg.post = nullptr; }
+  cudaGraph_t gr = nullptr;
+  CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
+  enqueue_pre<MODE>(e, A, S, cur, e->st);
+  CK(cudaStreamEndCapture(e->st, &gr));
+  CK(cudaGraphInstantiate(&sg.pre, gr, 0)); CK(cudaGraphDestroy(gr));
+  CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
+  enqueue_post(e, S, cur, e->st);
+  CK(cudaStreamEndCapture(e->st, &gr));
+  CK(cudaGraphInstantiate(&sg.post, gr, 0)); CK(cudaGraphDestroy(gr));
+  sg.key = key;
+}
+
+struct BatchStats { long long peak = 0; int maxH = 0, maxW = 0, maxT = 0; };
+
+// one batch of units through all its resolution steps (main_dir_loop rt_routines.f90:1366-1442 for every unit at once)
+template <int MODE>
+BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0, int capW0, int capT0) {
+  BatchStats bs; bs.peak = U;
   const DreDev& g = e->g;
   unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
-  const int L = g.L;
-  e->u_nc.ensure(U); e->u_gid.ensure(U); e->u_nk.ensure(U); e->u_nk_prev.ensure(U); e->u_step.ensure(U); e->u_mode.ensure(U); e->u_task_seg.ensure((size_t)U + 1);
-  DreUnits u; u.nc = e->u_nc.p; u.gid = e->u_gid.p; u.nk = e->u_nk.p; u.nk_prev = e->u_nk_prev.p; u.step = e->u_step.p; u.mode = e->u_mode.p;
-  u.task_seg = e->u_task_seg.p; u.U = U;
-  for (int i = 0; i < 2; i++) { e->H[i].ensure(U, L, U); e->W[i].ensure(64, L, U); }
-  int cur = 0;
-  e->H[0].n = U; e->W[0].n = 0;
-  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->H[0].view(), e->W[0].view(), e->srclist.p, unit0, e->nranks, e->rank);
-  e->extcnt.ensure(U); e->ext_seg.ensure((size_t)U + 1); e->reco_cnt.ensure(U);
-  e->keptH.ensure(U); e->keptW.ensure(U); e->newHcnt.ensure(U); e->newWcnt.ensure(U);
-  const int ub = cdiv(U, 256);
+  ensure_step(e, U, std::max(capH0, U), std::max(capW0, 64), std::max(capT0, 64), -1, 0, 0);
+  DreStep S = make_step(e, U);
+  int cur = 0, nH = U, nW = 0;
+  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(S, U, e->srclist.p, unit0, e->nranks, e->rank);
+  static const int verbose = getenv("DRE_VERBOSE") ? atoi(getenv("DRE_VERBOSE")) : 0;
   for (;;) {
-    DreList Hc = e->H[cur].view(), Wc = e->W[cur].view();
-    const int nH = Hc.n, nW = Wc.n;
-    (e->n_launch++, k_plan)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg);
-    if (nH > 0) {
-      e->selH.ensure(nH); e->posH.ensure((size_t)nH + 1);
-      (e->n_launch++, k_select)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p);
-      scan(e, e->selH.p, e->posH.p, nH);
+    const auto t_0 = std::chrono::steady_clock::now();
+    if (MODE == MODE_DEP) ensure_ftab(e, nkmask);
+    if (e->opt_graphs) {
+      step_graphs<MODE>(e, A, S, cur);
+      CK(cudaGraphLaunch(e->sgraph[MODE == MODE_DEP ? 1 : 0][cur].pre, e->st));
+      launch_trace<MODE>(e, A, S);
+      CK(cudaGraphLaunch(e->sgraph[MODE == MODE_DEP ? 1 : 0][cur].post, e->st));
+      e->n_launch += 16;
+    } else {
+      e->n_launch += enqueue_pre<MODE>(e, A, S, cur, e->st);
+      launch_trace<MODE>(e, A, S);
+      e->n_launch += enqueue_post(e, S, cur, e->st);
     }
-    if (nW > 0) {
-      e->selW.ensure(nW); e->posW.ensure((size_t)nW + 1);
-      (e->n_launch++, k_select)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p);
-      scan(e, e->selW.p, e->posW.p, nW);
-    }
-    (e->n_launch++, k_unit_ext)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->extcnt.p);
-    scan(e, e->extcnt.p, e->ext_seg.p, U);
-    const int nExt = read_int(e, e->ext_seg.p + U);
-    int nT = 0;
-    if (nExt > 0) {
-      e->ext.ensure(nExt); e->ipx.ensure(nExt); e->gone.ensure(nExt); e->cand.ensure((size_t)3 * nExt); e->ncand.ensure(nExt); e->nxt.ensure(nExt); e->hasprev.ensure(nExt);
-      e->leader.ensure(nExt); e->unit_of_ext.ensure(nExt); e->ntask.ensure(nExt); e->nreco.ensure(nExt);
-      e->task_off.ensure((size_t)nExt + 1); e->reco_off.ensure((size_t)nExt + 1);
-      const int xb = cdiv(nExt, 256);
-      if (nH > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hc, u, 1, e->selH.p, e->posH.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p, e->hasprev.p);
-      if (nW > 0) (e->n_launch++, k_fill_ext)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wc, u, 2, e->selW.p, e->posW.p, e->ext_seg.p, e->ext.p, e->ipx.p, e->gone.p, e->hasprev.p);
-      (e->n_launch++, k_unit_of_ext)<<<ub, 256, 0, e->st>>>(u, e->ext_seg.p, e->unit_of_ext.p);
-      (e->n_launch++, k_cand)<<<xb, 256, 0, e->st>>>(Wc, u, e->ext_seg.p, e->ext.p, e->unit_of_ext.p, e->ipx.p, nExt, e->cand.p, e->ncand.p, e->nxt.p, e->hasprev.p);
-      (e->n_launch++, k_resolve)<<<xb, 256, 0, e->st>>>(u, e->unit_of_ext.p, nExt, e->cand.p, e->ncand.p, e->nxt.p, e->hasprev.p, e->gone.p, e->leader.p);
-      (e->n_launch++, k_count)<<<xb, 256, 0, e->st>>>(Hc, u, e->ext_seg.p, e->ext.p, nExt, e->unit_of_ext.p, e->ncand.p, e->leader.p, e->ntask.p, e->nreco.p);
-      scan(e, e->ntask.p, e->task_off.p, nExt);
-      scan(e, e->nreco.p, e->reco_off.p, nExt);
-      (e->n_launch++, k_unit_tasks)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(u, e->ext_seg.p, e->task_off.p, e->reco_off.p, e->reco_cnt.p);
-      nT = read_int(e, e->task_off.p + nExt);
-      if (nT > 0) {
-        e->tasks.ensure(nT); e->OUT.ensure(nT, L, 1); e->OUT.n = nT;
-        e->fH.ensure(nT); e->fW.ensure(nT); e->posOH.ensure((size_t)nT + 1); e->posOW.ensure((size_t)nT + 1);
-        (e->n_launch++, k_emit_tasks)<<<xb, 256, 0, e->st>>>(u, e->ext.p, nExt, e->unit_of_ext.p, e->cand.p, e->ntask.p, e->task_off.p, e->tasks.p);
-        DreList out = e->OUT.view();
-        if (mode == MODE_DEP) ensure_ftab(e, nkmask);
-        if (mode == MODE_PRECALC) launch_trace<MODE_PRECALC>(e, A, u, Hc, Wc, nT, out);
-        else launch_trace<MODE_DEP>(e, A, u, Hc, Wc, nT, out);
-        (e->n_launch++, k_out_flags)<<<cdiv(nT, 256), 256, 0, e->st>>>(out, nT, e->fH.p, e->fW.p);
-        scan(e, e->fH.p, e->posOH.p, nT);
-        scan(e, e->fW.p, e->posOW.p, nT);
-      }
-    }
-    const int nx = 1 - cur;
-    (e->n_launch++, k_unit_new)<<<ub, 256, 0, e->st>>>(u, Hc.seg, Wc.seg, e->posH.p, e->posW.p, nH, nW, e->reco_cnt.p, e->posOH.p, e->posOW.p,
-                                      nExt > 0 ? 1 : 0, nT > 0 ? 1 : 0, e->keptH.p, e->keptW.p, e->newHcnt.p, e->newWcnt.p);
-    scan(e, e->newHcnt.p, e->H[nx].seg.p, U);
-    scan(e, e->newWcnt.p, e->W[nx].seg.p, U);
-    // define_next_level only needs the new segment offsets: run it now and read the list sizes, the number of
-    // unfinished units, their nside mask and the error flag with ONE synchronisation
-    CK(cudaMemsetAsync(e->active.p, 0, 2 * sizeof(int), e->st));
-    (e->n_launch++, k_next)<<<ub, 256, 0, e->st>>>(u, e->H[nx].seg.p, e->W[nx].seg.p, e->active.p, e->errflag.p, g.dir_kmax, e->counters.p + CNT_N);
-    int tot2[2], hv[2], hmask = 0;
-    CK(cudaMemcpyAsync(&tot2[0], e->H[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&tot2[1], e->W[nx].seg.p + U, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&hv[0], e->active.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&hmask, e->active.p + 1, sizeof(int), cudaMemcpyDeviceToHost, e->st));
-    CK(cudaMemcpyAsync(&hv[1], e->errflag.p, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    const auto t_1 = std::chrono::steady_clock::now();
     CK(cudaStreamSynchronize(e->st));
     CK(cudaGetLastError());
-    if (nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; }
-    const int nH2 = tot2[0], nW2 = tot2[1];
-    peak = std::max(peak, (long long)nH + nW + nT + nH2 + nW2);
-    if (hv[1] != 0) throw DreError{err_text(hv[1])};
-    // the seg arrays were just written: grow the payload arrays only (seg is sized U+1 already)
-    e->H[nx].ensure(std::max(nH2, 1), L, U); e->W[nx].ensure(std::max(nW2, 1), L, U);
-    e->H[nx].n = nH2; e->W[nx].n = nW2;
-    DreList Hn = e->H[nx].view(), Wn = e->W[nx].view();
-    if (nH > 0) (e->n_launch++, k_build_kept)<<<cdiv(nH, 256), 256, 0, e->st>>>(Hn, Hc, e->selH.p, e->posH.p, L);
-    if (nW > 0) (e->n_launch++, k_build_kept)<<<cdiv(nW, 256), 256, 0, e->st>>>(Wn, Wc, e->selW.p, e->posW.p, L);
-    if (nExt > 0) (e->n_launch++, k_build_reco)<<<cdiv(nExt, 256), 256, 0, e->st>>>(Hn, Wc, u, e->ext.p, nExt, e->unit_of_ext.p, e->ext_seg.p, e->cand.p,
-                                                                 e->nreco.p, e->reco_off.p, e->keptH.p, L);
-    if (nT > 0) (e->n_launch++, k_build_out)<<<cdiv(nT, 256), 256, 0, e->st>>>(Hn, Wn, e->OUT.view(), nT, u, e->tasks.p, e->posOH.p, e->posOW.p,
-                                                             e->keptH.p, e->keptW.p, e->reco_cnt.p, L);
-    cur = nx;
-    if (hv[1] != 0) throw DreError{err_text(hv[1])};
-    if (hv[0] == 0) break;
-    nkmask = (unsigned)hmask;
+    const DreCtl c = *e->h_ctl;
+    if (verbose >= 2) {
+      const auto t_2 = std::chrono::steady_clock::now();
+      float kms = 0; if (c.nT > 0) cudaEventElapsedTime(&kms, e->ev[2], e->ev[3]);
+      fprintf(stderr, "[dre step] rt %d U %d nH %d nW %d nExt %d nT %d -> nH2 %d nW2 %d active %d abort %d | enqueue %.0f us, wait %.0f us, march %.0f us\n",
+              e->g.rt_type, U, c.nH, c.nW, c.nExt, c.nT, c.nH2, c.nW2, c.active, c.abort,
+              std::chrono::duration<double, std::micro>(t_1 - t_0).count(), std::chrono::duration<double, std::micro>(t_2 - t_1).count(), kms * 1e3);
+    }
+    if (*e->h_err != 0) throw DreError{err_text(*e->h_err)};
+    if (c.abort) {          // a buffer was too small: the step changed nothing; grow and repeat it
+      const int nh = std::max(c.needH, c.nH), nw = std::max(c.needW, c.nW);
+      if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] step refused: need H %d W %d T %d E %d (have %d %d %d %d)\n", c.needH, c.needW, c.needT, c.needE, e->capH, e->capW, e->capT, e->capE);
+      ensure_step(e, U, nh > e->capH ? (int)std::min<long long>(2147483000ll, (long long)nh * 3 / 2) : e->capH,
+                  nw > e->capW ? (int)std::min<long long>(2147483000ll, (long long)nw * 3 / 2) : e->capW,
+                  c.needT > e->capT ? (int)std::min<long long>(2147483000ll, (long long)c.needT * 3 / 2) : e->capT, cur, c.nH, c.nW);
+      if (c.needE > e->capE) {
+        const size_t want = (size_t)std::min<long long>(2147483000ll, (long long)c.needE * 3 / 2);
+        e->evt.release(); e->evt.ensure(want, 1.0); e->capE = (int)want;
+      }
+      S = make_step(e, U);
+      continue;
+    }
+    if (c.nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; e->last_launches++; }
+    bs.peak = std::max(bs.peak, (long long)nH + nW + c.nT + c.nH2 + c.nW2);
+    bs.maxH = std::max(bs.maxH, std::max(c.needH, c.nH2)); bs.maxW = std::max(bs.maxW, std::max(c.needW, c.nW2)); bs.maxT = std::max(bs.maxT, c.nT);
+    nH = c.nH2; nW = c.nW2; cur ^= 1;
+    if (c.active == 0) break;
+    nkmask = (unsigned)c.nkmask;
   }
-  return peak;
+  (void)g;
+  return bs;
 }
 
 void fill_counters(dre_engine* e, dre_counters* out, float pass_ms) {
@@ -801,30 +930,35 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   const long long mine = total_units > e->rank ? (total_units - e->rank + e->nranks - 1) / e->nranks : 0;
   if (e->opt_det) det_prepare(e, rt_type, mode);
   DreAccum A = make_accum(e, e->prev.p);
-  // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known
-  // in advance.  Start from a quarter of the configured batch, measure list entries per unit, and size the
-  // following batches so that the lists stay within a third of the free device memory.
+  // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known in advance.
+  // The wavefront buffers hold `cap` entries per list (HIGH and LOW double-buffered, outcomes, tasks, packets, index arrays);
+  // cap comes from the entries per unit seen so far (high-water mark per rt_type, kept across passes) and is bounded by
+  // half of the memory left after configuration.  A step that would overflow is refused on the device and repeated after
+  // the buffers have grown (run_batch_mode), so an estimate that is too low costs time, not correctness.
   if (e->list_budget == 0) {     // once per configuration: cudaMemGetInfo costs ~10 ms, and the list buffers are kept afterwards
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
     e->list_budget = free_b / 2;
   }
-  const double bytes_per_entry = 3.0 * (48.0 + 8.0 * e->g.L) * 1.25 + 128.0 + 8.0 * (22 + e->g.L) * 1.25;   // H/W double buffers + OUT + index arrays, DBuf slack
-  const double max_entries = std::max(1.0e6, (double)e->list_budget / bytes_per_entry);
-  // entries per unit seen in the previous pass of this type (same scene): lets a warm engine start with full batches
-  double& est = e->per_unit_est[rt_type % 16];
+  const int L = e->g.L;
+  const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0);
+  const double max_cap = std::min(2.0e9, std::max(1.0e6, (double)e->list_budget / bytes_per_cap));
+  double& est = e->per_unit_est[rt_type % 16];   // max over steps of the per-list need / units
   double per_unit = 0;
-  long long U_next = est > 0 ? (long long)(max_entries / (1.5 * est))
-                             : std::max<long long>(e->opt_batch_units / 4, 3072);
+  long long U_next = est > 0 ? (long long)(max_cap / (1.5 * est)) : std::max<long long>(e->opt_batch_units / 4, 3072);
   U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   for (long long u0 = 0; u0 < mine;) {
     const int U = (int)std::min<long long>(U_next, mine - u0);
-    const long long peak = run_batch(e, mode, A, (int)u0, U);
-    e->peak_entries = std::max(e->peak_entries, peak);
-    per_unit = std::max(per_unit, (double)peak / U);
-    if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries (%.1f per unit)\n", rt_type, u0, U, peak, (double)peak / U);
+    int cap0 = (int)std::min(max_cap, std::max(4.0 * U, 1.25 * std::max(per_unit, est) * U) + 1024.0);
+    if (e->opt_cap0 > 0) cap0 = e->opt_cap0;   // test hook: start small so that steps are refused and the buffers grow
+    const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0)
+                                                 : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0);
+    e->peak_entries = std::max(e->peak_entries, bs.peak);
+    per_unit = std::max(per_unit, (double)std::max(bs.maxH, std::max(bs.maxW, bs.maxT)) / U);
+    if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries, per-list need %d / %d / %d (%.1f per unit), capacity %d\n",
+                                       rt_type, u0, U, bs.peak, bs.maxH, bs.maxW, bs.maxT, per_unit, e->capH);
     u0 += U;
-    U_next = (long long)(max_entries / (1.5 * std::max(per_unit, est)));   // x1.5: headroom for units richer than those seen so far
+    U_next = (long long)(max_cap / (1.5 * std::max(per_unit, est)));   // x1.5: headroom for units richer than those seen so far
     U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   }
   est = std::max(est, per_unit);   // high-water mark (the scattering iterations share one rt_type and shrink)
@@ -1433,7 +1567,10 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
-  else if (s == "scan_chained") e->opt_scan_chained = value ? 1 : 0;
+  else if (s == "graphs") e->opt_graphs = value ? 1 : 0;
+  else if (s == "cap0") e->opt_cap0 = std::max(0, (int)value);
+  else if (s == "split") e->opt_split = value ? 1 : 0;
+  else if (s == "scan_chained") { /* accepted for compatibility: every prefix sum is the chained single-launch scan */ }
   else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));
   else if (s == "deterministic") e->opt_det = value != 0;

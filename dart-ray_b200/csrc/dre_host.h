@@ -2,6 +2,7 @@
 // routines used to build the direction tables (pix2ang_nest healpix_routines.f90:30-136,
 // ang2pix_nest :238-348) with the same libm the Fortran host uses.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -28,6 +29,16 @@ template <class T> struct DBuf {
     CK(cudaMalloc(&p, want * sizeof(T)));
     cap = want;
   }
+  // grow to at least n elements, keeping the first `keep` ones
+  void grow_keep(size_t n, size_t keep, cudaStream_t s, double slack = 1.25) {
+    if (n <= cap) return;
+    const size_t want = (size_t)(n * slack) + 64;
+    T* q = nullptr;
+    CK(cudaMalloc(&q, want * sizeof(T)));
+    if (p && keep) CK(cudaMemcpyAsync(q, p, std::min(keep, cap) * sizeof(T), cudaMemcpyDeviceToDevice, s));
+    if (p) { CK(cudaStreamSynchronize(s)); cudaFree(p); }
+    p = q; cap = want;
+  }
   void upload(const T* h, size_t n, cudaStream_t s) { ensure(n, 1.0); CK(cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s)); }
   void zero(size_t n, cudaStream_t s) { ensure(n, 1.0); CK(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
 };
@@ -39,6 +50,11 @@ struct ListStore {
   void ensure(size_t cap, int L, size_t nunits) {
     unit.ensure(cap); dir_ipix.ensure(cap); cc_old.ensure(cap); meta.ensure(cap); dplane.ensure(cap); prev.ensure(cap);
     lum.ensure(cap * (size_t)L); seg.ensure(nunits + 1, 1.0);
+  }
+  // grow to `cap` entries keeping the first `keep` (the segment array is sized by the unit count and kept as it is)
+  void grow_keep(size_t cap, size_t keep, int L, cudaStream_t s) {
+    unit.grow_keep(cap, keep, s); dir_ipix.grow_keep(cap, keep, s); cc_old.grow_keep(cap, keep, s); meta.grow_keep(cap, keep, s);
+    dplane.grow_keep(cap, keep, s); prev.grow_keep(cap, keep, s); lum.grow_keep(cap * (size_t)L, keep * (size_t)L, s);
   }
   DreList view() {
     DreList l; l.unit = unit.p; l.dir_ipix = dir_ipix.p; l.meta = meta.p; l.cc_old = cc_old.p; l.dplane = dplane.p;

@@ -2,6 +2,7 @@
 // (cell list, point locator, pix2vec, layout transposes, scattering-iteration bookkeeping).
 #pragma once
 #include "dre_trace.cuh"
+#include "dre_lists.cuh"
 
 __device__ __forceinline__ void dre_src_coord(const DreDev& g, int nc, double src[3]) {   // calc_src_ccoord :1922-1939
   const int rt = g.rt_type;
@@ -164,23 +165,35 @@ __device__ __forceinline__ void dre_prep_lum(const DreDev& g, const DreAccum& A,
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(128) k_prep_rays(DreAccum A, DreUnits u, DreList H, DreList W, const DreTask* __restrict__ tasks, int nt,
-                                                   double* __restrict__ pkts, int pstride) {
+__global__ void __launch_bounds__(128) k_prep_rays(DreAccum A, DreStep S, int cur) {
   const DreDev& g = c_g;
   __shared__ int s_e[4][128], s_mode[128], s_w[128], s_nc[128], s_dk[128], s_dip[128];
-  const int t0 = blockIdx.x * 128, t = t0 + threadIdx.x;
-  if (t < nt) dre_prep_record<MODE>(g, u, H, W, tasks, t, pkts, pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
-  __syncthreads();
-  dre_prep_lum(g, A, H, W, t0, min(128, nt - t0), pkts, pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+  const int nt = S.ctl->nT;          // 0 when the step was refused (DreCtl::abort)
+  const DreList H = S.H[cur], W = S.W[cur];
+  for (int t0 = blockIdx.x * 128; t0 < nt; t0 += gridDim.x * 128) {
+    const int t = t0 + threadIdx.x;
+    if (t < nt) dre_prep_record<MODE>(g, S.u, H, W, S.tasks, t, S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    __syncthreads();
+    dre_prep_lum(g, A, H, W, t0, min(128, nt - t0), S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    __syncthreads();
+  }
 }
 
 // ---- ray-march kernel of the list passes (precalc / direct / scattering) ----------------
 template <int MODE, int KL, int DET>
-__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, const double* __restrict__ pkts, int pstride, int nt,
-                        DreList out, int* __restrict__ counter, int chunk) {
+__global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_trace(DreAccum A, DreStep S, int chunk_max) {
   extern __shared__ __align__(128) unsigned char smem[];
   const DreDev& g = c_g;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // the number of rays of the step lives on the device (0 when the step was refused, DreCtl::abort)
+  const int nt = S.ctl->nT;
+  if (nt <= 0) return;
+  const double* __restrict__ pkts = S.pkts;
+  const int pstride = S.pstride;
+  const DreList out = S.OUT;
+  int* __restrict__ counter = &S.ctl->trace_counter;
+  // rays are handed out in chunks of consecutive tasks: one atomic per chunk, >= 8 chunks per warp for balance
+  const int chunk = max(1, min(chunk_max, nt / ((int)gridDim.x * (int)(blockDim.x >> 5) * 8)));
   WarpSmem ws;
   dre_warp_smem(g, smem, warp, lane, ws, MODE == MODE_DEP, A.stage_split, DET ? A.qc : nullptr);
   WarpStats st; memset(&st, 0, sizeof(st));
@@ -375,13 +388,15 @@ __global__ void k_src_compact(const int* __restrict__ flag, const int* __restric
 }
 
 // seeds of a batch of units: create_high_ray_list ray_list.f90:71-106 (nside 2 pixel = sector)
-__global__ void k_seed(DreUnits u, DreList H, DreList W, const int* __restrict__ srclist, int unit0, int stride,
-                       int rank_off) {
+__global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int unit0, int stride, int rank_off) {
   const DreDev& g = c_g;
+  const DreUnits u = S.u;
+  const DreList H = S.H[0], W = S.W[0];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i > u.U) return;
+  if (i == 0) S.ctl->U = U;
+  if (i > U) return;
   H.seg[i] = i; W.seg[i] = 0;
-  if (i == u.U) return;
+  if (i == U) return;
   const int gid = rank_off + (unit0 + i) * stride;     // global unit id = source_ordinal*48 + sector
   const int nc = srclist[gid / 48], sector = gid % 48;
   u.nc[i] = nc; u.gid[i] = gid; u.nk[i] = DRE_NSIDE_MIN_K; u.step[i] = 0; u.mode[i] = 1;

@@ -7,365 +7,411 @@
 // resolution (the 4-ray merge), task emission, the ray-march kernel, and a stable rebuild of
 // both lists.  Prefix sums keep the reference's list order (append order == processing order),
 // which the merge and therefore the intersection lists depend on.
+//
+// The step is DEVICE-DRIVEN: every count (list lengths, extracted entries, tasks) stays in device
+// memory -- the length of a list is the last element of its segment array -- and every kernel is
+// launched with a fixed grid that strides over a count it reads itself.  The host enqueues the whole
+// step without a single read-back and looks at one small control block (DreCtl) per step: units still
+// active, error flag, and "a buffer is too small" (the step then changes nothing and is repeated after
+// the buffers have grown).  The launch sequence of a step is therefore a constant and is replayed
+// from a CUDA graph.
 #pragma once
 #include "dre_common.cuh"
 
+#define STEP_THREADS 256
+#define GRID_LOOP(i, n) for (int i = blockIdx.x * blockDim.x + threadIdx.x, _n = (n); i < _n; i += gridDim.x * blockDim.x)
+
+// Device-written control block of the wavefront; copied to the host once per step.
+struct DreCtl {
+  int U;               // units of the batch (set by k_seed)
+  int active;          // units that still have rays after this step
+  int nkmask;          // bit mask of their log2(nside)
+  int abort;           // a buffer is too small for this step: nothing was changed, grow to need* and repeat
+  int nH, nW;          // list lengths at the start of the step
+  int nExt, nT;        // extracted entries, ray_tracing calls of the step
+  int nH2, nW2;        // list lengths after the step
+  int needH, needW, needT, needE;   // entries the step needs in the HIGH / LOW lists, the task arrays and the event buffer
+  int trace_counter;   // task fetch counter of the ray-march kernel
+  unsigned scan_epoch; // epoch base of the chained scans of the step
+  int tickets[16];     // tile tickets, one per scan job of the step
+};
+
+// Pointers and capacities of the wavefront scratch (host-owned; passed to the kernels by value).
+struct DreStep {
+  DreList H[2], W[2], OUT;           // n unused: the length of H / W is seg[U]
+  DreUnits u;
+  int *selH, *posH, *selW, *posW;    // [capH (+1)], [capW (+1)]
+  int *extcnt, *ext_seg;             // [U], [U+1]
+  int *ext, *ipx, *gone, *cand, *ncand, *nxt, *hasprev, *unit_of_ext, *ntask, *nreco, *task_off, *reco_off;   // [capH + capW (+1)]
+  int *reco_cnt, *keptH, *keptW, *newHcnt, *newWcnt;   // [U]
+  int *fH, *fW, *posOH, *posOW;      // [capT (+1)]
+  DreTask* tasks;                    // [capT]
+  double* pkts; int pstride;         // [capT] ray packets
+  int capH, capW, capT;
+  DreCtl* ctl;
+  unsigned long long* scan_desc; int desc_stride;   // tile descriptors of the chained scans, one region per job slot
+  int* err;                          // first reference STOP condition hit
+  unsigned long long* steps;         // counter of (unit, step) pairs executed
+  int kmax;                          // largest log2(nside) with a direction table
+};
+
 // ---------------------------------------------------------------------------------------
-// exclusive scan: out[0..n] (n+1 values, out[n] = total)
+// exclusive scans: out[0..n] (n+1 values, out[n] = total), up to 2 independent jobs per launch
 // ---------------------------------------------------------------------------------------
 #define SCAN_THREADS 512
 #define SCAN_ITEMS 4
 #define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+struct ScanJob { const int* in; int* out; const int* n_ptr; int n_const; int slot; int* total_out; };   // n = n_ptr ? *n_ptr : n_const; total also to *total_out
+struct ScanJobs { ScanJob j[2]; };
 
-__global__ void k_scan_tile(const int* __restrict__ in, int* __restrict__ out, int* __restrict__ sums, int n) {
-  __shared__ int wsum[SCAN_THREADS / 32];
-  const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-  int v[SCAN_ITEMS], tot = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? in[base + i] : 0; tot += v[i]; }
-  int x = tot;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-  if (lane == 31) wsum[w] = x;
-  __syncthreads();
-  if (w == 0) {
-    int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
-    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
-  }
-  __syncthreads();
-  int excl = x - tot + (w > 0 ? wsum[w - 1] : 0);
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
-  if (threadIdx.x == SCAN_THREADS - 1) sums[blockIdx.x] = excl;
-}
-// n <= SCAN_TILE: the whole scan (and the total out[n]) in one launch
-__global__ void k_scan_small(const int* __restrict__ in, int* __restrict__ out, int n) {
-  __shared__ int wsum[SCAN_THREADS / 32];
-  const int base = threadIdx.x * SCAN_ITEMS;
-  int v[SCAN_ITEMS], tot = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? in[base + i] : 0; tot += v[i]; }
-  int x = tot;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-  if (lane == 31) wsum[w] = x;
-  __syncthreads();
-  if (w == 0) {
-    int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
-    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
-  }
-  __syncthreads();
-  int excl = x - tot + (w > 0 ? wsum[w - 1] : 0);
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
-  if (threadIdx.x == SCAN_THREADS - 1) out[n] = excl;
-}
-// Any n in ONE launch: chained scan with decoupled look-back.  Tile t publishes {epoch, state, value} as one 64-bit word
-// (state 1 = tile aggregate, 2 = inclusive prefix); a tile adds up the aggregates of its predecessors until it meets an
-// inclusive prefix.  The epoch (one per call, 30 bits) makes the words of earlier scans on the same descriptor array read
-// as "not published", so the array is never cleared.  Tiles are taken in blockIdx order: CUDA dispatches the blocks of
-// a grid in index order, so every predecessor of a resident block has been dispatched and the wait terminates.
+// Chained scan with decoupled look-back, persistent form.  A block takes tile tickets from an atomic counter, so a
+// tile's predecessors are always held by blocks that are already running (no assumption on the dispatch order of the
+// grid).  Tile t publishes {epoch, state, value} as one 64-bit word (state 1 = tile aggregate, 2 = inclusive prefix) and
+// adds up the aggregates of its predecessors until it meets an inclusive prefix.  The epoch makes the words of earlier
+// scans on the same descriptor region read as "not published", so the region is never cleared.  The ticket counters of a
+// step are cleared by its first kernel.  `skip` (DreCtl::abort) turns the scan into n = 0.
 #define SCAN_DESC(epoch, state, val) (((unsigned long long)(epoch) << 34) | ((unsigned long long)(state) << 32) | (unsigned long long)(unsigned)(val))
-__global__ void k_scan_chained(const int* __restrict__ in, int* __restrict__ out, int n, unsigned long long* desc, unsigned epoch) {
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* ctl, unsigned long long* desc_all, int desc_stride,
+                                                            unsigned epoch_off, int skip_on_abort) {
   __shared__ int wsum[SCAN_THREADS / 32];
-  __shared__ int s_prefix;
-  const int tile = blockIdx.x;
-  const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
-  int v[SCAN_ITEMS], tot = 0;
-#pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? in[base + i] : 0; tot += v[i]; }
-  int x = tot;
+  __shared__ int s_prefix, s_tile;
+  const ScanJob jb = J.j[blockIdx.y];
+  if (jb.out == nullptr) return;
+  int n = jb.n_ptr ? *jb.n_ptr : jb.n_const;
+  if (skip_on_abort && ctl->abort) return;
+  if (n < 0) n = 0;
+  const int ntiles = n > 0 ? (n + SCAN_TILE - 1) / SCAN_TILE : 1;
+  unsigned epoch = (ctl->scan_epoch + epoch_off + (unsigned)blockIdx.y) % 0x3fffffffu + 1u;   // never 0: a cleared word reads as unpublished
+  volatile unsigned long long* d = desc_all + (size_t)jb.slot * desc_stride;
+  int* ticket = &ctl->tickets[jb.slot];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-  if (lane == 31) wsum[w] = x;
-  __syncthreads();
-  if (w == 0) {
-    int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
-    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
-    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
-  }
-  __syncthreads();
-  if (w == 0) {          // look-back by one warp: 32 predecessors per round
-    const int agg = wsum[SCAN_THREADS / 32 - 1];
-    volatile unsigned long long* d = desc;
-    int prefix = 0;
-    if (tile > 0) {
-      if (lane == 0) d[tile] = SCAN_DESC(epoch, 1u, agg);
-      for (int j0 = tile - 1; ; ) {
-        const int j = j0 - lane;
-        // tile -1 stands for "inclusive prefix 0"
-        const unsigned long long q = (j >= 0) ? d[j] : SCAN_DESC(epoch, 2u, 0);
-        const unsigned state = (unsigned)(q >> 32) & 3u;
-        const bool ready = ((unsigned)(q >> 34) == epoch) && state != 0;
-        const unsigned rm = __ballot_sync(0xffffffffu, ready), im = __ballot_sync(0xffffffffu, ready && state == 2u);
-        int upto;                                          // lanes 0..upto take part in this round
-        if (im) {
-          upto = __ffs(im) - 1;                            // nearest predecessor that knows its inclusive prefix
-          const unsigned need = (upto == 31) ? 0xffffffffu : ((2u << upto) - 1u);
-          if ((rm & need) != need) continue;               // an aggregate in between is not published yet
-        } else {
-          if (rm != 0xffffffffu) continue;
-          upto = 31;
-        }
-        int val = (lane <= upto) ? (int)(unsigned)(q & 0xffffffffull) : 0;
-        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-        prefix += val;
-        if (im) break;
-        j0 -= 32;
-      }
-    }
-    if (lane == 0) { d[tile] = SCAN_DESC(epoch, 2u, prefix + agg); s_prefix = prefix; }
-  }
-  __syncthreads();
-  int excl = s_prefix + x - tot + (w > 0 ? wsum[w - 1] : 0);
+  for (;;) {
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int tile = s_tile;
+    if (tile >= ntiles) break;
+    const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS], tot = 0;
 #pragma unroll
-  for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = excl; excl += v[i]; }
-  if (tile == gridDim.x - 1 && threadIdx.x == SCAN_THREADS - 1) out[n] = excl;
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = (base + i < n) ? jb.in[base + i] : 0; tot += v[i]; }
+    int x = tot;
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int s = (lane < SCAN_THREADS / 32) ? wsum[lane] : 0;
+      for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+      if (lane < SCAN_THREADS / 32) wsum[lane] = s;
+    }
+    __syncthreads();
+    if (w == 0) {          // look-back by one warp: 32 predecessors per round
+      const int agg = wsum[SCAN_THREADS / 32 - 1];
+      int prefix = 0;
+      if (tile > 0) {
+        if (lane == 0) { d[tile] = SCAN_DESC(epoch, 1u, agg); __threadfence(); }
+        for (int j0 = tile - 1; ; ) {
+          const int j = j0 - lane;
+          // tile -1 stands for "inclusive prefix 0"
+          const unsigned long long q = (j >= 0) ? d[j] : SCAN_DESC(epoch, 2u, 0);
+          const unsigned state = (unsigned)(q >> 32) & 3u;
+          const bool ready = ((unsigned)(q >> 34) == epoch) && state != 0;
+          const unsigned rm = __ballot_sync(0xffffffffu, ready), im = __ballot_sync(0xffffffffu, ready && state == 2u);
+          int upto;                                          // lanes 0..upto take part in this round
+          if (im) {
+            upto = __ffs(im) - 1;                            // nearest predecessor that knows its inclusive prefix
+            const unsigned need = (upto == 31) ? 0xffffffffu : ((2u << upto) - 1u);
+            if ((rm & need) != need) continue;               // an aggregate in between is not published yet
+          } else {
+            if (rm != 0xffffffffu) continue;
+            upto = 31;
+          }
+          int val = (lane <= upto) ? (int)(unsigned)(q & 0xffffffffull) : 0;
+          for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+          prefix += val;
+          if (im) break;
+          j0 -= 32;
+        }
+      }
+      if (lane == 0) { d[tile] = SCAN_DESC(epoch, 2u, prefix + agg); s_prefix = prefix; }
+    }
+    __syncthreads();
+    int excl = s_prefix + x - tot + (w > 0 ? wsum[w - 1] : 0);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) jb.out[base + i] = excl; excl += v[i]; }
+    if (tile == ntiles - 1 && threadIdx.x == SCAN_THREADS - 1) { jb.out[n] = excl; if (jb.total_out) *jb.total_out = excl; }
+    __syncthreads();       // wsum / s_tile are reused by the next tile
+  }
 }
-__global__ void k_scan_add(int* __restrict__ out, const int* __restrict__ sums_scanned, int n, int nblocks) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] += sums_scanned[i / SCAN_TILE];
-  if (i == 0) out[n] = sums_scanned[nblocks];
-}
-__global__ void k_set_int(int* p, int v) { *p = v; }
 
 // ---------------------------------------------------------------------------------------
 // step kernels
 // ---------------------------------------------------------------------------------------
-// mode of each unit: extract from HIGH if it has entries, else from LOW (ray_list.f90:120,167)
-__global__ void k_plan(DreUnits u, const int* __restrict__ segH, const int* __restrict__ segW) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= u.U) return;
-  const int nh = segH[i + 1] - segH[i], nw = segW[i + 1] - segW[i];
-  u.mode[i] = nh > 0 ? 1 : (nw > 0 ? 2 : 0);
+// Start of a step: mode of each unit -- extract from HIGH if it has entries, else from LOW (ray_list.f90:120,167) -- and the
+// selection flags of extract_ray_list: HIGH entries with nside == nside/2, LOW entries with nside == 2*nside.
+__global__ void __launch_bounds__(STEP_THREADS) k_step_select(DreStep S, int cur) {
+  const DreList H = S.H[cur], W = S.W[cur];
+  const DreUnits u = S.u;
+  const int U = S.ctl->U, nH = H.seg[U], nW = W.seg[U];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    DreCtl* c = S.ctl;
+    c->abort = 0; c->active = 0; c->nkmask = 0; c->trace_counter = 0; c->nH = nH; c->nW = nW;
+    for (int i = 0; i < 16; i++) c->tickets[i] = 0;
+  }
+  GRID_LOOP(i, U) {
+    const int nh = H.seg[i + 1] - H.seg[i], nw = W.seg[i + 1] - W.seg[i];
+    u.mode[i] = nh > 0 ? 1 : (nw > 0 ? 2 : 0);
+  }
+  GRID_LOOP(i, nH) {                     // a unit with HIGH entries is in mode 1
+    const int un = H.unit[i];
+    S.selH[i] = (META_NSK(H.meta[i]) == u.nk[un] - 1) ? 1 : 0;
+  }
+  GRID_LOOP(i, nW) {
+    const int un = W.unit[i];
+    const int nh = H.seg[un + 1] - H.seg[un];
+    S.selW[i] = (nh == 0 && META_NSK(W.meta[i]) == u.nk[un] + 1) ? 1 : 0;
+  }
 }
 
-// which == 1: HIGH entries with nside == nside/2 ; which == 2: LOW entries with nside == 2*nside
-__global__ void k_select(DreList l, DreUnits u, int which, int* __restrict__ sel) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= l.n) return;
-  const int un = l.unit[i];
-  const int want = (which == 1) ? u.nk[un] - 1 : u.nk[un] + 1;
-  sel[i] = (u.mode[un] == which && META_NSK(l.meta[i]) == want) ? 1 : 0;
-}
-
-__global__ void k_unit_ext(DreUnits u, const int* __restrict__ segH, const int* __restrict__ segW,
-                           const int* __restrict__ posH, const int* __restrict__ posW, int nH, int nW,
-                           int* __restrict__ extcnt) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= u.U) return;
-  int c = 0;
-  if (u.mode[i] == 1 && nH > 0) c = posH[segH[i + 1]] - posH[segH[i]];
-  else if (u.mode[i] == 2 && nW > 0) c = posW[segW[i + 1]] - posW[segW[i]];
-  extcnt[i] = c;
+__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_ext(DreStep S, int cur) {
+  const DreList H = S.H[cur], W = S.W[cur];
+  const DreUnits u = S.u;
+  GRID_LOOP(i, S.ctl->U) {
+    int c = 0;
+    if (u.mode[i] == 1) c = S.posH[H.seg[i + 1]] - S.posH[H.seg[i]];
+    else if (u.mode[i] == 2) c = S.posW[W.seg[i + 1]] - S.posW[W.seg[i]];
+    S.extcnt[i] = c;
+  }
 }
 
 // EXT[x] = index of the extracted entry in its old list; for LOW-mode units also the parent
 // pixel at the current nside (ang2pix_nest(nside, theta, phi), ray_list.f90:218) and gone = 0.
-__global__ void k_fill_ext(DreList l, DreUnits u, int which, const int* __restrict__ sel, const int* __restrict__ pos,
-                           const int* __restrict__ ext_seg, int* __restrict__ ext, int* __restrict__ ipx,
-                           int* __restrict__ gone, int* __restrict__ hasprev) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= l.n || !sel[i]) return;
-  const int un = l.unit[i];
-  const int x = ext_seg[un] + (pos[i] - pos[l.seg[un]]);
-  ext[x] = i;
-  gone[x] = 0; hasprev[x] = 0;
-  if (which == 2) {
-    const unsigned m = l.meta[i];
-    ipx[x] = l.dir_ipix[i] >> (2 * (META_DIRK(m) - u.nk[un]));
-  } else ipx[x] = -1;
+__global__ void __launch_bounds__(STEP_THREADS) k_step_fill_ext(DreStep S, int cur) {
+  const DreUnits u = S.u;
+  for (int which = 1; which <= 2; which++) {
+    const DreList l = (which == 1) ? S.H[cur] : S.W[cur];
+    const int* sel = (which == 1) ? S.selH : S.selW;
+    const int* pos = (which == 1) ? S.posH : S.posW;
+    GRID_LOOP(i, l.seg[S.ctl->U]) {
+      if (!sel[i]) continue;
+      const int un = l.unit[i];
+      const int x = S.ext_seg[un] + (pos[i] - pos[l.seg[un]]);
+      S.ext[x] = i; S.unit_of_ext[x] = un;
+      S.gone[x] = 0; S.hasprev[x] = 0;
+      if (which == 2) S.ipx[x] = l.dir_ipix[i] >> (2 * (META_DIRK(l.meta[i]) - u.nk[un]));
+      else S.ipx[x] = -1;
+    }
+  }
 }
 
 // sibling search of extract_ray_list (ray_list.f90:237-253): the first <= 3 later entries of the
 // same unit with the same parent pixel, the same isel and dplane within 0.001 (relative to the
 // leader).  `gone` is NOT consulted for the members, as in the reference (SURVEY A.3 note).
-__global__ void k_cand(DreList w, DreUnits u, const int* __restrict__ ext_seg, const int* __restrict__ ext,
-                       const int* __restrict__ unit_of_ext, const int* __restrict__ ipx, int next,
-                       int* __restrict__ cand, int* __restrict__ ncand, int* __restrict__ nxt, int* __restrict__ hasprev) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= next) return;
-  const int un = unit_of_ext[x];
-  if (u.mode[un] != 2) { ncand[x] = 0; nxt[x] = -1; return; }
-  const int i = ext[x];
-  const int end = ext_seg[un + 1];
-  const int ip = ipx[x], isel = META_ISEL(w.meta[i]);
-  const double dpl = w.dplane[i];
-  int n = 0, first = -1;
-  for (int y = x + 1; y < end && (n < 3 || first < 0); y++) {
-    if (ipx[y] != ip) continue;
-    if (first < 0) first = y;
-    if (n == 3) break;
-    const int j = ext[y];
-    if (META_ISEL(w.meta[j]) != isel) continue;
-    if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) cand[3 * (size_t)x + n++] = y;
-  }
-  ncand[x] = n;
-  nxt[x] = first;                 // chain of the entries of this unit with the same parent pixel
-  if (first >= 0) hasprev[first] = 1;
-}
-
-// leader resolution in list order (ray_list.f90:222-226, 268, 290): an entry is a leader unless an
-// earlier leader already consumed it.  Members always share the leader's parent pixel, so the entries
-// of one (unit, parent pixel) chain are independent of every other chain: one thread walks each chain
-// in list order (the head is the entry no earlier entry links to).
-__global__ void k_resolve(DreUnits u, const int* __restrict__ unit_of_ext, int next, const int* __restrict__ cand,
-                          const int* __restrict__ ncand, const int* __restrict__ nxt, const int* __restrict__ hasprev,
-                          int* __restrict__ gone, int* __restrict__ leader) {
-  const int x0 = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x0 >= next || u.mode[unit_of_ext[x0]] != 2 || hasprev[x0]) return;
-  for (int x = x0; x >= 0; x = nxt[x]) {
-    if (gone[x]) { leader[x] = 0; continue; }
-    leader[x] = 1;
-    for (int m = 0; m < ncand[x]; m++) gone[cand[3 * (size_t)x + m]] = 1;
-  }
-}
-
-// tasks / re-queued (ray_type_reco) entries produced by each extracted entry
-__global__ void k_count(DreList h, DreUnits u, const int* __restrict__ ext_seg, const int* __restrict__ ext, int next,
-                        const int* __restrict__ unit_of_ext, const int* __restrict__ ncand, const int* __restrict__ leader,
-                        int* __restrict__ ntask, int* __restrict__ nreco) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= next) return;
-  const int un = unit_of_ext[x];
-  int nt = 0, nr = 0;
-  if (u.mode[un] == 1) nt = (META_TYPE(h.meta[ext[x]]) == RT_RECO) ? 1 : 4;     // rt_routines.f90:1389-1403
-  else if (leader[x]) { if (ncand[x] == 3) nt = 1; else nr = 1 + ncand[x]; }      // ray_list.f90:255-291
-  ntask[x] = nt; nreco[x] = nr;
-}
-
-__global__ void k_unit_of_ext(DreUnits u, const int* __restrict__ ext_seg, int* __restrict__ unit_of_ext) {
-  const int un = blockIdx.x * blockDim.x + threadIdx.x;
-  if (un >= u.U) return;
-  for (int x = ext_seg[un]; x < ext_seg[un + 1]; x++) unit_of_ext[x] = un;
-}
-
-__global__ void k_emit_tasks(DreUnits u, const int* __restrict__ ext, int next, const int* __restrict__ unit_of_ext,
-                             const int* __restrict__ cand, const int* __restrict__ ntask, const int* __restrict__ task_off,
-                             DreTask* __restrict__ tasks) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= next) return;
-  const int nt = ntask[x];
-  if (nt == 0) return;
-  const int un = unit_of_ext[x];
-  for (int s = 0; s < nt; s++) {
-    DreTask t; t.unit = un; t.e0 = ext[x]; t.e1 = t.e2 = t.e3 = -1; t.sub = s; t.pad = 0;
-    if (u.mode[un] == 1) t.kind = (nt == 4) ? 0 : 1;
-    else {
-      t.kind = 2;
-      t.e1 = ext[cand[3 * (size_t)x + 0]]; t.e2 = ext[cand[3 * (size_t)x + 1]]; t.e3 = ext[cand[3 * (size_t)x + 2]];
+__global__ void __launch_bounds__(STEP_THREADS) k_step_cand(DreStep S, int cur) {
+  const DreList w = S.W[cur];
+  const DreUnits u = S.u;
+  GRID_LOOP(x, S.ext_seg[S.ctl->U]) {
+    const int un = S.unit_of_ext[x];
+    if (u.mode[un] != 2) { S.ncand[x] = 0; S.nxt[x] = -1; continue; }
+    const int i = S.ext[x];
+    const int end = S.ext_seg[un + 1];
+    const int ip = S.ipx[x], isel = META_ISEL(w.meta[i]);
+    const double dpl = w.dplane[i];
+    int n = 0, first = -1;
+    for (int y = x + 1; y < end && (n < 3 || first < 0); y++) {
+      if (S.ipx[y] != ip) continue;
+      if (first < 0) first = y;
+      if (n == 3) break;
+      const int j = S.ext[y];
+      if (META_ISEL(w.meta[j]) != isel) continue;
+      if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) S.cand[3 * (size_t)x + n++] = y;
     }
-    tasks[task_off[x] + s] = t;
+    S.ncand[x] = n;
+    S.nxt[x] = first;                 // chain of the entries of this unit with the same parent pixel
+    if (first >= 0) S.hasprev[first] = 1;
   }
 }
 
-// per-unit task segment (ray ordinal = task index - task_seg[unit]) and reco count
-__global__ void k_unit_tasks(DreUnits u, const int* __restrict__ ext_seg, const int* __restrict__ task_off,
-                             const int* __restrict__ reco_off, int* __restrict__ reco_cnt) {
-  const int un = blockIdx.x * blockDim.x + threadIdx.x;
-  if (un > u.U) return;
-  if (un == u.U) { u.task_seg[un] = task_off[ext_seg[un]]; return; }
-  u.task_seg[un] = task_off[ext_seg[un]];
-  reco_cnt[un] = reco_off[ext_seg[un + 1]] - reco_off[ext_seg[un]];
+// Leader resolution in list order (ray_list.f90:222-226, 268, 290) and the tasks / re-queued (ray_type_reco) entries each
+// extracted entry produces.  An entry is a leader unless an earlier leader already consumed it.  Members always share the
+// leader's parent pixel, so the entries of one (unit, parent pixel) chain are independent of every other chain: one thread
+// walks each chain in list order (the head is the entry no earlier entry links to).
+//   HIGH-mode entry: 4 child rays, or 1 for a ray_type_reco entry (rt_routines.f90:1389-1403)
+//   LOW-mode leader: 1 merged ray when it has 3 siblings, else the group is re-queued on HIGH (ray_list.f90:255-291)
+__global__ void __launch_bounds__(STEP_THREADS) k_step_resolve(DreStep S, int cur) {
+  const DreList h = S.H[cur];
+  const DreUnits u = S.u;
+  GRID_LOOP(x0, S.ext_seg[S.ctl->U]) {
+    const int md = u.mode[S.unit_of_ext[x0]];
+    if (md == 1) { S.ntask[x0] = (META_TYPE(h.meta[S.ext[x0]]) == RT_RECO) ? 1 : 4; S.nreco[x0] = 0; continue; }
+    if (md != 2) { S.ntask[x0] = 0; S.nreco[x0] = 0; continue; }
+    if (S.hasprev[x0]) continue;
+    for (int x = x0; x >= 0; x = S.nxt[x]) {
+      if (S.gone[x]) { S.ntask[x] = 0; S.nreco[x] = 0; continue; }
+      const int nc = S.ncand[x];
+      for (int m = 0; m < nc; m++) S.gone[S.cand[3 * (size_t)x + m]] = 1;
+      if (nc == 3) { S.ntask[x] = 1; S.nreco[x] = 0; } else { S.ntask[x] = 0; S.nreco[x] = 1 + nc; }
+    }
+  }
 }
 
-__global__ void k_out_flags(DreList out, int nt, int* __restrict__ fH, int* __restrict__ fW) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nt) return;
-  const int ty = META_TYPE(out.meta[t]);
-  fH[t] = (ty == RT_HIGH) ? 1 : 0;
-  fW[t] = (ty == RT_LOW) ? 1 : 0;
+// Per-unit task segments (ray ordinal = task index - task_seg[unit]) and reco counts, the capacity check of the step, and
+// the tasks themselves: one per ray_tracing call, in the reference's processing order.
+__global__ void __launch_bounds__(STEP_THREADS) k_step_tasks(DreStep S, int cur) {
+  const DreUnits u = S.u;
+  const int U = S.ctl->U, nExt = S.ext_seg[U], nT = S.task_off[nExt], nR = S.reco_off[nExt];
+  const int nH = S.H[cur].seg[U], nW = S.W[cur].seg[U];
+  // worst case of the rebuilt lists: HIGH' = kept ++ reco ++ outcomes, LOW' = kept ++ outcomes, outcomes <= tasks
+  const int needH = (nH - S.posH[nH]) + nR + nT, needW = (nW - S.posW[nW]) + nT;
+  const bool ab = nT > S.capT || needH > S.capH || needW > S.capW;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    DreCtl* c = S.ctl;
+    c->nExt = nExt; c->nT = ab ? 0 : nT; c->needH = needH; c->needW = needW; c->needT = nT; c->needE = 0; c->abort = ab ? 1 : 0;
+  }
+  if (ab) return;
+  GRID_LOOP(un, U + 1) {
+    u.task_seg[un] = S.task_off[S.ext_seg[un]];
+    if (un < U) S.reco_cnt[un] = S.reco_off[S.ext_seg[un + 1]] - S.reco_off[S.ext_seg[un]];
+  }
+  GRID_LOOP(x, nExt) {
+    const int nt = S.ntask[x];
+    if (nt == 0) continue;
+    const int un = S.unit_of_ext[x];
+    for (int s = 0; s < nt; s++) {
+      DreTask t; t.unit = un; t.e0 = S.ext[x]; t.e1 = t.e2 = t.e3 = -1; t.sub = s; t.pad = 0;
+      if (u.mode[un] == 1) t.kind = (nt == 4) ? 0 : 1;
+      else {
+        t.kind = 2;
+        t.e1 = S.ext[S.cand[3 * (size_t)x + 0]]; t.e2 = S.ext[S.cand[3 * (size_t)x + 1]]; t.e3 = S.ext[S.cand[3 * (size_t)x + 2]];
+      }
+      S.tasks[S.task_off[x] + s] = t;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(STEP_THREADS) k_step_out_flags(DreStep S) {
+  if (S.ctl->abort) return;
+  GRID_LOOP(t, S.ctl->nT) {
+    const int ty = META_TYPE(S.OUT.meta[t]);
+    S.fH[t] = (ty == RT_HIGH) ? 1 : 0;
+    S.fW[t] = (ty == RT_LOW) ? 1 : 0;
+  }
 }
 
 // sizes of the rebuilt lists: HIGH' = kept ++ reco ++ go_high outcomes ; LOW' = kept ++ go_low outcomes
-__global__ void k_unit_new(DreUnits u, const int* __restrict__ segH, const int* __restrict__ segW,
-                           const int* __restrict__ posH, const int* __restrict__ posW, int nH, int nW,
-                           const int* __restrict__ reco_cnt, const int* __restrict__ posOH, const int* __restrict__ posOW,
-                           int have_ext, int have_tasks, int* __restrict__ keptH, int* __restrict__ keptW,
-                           int* __restrict__ newHcnt, int* __restrict__ newWcnt) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= u.U) return;
-  int kh = segH[i + 1] - segH[i], kw = segW[i + 1] - segW[i];
-  if (nH > 0) kh -= posH[segH[i + 1]] - posH[segH[i]];
-  if (nW > 0) kw -= posW[segW[i + 1]] - posW[segW[i]];
-  keptH[i] = kh; keptW[i] = kw;
-  int oh = 0, ow = 0, rc = 0;
-  if (have_tasks) {
-    oh = posOH[u.task_seg[i + 1]] - posOH[u.task_seg[i]];
-    ow = posOW[u.task_seg[i + 1]] - posOW[u.task_seg[i]];
+__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_new(DreStep S, int cur) {
+  if (S.ctl->abort) return;
+  const DreList H = S.H[cur], W = S.W[cur];
+  const DreUnits u = S.u;
+  GRID_LOOP(i, S.ctl->U) {
+    const int kh = (H.seg[i + 1] - H.seg[i]) - (S.posH[H.seg[i + 1]] - S.posH[H.seg[i]]);
+    const int kw = (W.seg[i + 1] - W.seg[i]) - (S.posW[W.seg[i + 1]] - S.posW[W.seg[i]]);
+    S.keptH[i] = kh; S.keptW[i] = kw;
+    const int oh = S.posOH[u.task_seg[i + 1]] - S.posOH[u.task_seg[i]];
+    const int ow = S.posOW[u.task_seg[i + 1]] - S.posOW[u.task_seg[i]];
+    S.newHcnt[i] = kh + S.reco_cnt[i] + oh; S.newWcnt[i] = kw + ow;
   }
-  if (have_ext) rc = reco_cnt[i];
-  newHcnt[i] = kh + rc + oh; newWcnt[i] = kw + ow;
 }
 
-__device__ __forceinline__ void dre_copy_entry(const DreList& d, int di, const DreList& s, int si, int L, int un) {
+__device__ __forceinline__ void dre_copy_entry_hdr(const DreList& d, int di, const DreList& s, int si, int un) {
   d.unit[di] = un; d.dir_ipix[di] = s.dir_ipix[si]; d.meta[di] = s.meta[si]; d.cc_old[di] = s.cc_old[si];
   d.dplane[di] = s.dplane[si]; d.prev[di] = s.prev[si];
-  const double* a = s.lum + (size_t)si * L; double* b = d.lum + (size_t)di * L;
-  for (int l = 0; l < L; l++) b[l] = a[l];
 }
 
-// kept entries of an old list (stable)
-__global__ void k_build_kept(DreList dst, DreList src, const int* __restrict__ sel, const int* __restrict__ pos, int L) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= src.n || sel[i]) return;
-  const int un = src.unit[i];
-  const int s0 = src.seg[un];
-  const int rank = (i - s0) - (pos[i] - pos[s0]);
-  dre_copy_entry(dst, dst.seg[un] + rank, src, i, L, un);
+// destination slots of the four kinds of entries of the rebuilt lists (-1: the entry is not copied)
+__device__ __forceinline__ int dre_dst_kept(const DreList& dst, const DreList& src, const int* sel, const int* pos, int i) {
+  if (sel[i]) return -1;
+  const int un = src.unit[i], s0 = src.seg[un];
+  return dst.seg[un] + (i - s0) - (pos[i] - pos[s0]);          // kept entries of an old list (stable)
 }
-// failed merges re-queued on HIGH as ray_type_reco with the current nside (ray_list.f90:276-291,
-// add_to_high_ray_list :463-521)
-__global__ void k_build_reco(DreList dstH, DreList srcW, DreUnits u, const int* __restrict__ ext, int next,
-                             const int* __restrict__ unit_of_ext, const int* __restrict__ ext_seg,
-                             const int* __restrict__ cand, const int* __restrict__ nreco, const int* __restrict__ reco_off,
-                             const int* __restrict__ keptH, int L) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= next) return;
-  const int nr = nreco[x];
-  if (nr == 0) return;
-  const int un = unit_of_ext[x];
-  const int base = dstH.seg[un] + keptH[un] + (reco_off[x] - reco_off[ext_seg[un]]);
-  for (int m = 0; m < nr; m++) {
-    const int si = (m == 0) ? ext[x] : ext[cand[3 * (size_t)x + m - 1]];
-    const int di = base + m;
-    dre_copy_entry(dstH, di, srcW, si, L, un);
-    const unsigned mt = srcW.meta[si];
-    const int isel = META_ISEL(mt);
-    dstH.meta[di] = dre_meta(META_DIRK(mt), u.nk_prev[un], isel, RT_RECO);
-    if (isel == 0) { dstH.dplane[di] = 0.; dstH.prev[di] = 0.; }
+__device__ __forceinline__ int dre_dst_out(const DreStep& S, const DreList& Hn, const DreList& Wn, int t, int& toH) {
+  const int ty = META_TYPE(S.OUT.meta[t]);
+  if (ty != RT_HIGH && ty != RT_LOW) return -1;
+  const int un = S.tasks[t].unit, t0 = S.u.task_seg[un];
+  toH = (ty == RT_HIGH);
+  return toH ? Hn.seg[un] + S.keptH[un] + S.reco_cnt[un] + (S.posOH[t] - S.posOH[t0])
+             : Wn.seg[un] + S.keptW[un] + (S.posOW[t] - S.posOW[t0]);
+}
+
+// Rebuild of both lists in one launch: kept entries (stable), failed merges re-queued on HIGH as ray_type_reco with the
+// current nside (ray_list.f90:276-291, add_to_high_ray_list :463-521), and the go_high / go_low outcomes of the ray-march
+// kernel in task (= processing) order.  The luminosity rows are copied by L consecutive threads per entry (coalesced).
+__global__ void __launch_bounds__(STEP_THREADS) k_step_build(DreStep S, int cur, int L) {
+  if (S.ctl->abort) return;
+  const DreList Hc = S.H[cur], Wc = S.W[cur], Hn = S.H[1 - cur], Wn = S.W[1 - cur];
+  const DreUnits u = S.u;
+  const int U = S.ctl->U, nH = Hc.seg[U], nW = Wc.seg[U], nExt = S.ext_seg[U], nT = S.ctl->nT;
+  // ---- headers
+  GRID_LOOP(i, nH) { const int di = dre_dst_kept(Hn, Hc, S.selH, S.posH, i); if (di >= 0) dre_copy_entry_hdr(Hn, di, Hc, i, Hc.unit[i]); }
+  GRID_LOOP(i, nW) { const int di = dre_dst_kept(Wn, Wc, S.selW, S.posW, i); if (di >= 0) dre_copy_entry_hdr(Wn, di, Wc, i, Wc.unit[i]); }
+  GRID_LOOP(x, nExt) {
+    const int nr = S.nreco[x];
+    if (nr == 0) continue;
+    const int un = S.unit_of_ext[x];
+    const int base = Hn.seg[un] + S.keptH[un] + (S.reco_off[x] - S.reco_off[S.ext_seg[un]]);
+    for (int m = 0; m < nr; m++) {
+      const int si = (m == 0) ? S.ext[x] : S.ext[S.cand[3 * (size_t)x + m - 1]];
+      const int di = base + m;
+      dre_copy_entry_hdr(Hn, di, Wc, si, un);
+      const unsigned mt = Wc.meta[si];
+      const int isel = META_ISEL(mt);
+      Hn.meta[di] = dre_meta(META_DIRK(mt), u.nk[un], isel, RT_RECO);
+      if (isel == 0) { Hn.dplane[di] = 0.; Hn.prev[di] = 0.; }
+    }
+  }
+  GRID_LOOP(t, nT) {
+    int toH = 0;
+    const int di = dre_dst_out(S, Hn, Wn, t, toH);
+    if (di >= 0) dre_copy_entry_hdr(toH ? Hn : Wn, di, S.OUT, t, S.tasks[t].unit);
+  }
+  // ---- luminosity rows
+  const long long gsz = (long long)gridDim.x * blockDim.x, g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long long q = g0; q < (long long)nH * L; q += gsz) {
+    const int i = (int)(q / L), l = (int)(q - (long long)i * L);
+    const int di = dre_dst_kept(Hn, Hc, S.selH, S.posH, i);
+    if (di >= 0) Hn.lum[(size_t)di * L + l] = Hc.lum[(size_t)i * L + l];
+  }
+  for (long long q = g0; q < (long long)nW * L; q += gsz) {
+    const int i = (int)(q / L), l = (int)(q - (long long)i * L);
+    const int di = dre_dst_kept(Wn, Wc, S.selW, S.posW, i);
+    if (di >= 0) Wn.lum[(size_t)di * L + l] = Wc.lum[(size_t)i * L + l];
+  }
+  for (long long q = g0; q < (long long)nExt * L; q += gsz) {
+    const int x = (int)(q / L), l = (int)(q - (long long)x * L);
+    const int nr = S.nreco[x];
+    if (nr == 0) continue;
+    const int un = S.unit_of_ext[x];
+    const int base = Hn.seg[un] + S.keptH[un] + (S.reco_off[x] - S.reco_off[S.ext_seg[un]]);
+    for (int m = 0; m < nr; m++) {
+      const int si = (m == 0) ? S.ext[x] : S.ext[S.cand[3 * (size_t)x + m - 1]];
+      Hn.lum[(size_t)(base + m) * L + l] = Wc.lum[(size_t)si * L + l];
+    }
+  }
+  for (long long q = g0; q < (long long)nT * L; q += gsz) {
+    const int t = (int)(q / L), l = (int)(q - (long long)t * L);
+    int toH = 0;
+    const int di = dre_dst_out(S, Hn, Wn, t, toH);
+    if (di >= 0) (toH ? Hn : Wn).lum[(size_t)di * L + l] = S.OUT.lum[(size_t)t * L + l];
   }
 }
-// go_high / go_low outcomes of the ray-march kernel, in task (= processing) order
-__global__ void k_build_out(DreList dstH, DreList dstW, DreList out, int nt, DreUnits u, const DreTask* __restrict__ tasks,
-                            const int* __restrict__ posOH, const int* __restrict__ posOW, const int* __restrict__ keptH,
-                            const int* __restrict__ keptW, const int* __restrict__ reco_cnt, int L) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nt) return;
-  const int ty = META_TYPE(out.meta[t]);
-  if (ty != RT_HIGH && ty != RT_LOW) return;
-  const int un = tasks[t].unit;
-  const int t0 = u.task_seg[un];
-  if (ty == RT_HIGH) dre_copy_entry(dstH, dstH.seg[un] + keptH[un] + reco_cnt[un] + (posOH[t] - posOH[t0]), out, t, L, un);
-  else dre_copy_entry(dstW, dstW.seg[un] + keptW[un] + (posOW[t] - posOW[t0]), out, t, L, un);
-}
 
-// define_next_level rt_routines.f90:2745-2770 ; *active counts units that still have rays
-__global__ void k_next(DreUnits u, const int* __restrict__ segH, const int* __restrict__ segW, int* __restrict__ active,
-                       int* __restrict__ err, int kmax, unsigned long long* __restrict__ steps) {
-  // active[0] = units that still have rays, active[1] = bit mask of their log2(nside)
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= u.U) return;
-  u.nk_prev[i] = u.nk[i];
-  if (u.mode[i] == 0) return;
-  u.step[i]++;
-  atomicAdd(steps, 1ull);
-  const int nh = segH[i + 1] - segH[i], nw = segW[i + 1] - segW[i];
-  if (nh > 0) u.nk[i]++; else if (nw > 0) u.nk[i]--; else return;
-  if (u.nk[i] > kmax) { atomicCAS(err, 0, 4); return; }
-  if (u.nk[i] < 1) { atomicCAS(err, 0, 5); return; }
-  atomicAdd(active, 1);
-  atomicOr(active + 1, 1 << u.nk[i]);
+// define_next_level rt_routines.f90:2745-2770 on the rebuilt lists; the last kernel of a step
+__global__ void __launch_bounds__(STEP_THREADS) k_step_next(DreStep S, int cur) {
+  DreCtl* c = S.ctl;
+  if (blockIdx.x == 0 && threadIdx.x == 0) c->scan_epoch += 16u;
+  if (c->abort) return;
+  const DreList Hn = S.H[1 - cur], Wn = S.W[1 - cur];
+  const DreUnits u = S.u;
+  const int U = c->U;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { c->nH2 = Hn.seg[U]; c->nW2 = Wn.seg[U]; }
+  GRID_LOOP(i, U) {
+    if (u.mode[i] == 0) continue;
+    u.step[i]++;
+    atomicAdd(S.steps, 1ull);
+    const int nh = Hn.seg[i + 1] - Hn.seg[i], nw = Wn.seg[i + 1] - Wn.seg[i];
+    if (nh > 0) u.nk[i]++; else if (nw > 0) u.nk[i]--; else continue;
+    if (u.nk[i] > S.kmax) { atomicCAS(S.err, 0, 4); continue; }
+    if (u.nk[i] < 1) { atomicCAS(S.err, 0, 5); continue; }
+    atomicAdd(&c->active, 1);
+    atomicOr(&c->nkmask, 1 << u.nk[i]);
+  }
 }
