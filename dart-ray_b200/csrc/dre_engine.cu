@@ -22,6 +22,8 @@ struct Nccl {
   int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
   int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
   bool load(std::string& err) {
     if (h) return true;
@@ -33,6 +35,8 @@ struct Nccl {
     AllReduce = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))dlsym(h, "ncclAllReduce");
     CommDestroy = (int (*)(ncclComm_t))dlsym(h, "ncclCommDestroy");
     GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+    GroupStart = (int (*)())dlsym(h, "ncclGroupStart");
+    GroupEnd = (int (*)())dlsym(h, "ncclGroupEnd");
     if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy) { err = "NCCL symbols missing"; return false; }
     return true;
   }
@@ -1118,40 +1122,34 @@ int dre_allreduce(dre_engine* e, int rt_type) {
     const int rc = g_nccl.AllReduce(p, p, n, dt, NCCL_SUM, e->comm, e->st);
     if (rc != 0) throw DreError{std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error")};
   };
+  auto grp = [&](bool start) {
+    if (!g_nccl.GroupStart || !g_nccl.GroupEnd) return;
+    const int rc = start ? g_nccl.GroupStart() : g_nccl.GroupEnd();
+    if (rc != 0) throw DreError{std::string("ncclGroup: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error")};
+  };
   switch (rt_type) {
     case DRE_RTT_PRECALC_CELL: case DRE_RTT_PRECALC_SRC:       // reduce_u_fest_arr io_routines.f90:3708-3730
       ar(e->u_fest.p, NL, NCCL_FLOAT64); break;
     case DRE_RTT_DIR_CELL: case DRE_RTT_DIR_SRC:               // reduce_u_final_arr / reduce_scaspe_arr / reduce_lum_lost
+      grp(true);
       ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64); ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
-      ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64); break;
+      ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64);
+      grp(false); break;
     case DRE_RTT_SCATT: {
-      // delta trick io_routines.f90:3743-3757 and lum_lost correction :3846-3848
+      // delta trick io_routines.f90:3743-3757 and lum_lost correction :3846-3848, all on the device: the four reductions
+      // go out as one NCCL group and nothing waits for the host
       const bool det = e->opt_det && e->qc.p && (int)e->h_qc.size() == 3 * dre_lq(g.L) + 2;
       const double* qc_u = det ? e->qc.p + dre_lq(g.L) : nullptr;
+      const double* qc_l = det ? e->qc.p + 2 * dre_lq(g.L) : nullptr;
+      e->red_d.ensure((size_t)2 * g.L);
       (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 0, qc_u);
-      ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64);
-      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1, qc_u);
-      std::vector<double> ll(g.L), lp(g.L);
-      CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
-      CK(cudaMemcpyAsync(lp.data(), e->lum_lost_prev.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
-      CK(cudaStreamSynchronize(e->st));
-      std::vector<double> lpq(g.L, 0.0);
-      if (det) {   // exact form of the same correction: sum the per-rank increments over the grid value of lum_lost_prev
-        for (int l = 0; l < g.L; l++) {
-          volatile double c = e->h_qc[2 * dre_lq(g.L) + l], t = lp[l] + c;
-          lpq[l] = t - c;
-          ll[l] = ll[l] - lpq[l];
-        }
-      } else for (int l = 0; l < g.L; l++) ll[l] = ll[l] - (e->nranks - 1) / (double)e->nranks * lp[l];
-      CK(cudaMemcpyAsync(e->lum_lost.p, ll.data(), g.L * 8, cudaMemcpyHostToDevice, e->st));
-      ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
-      if (det) {
-        CK(cudaMemcpyAsync(ll.data(), e->lum_lost.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
-        CK(cudaStreamSynchronize(e->st));
-        for (int l = 0; l < g.L; l++) ll[l] = ll[l] + lpq[l];
-        CK(cudaMemcpyAsync(e->lum_lost.p, ll.data(), g.L * 8, cudaMemcpyHostToDevice, e->st));
-      }
+      (e->n_launch++, k_lum_lost_corr)<<<cdiv(g.L, 128), 128, 0, e->st>>>(e->lum_lost.p, e->lum_lost_prev.p, e->red_d.p, g.L, e->nranks, qc_l, 0);
+      grp(true);
+      ar(e->acc.p, e->rows_elems(), NCCL_FLOAT64); ar(e->lum_lost.p, g.L, NCCL_FLOAT64);
       ar(e->psel_sum.p, NS, NCCL_FLOAT64); ar(e->ipsel.p, NS, NCCL_INT64);
+      grp(false);
+      (e->n_launch++, k_u_delta)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->u_fest.p, g.N, g.L, g.ROW, 1, qc_u);
+      if (det) (e->n_launch++, k_lum_lost_corr)<<<cdiv(g.L, 128), 128, 0, e->st>>>(e->lum_lost.p, e->lum_lost_prev.p, e->red_d.p, g.L, e->nranks, qc_l, 1);
       break;
     }
     default: break;   // i_obs passes are not sharded (rt_loop_iobs has no MPI split, rt_routines.f90:1498)

@@ -571,6 +571,19 @@ __global__ void k_u_delta(double* __restrict__ rows, const double* __restrict__ 
   const double uf = qc_u ? dre_rq(u_fest[i], qc_u[i % L]) : u_fest[i];
   if (dir == 0) { const double v = rows[j] - uf; rows[j] = v < 0 ? 0 : v; } else rows[j] = rows[j] + uf;
 }
+// rt_mpi, lum_lost correction of the scattering iterations (io_routines.f90:3846-3848): every rank starts the pass from the
+// reduced lum_lost of the previous one, so before the sum  lum_lost_r -= (R-1)/R lum_lost_prev.  Deterministic mode (qc):
+// the exact form of the same correction -- subtract the grid value of lum_lost_prev (kept in `keep`) before the sum (phase 0)
+// and add it back once after it (phase 1).
+__global__ void k_lum_lost_corr(double* __restrict__ ll, const double* __restrict__ lp, double* __restrict__ keep, int L, int R,
+                                const double* __restrict__ qc, int phase) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= L) return;
+  if (qc) {
+    if (phase == 0) { const double q = dre_rq(lp[l], qc[l]); keep[l] = q; ll[l] = ll[l] - q; }
+    else ll[l] = ll[l] + keep[l];
+  } else if (phase == 0) ll[l] = ll[l] - (R - 1) / (double)R * lp[l];
+}
 // Deterministic mode, start of a pass: what the accumulators already hold is put on the rounding grid of the pass.
 __global__ void k_quantize_rows(double* __restrict__ rows, size_t n, int ROW, int L, const unsigned short* __restrict__ lamof,
                                 const double* __restrict__ qc) {

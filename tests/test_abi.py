@@ -53,3 +53,24 @@ def test_no_cpu_fallback(lib):
         lib.dre_destroy(h)
     else:
         assert rc != 0 and not h.value
+
+
+def build_abi_host(out_dir):
+    """gcc-compiles tests/abi_host.c (a C host that calls the ABI the way the Fortran wrappers do) against the library."""
+    import subprocess
+    exe = os.path.join(str(out_dir), "abi_host")
+    libdir = os.path.join(ROOT, "dart-ray_b200")
+    subprocess.check_call(["gcc", "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "abi_host.c"),
+                           "-L" + libdir, "-ldartray_engine", "-Wl,-rpath," + libdir, "-o", exe])
+    return exe
+
+
+def test_c_host_compiles_and_links(lib, tmp_path):
+    """The header is valid C (no C++-isms, no torch types) and a plain C program links against the library; without a GPU
+    the program stops at dre_create with a message, it never computes on the CPU."""
+    import subprocess
+    import torch
+    exe = build_abi_host(tmp_path)
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+        assert r.returncode != 0          # no scene files and no device: a loud failure, not a CPU result
