@@ -102,6 +102,14 @@ def algorithmic_bytes(c):
     return 28 * c.intersections + 4 * c.descent_loads + 24 * c.active_lambda_dep + 16 * c.sca_elems + 16 * beam_act
 
 
+def deposit_bytes(c):
+    """The part of algorithmic_bytes that belongs to the deposit kernel k_deposit (the geometry -- cell records and tree
+    descent, 28 B per intersection + 4 B per cchild load, < 1 % of the total -- is done by the march kernels, which are
+    not inside the timed launches)."""
+    beam_act = c.active_lambda - c.active_lambda_dep
+    return 24 * c.active_lambda_dep + 16 * c.sca_elems + 16 * beam_act
+
+
 def solve_resident(eng, scene, abi, max_iterations=30):
     """precalc -> direct -> scattering iterations on device-resident state; returns the pass counters."""
     for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST,
@@ -423,12 +431,13 @@ def main():
         deposits = sumr(float(sum(c.deposits for _, c in last)))
         ms = float(np.mean(step_ms))
         dep = [c for n, c in last if n.startswith("dir") or n.startswith("scatt")]
-        abytes = sumr(float(sum(algorithmic_bytes(c) for c in dep)))
+        abytes = sumr(float(sum(deposit_bytes(c) for c in dep)))
+        abytes_all = sumr(float(sum(algorithmic_bytes(c) for c in dep)))
         kms = maxr(float(sum(c.kernel_ms for c in dep)))
         mpi_ms = maxr(getattr(solve_resident, "last_mpi_ms", 0.0))
         psum = float(sum(c.pass_ms for _, c in last))
         pass_minmax = [-maxr(-psum), maxr(psum)]     # fastest / slowest rank: device time inside the passes
-        return {"pass_minmax": pass_minmax, "mpi_ms": mpi_ms, "ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "kms": kms, "last": last, "launches": launches,
+        return {"pass_minmax": pass_minmax, "mpi_ms": mpi_ms, "ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "abytes_all": abytes_all, "kms": kms, "last": last, "launches": launches,
                 "trace_launches": int(sum(c.trace_launches for c in dep))}
 
     with ClockSampler(local_rank) as clk:
@@ -462,14 +471,16 @@ def main():
     def roof_block(mm, workload):
         ach_ = roofline(mm)
         traffic, ent = traffic_of(workload)
-        return {"bound": "hbm", "kernel": "k_trace<MODE_DEP>", "achieved": ach_, "peak": peak, "unit": "GB/s", "frac": ach_ / peak,
+        return {"bound": "hbm", "kernel": "k_deposit", "achieved": ach_, "peak": peak, "unit": "GB/s", "frac": ach_ / peak,
                 "traffic": traffic, "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
-                "algorithmic_bytes_per_step": mm["abytes"], "kernel_ms_per_step": mm["kms"], "launches_per_step": mm["trace_launches"],
+                "algorithmic_bytes_per_step": mm["abytes"], "algorithmic_bytes_with_geometry": mm["abytes_all"],
+                "kernel_ms_per_step": mm["kms"], "launches_per_step": mm["trace_launches"],
                 "per": "GPU (algorithmic bytes of the whole job / n_gpus / slowest rank's kernel time)",
                 "traffic_note": (ent or {}).get("launch"),
-                "note": "achieved = ALGORITHMIC bytes (SURVEY 8d: reductions into the accumulator rows count 16 B per element) / device time of "
-                        "the k_trace launches; the rows are reduced in L2 (cp.reduce.async.bulk), so DRAM `traffic` is far below it when "
-                        "the rows fit the 126-MB L2"}
+                "note": "achieved = ALGORITHMIC bytes of the deposits (SURVEY 8d: opacity row 8 B, u_final RMW 16 B per active wavelength, "
+                        "scaspe RMW 16 B per element, beam test 16 B per active wavelength) / device time of the k_deposit launches (CUDA "
+                        "events on the engine's stream around every launch); the rows are reduced in L2 (cp.reduce.async.bulk), so DRAM "
+                        "`traffic` is far below it when the rows fit the 126-MB L2"}
 
     roof = roof_block(m, args.workload)
     line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

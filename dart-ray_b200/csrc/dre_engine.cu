@@ -92,13 +92,14 @@ struct dre_engine {
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 18, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_det = 0;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 1, opt_det = 0;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double last_kernel_ms = 0;
   long long peak_entries = 0;
   double est_H[16] = {0}, est_W[16] = {0}, est_T[16] = {0};   // list entries / tasks per unit seen so far, by rt_type
+  size_t ftab_budget = (size_t)24 << 30, ftab_bytes = 0; unsigned ftab_skipped = 0;   // phase-function tables: at most 24 GiB or 15 % of the free memory
   size_t list_budget = 0;          // bytes the ray lists of a batch may take (half of the memory free after configuration)
   double per_unit_est[16] = {0};   // list entries per unit of the last pass, by rt_type
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
@@ -276,6 +277,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   const int N = g.N;
   g.L = L; g.KLn = (L + 31) / 32; g.ndir = ndir;
   for (int k = 0; k <= DRE_MAXK; k++) { e->ftab[k].release(); g.ftab[k] = nullptr; }
+  e->ftab_bytes = 0; e->ftab_skipped = 0; e->ftab_budget = (size_t)24 << 30;
   e->dens.upload(dens_arr, (size_t)L * N, e->st); e->ksca.upload(ksca_arr_norm, L, e->st); e->gsca.upload(gsca_arr, L, e->st);
   // classes: set_npix_arr rt_routines.f90:5289-5311
   e->h_npix.assign(L, 0); e->h_npix_hp.assign(L, 0); e->h_off.assign(L, 0); e->h_ik.assign(L, -1);
@@ -540,7 +542,7 @@ int trace_warps(dre_engine* e, size_t* smem) {
   int w = std::max(1, std::min(e->opt_warps, 32));
   w = std::min(w, DRE_TRACE_THREADS / 32);
   const size_t extra = e->opt_det ? dre_det_smem_bytes(g.L) : 0;
-  while (w > 1 && (dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) + extra) * e->opt_ctas_per_sm > (size_t)226 * 1024) w--;
+  while (w > 1 && (dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) + extra) * e->opt_ctas_per_sm > (size_t)224 * 1024) w--;
   *smem = dre_trace_smem_bytes(g.ROW, g.L, w, e->opt_stage_split) + extra;
   DRE_REQUIRE(*smem <= (size_t)227 * 1024, "accumulator row does not fit in shared memory");
   return w;
@@ -550,9 +552,13 @@ int trace_warps(dre_engine* e, size_t* smem) {
 void ensure_ftab(dre_engine* e, unsigned nkmask) {
   DreDev& g = e->g;
   for (int k = DRE_NSIDE_MIN_K; k <= std::min(e->opt_ftab_kmax, 8); k++) {
-    if (!((nkmask >> k) & 1u) || g.ftab[k]) continue;
+    if (!((nkmask >> k) & 1u) || g.ftab[k] || ((e->ftab_skipped >> k) & 1u)) continue;
     build_dir_table(e, k);
     const size_t npix = (size_t)12 << (2 * k);
+    // the tables are a cache of calc_ffn_arr: beyond the byte budget a level stays untabulated and its rays evaluate the
+    // phase function themselves (dre_phase), as the rays above ftab_kmax do
+    if (e->ftab_bytes + npix * g.ROW * 8 > e->ftab_budget) { e->ftab_skipped |= 1u << k; continue; }
+    e->ftab_bytes += npix * g.ROW * 8;
     e->ftab[k].ensure(npix * g.ROW, 1.0);
     sync_g(e);
     e->n_launch++;
@@ -583,39 +589,42 @@ void launch_trace_kl(dre_engine* e, const DreAccum& A, const DreStep& S) {
   CK(cudaGetLastError());
 }
 
-// deposit passes as geometry (thread per ray, two passes around a prefix sum) + deposit (warp per ray): dre_split.cuh
+// deposit passes as geometry (thread per ray, two passes around a prefix sum) + deposit (warp per ray): dre_split.cuh.
+// with_geom: the event offsets and pass 1 of the march are launched here (they are part of k_step_pre_coop otherwise).
 template <int KL, int DET>
-void launch_split_kl(dre_engine* e, const DreAccum& A, const DreStep& S) {
+void launch_split_kl(dre_engine* e, const DreAccum& A, const DreStep& S, bool with_geom) {
   size_t smem = 0;
   const int warps = trace_warps(e, &smem);
   static_assert(KL == 1 || KL == 2 || KL == 4, "wavelengths per lane");
   int& set = g_smem_set[e->device & 63][2][KL == 4 ? 2 : KL - 1][DET];   // slot [2]: k_deposit
   if (set != (int)smem) { CK(cudaFuncSetAttribute(k_deposit<KL, DET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = (int)smem; }
-  ScanJobs J; memset(&J, 0, sizeof(J));
-  J.j[0].in = e->nev.p; J.j[0].out = e->evoff.p; J.j[0].n_ptr = &S.ctl->nT; J.j[0].slot = 10;
+  if (with_geom) {
+    ScanJobs J; memset(&J, 0, sizeof(J));
+    J.j[0].in = e->nev.p; J.j[0].out = e->evoff.p; J.j[0].n_ptr = &S.ctl->nT; J.j[0].slot = 10;
+    k_scan_jobs<<<dim3(e->sm_count, 1), SCAN_THREADS, 0, e->st>>>(J, S.ctl, S.scan_desc, S.desc_stride, 10u, 1);
+    k_geom_write<<<e->sm_count * 8, 128, 0, e->st>>>(A, S, e->evt.p, e->evoff.p, e->capE);
+    e->n_launch += 2;
+  }
   CK(cudaEventRecord(e->ev[2], e->st));
-  k_geom<0><<<e->sm_count * 8, 128, 0, e->st>>>(A, S, nullptr, e->nev.p, nullptr, 0);
-  k_scan_jobs<<<dim3(e->sm_count, 1), SCAN_THREADS, 0, e->st>>>(J, S.ctl, S.scan_desc, S.desc_stride, 10u, 1);
-  k_geom<1><<<e->sm_count * 8, 128, 0, e->st>>>(A, S, e->evt.p, e->nev.p, e->evoff.p, e->capE);
   k_deposit<KL, DET><<<e->sm_count * e->opt_ctas_per_sm, warps * 32, smem, e->st>>>(A, S, e->evt.p, e->opt_chunk);
   CK(cudaEventRecord(e->ev[3], e->st));
   CK(cudaGetLastError());
-  e->n_launch += 4;
+  e->n_launch += 1;
+}
+void launch_split(dre_engine* e, const DreAccum& A, const DreStep& S, bool with_geom) {
+  const int det = A.det ? 1 : 0;
+  switch (e->g.KLn * 2 + det) {
+    case 2: launch_split_kl<1, 0>(e, A, S, with_geom); break;
+    case 3: launch_split_kl<1, 1>(e, A, S, with_geom); break;
+    case 4: launch_split_kl<2, 0>(e, A, S, with_geom); break;
+    case 5: launch_split_kl<2, 1>(e, A, S, with_geom); break;
+    default: if (det) launch_split_kl<4, 1>(e, A, S, with_geom); else launch_split_kl<4, 0>(e, A, S, with_geom); break;
+  }
 }
 
 template <int MODE>
 void launch_trace(dre_engine* e, const DreAccum& A, const DreStep& S) {
-  if (MODE == MODE_DEP && e->opt_split) {
-    const int det = A.det ? 1 : 0;
-    switch (e->g.KLn * 2 + det) {
-      case 2: launch_split_kl<1, 0>(e, A, S); break;
-      case 3: launch_split_kl<1, 1>(e, A, S); break;
-      case 4: launch_split_kl<2, 0>(e, A, S); break;
-      case 5: launch_split_kl<2, 1>(e, A, S); break;
-      default: if (det) launch_split_kl<4, 1>(e, A, S); else launch_split_kl<4, 0>(e, A, S); break;
-    }
-    return;
-  }
+  if (MODE == MODE_DEP && e->opt_split) { launch_split(e, A, S, true); return; }
   if (A.det) {
     switch (e->g.KLn) {
       case 1: launch_trace_kl<MODE, 1, 1>(e, A, S); break;
@@ -754,14 +763,15 @@ int enqueue_pre(dre_engine* e, const DreAccum& A, const DreStep& S, int cur, cud
   k_step_resolve<<<G, STEP_THREADS, 0, st>>>(S, cur);
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.ntask, S.task_off, &S.ctl->nExt, 0, 3, S.nreco, S.reco_off, &S.ctl->nExt, 0, 4), S.ctl, S.scan_desc, S.desc_stride, 3u, 0);
   k_step_tasks<<<G, STEP_THREADS, 0, st>>>(S, cur);
-  k_prep_rays<MODE><<<e->sm_count * 8, 128, 0, st>>>(A, S, cur);
+  if (MODE == MODE_DEP && e->opt_split) k_prep_geom<<<e->sm_count * 8, 128, 0, st>>>(A, S, cur, e->nev.p);   // packets + pass 0 of the march
+  else k_prep_rays<MODE><<<e->sm_count * 8, 128, 0, st>>>(A, S, cur);
   return 10;
 }
 // launches of a step behind the ray-march kernel, ending with the copy of the control block to the host
-int enqueue_post(dre_engine* e, const DreStep& S, int cur, cudaStream_t st) {
+int enqueue_post(dre_engine* e, const DreStep& S, int cur, cudaStream_t st, bool split) {
   const int G = e->sm_count * 2, Gs = e->sm_count;
   const int* Un = &S.ctl->U;
-  k_step_out_flags<<<G, STEP_THREADS, 0, st>>>(S);
+  if (!split) k_step_out_flags<<<G, STEP_THREADS, 0, st>>>(S);   // k_geom / k_deposit leave the outcome flags themselves
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.fH, S.posOH, &S.ctl->nT, 0, 5, S.fW, S.posOW, &S.ctl->nT, 0, 6), S.ctl, S.scan_desc, S.desc_stride, 5u, 1);
   k_step_unit_new<<<G, STEP_THREADS, 0, st>>>(S, cur);
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.newHcnt, S.H[1 - cur].seg, Un, 0, 7, S.newWcnt, S.W[1 - cur].seg, Un, 0, 8), S.ctl, S.scan_desc, S.desc_stride, 7u, 1);
@@ -769,7 +779,7 @@ int enqueue_post(dre_engine* e, const DreStep& S, int cur, cudaStream_t st) {
   k_step_next<<<G, STEP_THREADS, 0, st>>>(S, cur);
   CK(cudaMemcpyAsync(e->h_ctl, S.ctl, sizeof(DreCtl), cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(e->h_err, S.err, sizeof(int), cudaMemcpyDeviceToHost, st));
-  return 6;
+  return split ? 5 : 6;
 }
 
 // the two replayable halves of a step for list parity `cur`; re-captured when a pointer, a capacity or an option changed
@@ -789,8 +799,8 @@ void step_graphs(dre_engine* e, const DreAccum& A, const DreStep& S, int cur) {
   kp(S.nxt); kp(S.hasprev); kp(S.unit_of_ext); kp(S.ntask); kp(S.nreco); kp(S.task_off); kp(S.reco_off); kp(S.reco_cnt); kp(S.keptH);
   kp(S.keptW); kp(S.newHcnt); kp(S.newWcnt); kp(S.fH); kp(S.fW); kp(S.posOH); kp(S.posOW); kp(S.tasks); kp(S.pkts); kp(S.pstride);
   kp(S.capH); kp(S.capW); kp(S.capT); kp(S.ctl); kp(S.scan_desc); kp(S.desc_stride); kp(S.err); kp(S.steps); kp(S.kmax);
-  const int mode = MODE, L = e->g.L, smc = e->sm_count;
-  kp(mode); kp(L); kp(smc);
+  const int mode = MODE, L = e->g.L, smc = e->sm_count, split = e->opt_split;
+  kp(mode); kp(L); kp(smc); kp(split); kp(e->nev.p);
   if (sg.pre && sg.key == key) return;
   if (sg.pre) { cudaGraphExecDestroy(sg.pre); sg.pre = nullptr; }
   if (sg.post) { cudaGraphExecDestroy(sg.post); sg.post = nullptr; }
@@ -800,7 +810,7 @@ void step_graphs(dre_engine* e, const DreAccum& A, const DreStep& S, int cur) {
   CK(cudaStreamEndCapture(e->st, &gr));
   CK(cudaGraphInstantiate(&sg.pre, gr, 0)); CK(cudaGraphDestroy(gr));
   CK(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
-  enqueue_post(e, S, cur, e->st);
+  enqueue_post(e, S, cur, e->st, MODE == MODE_DEP && e->opt_split);
   CK(cudaStreamEndCapture(e->st, &gr));
   CK(cudaGraphInstantiate(&sg.post, gr, 0)); CK(cudaGraphDestroy(gr));
   sg.key = key;
@@ -822,16 +832,28 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
   for (;;) {
     const auto t_0 = std::chrono::steady_clock::now();
     if (MODE == MODE_DEP) ensure_ftab(e, nkmask);
-    if (e->opt_graphs) {
+    if (MODE == MODE_DEP && e->opt_split && e->opt_coop) {
+      // the list side of the step as two cooperative launches around the deposit kernel
+      DreCoop cq; cq.evt = e->evt.p; cq.nev = e->nev.p; cq.evoff = e->evoff.p; cq.capE = e->capE; cq.L = e->g.L;
+      DreAccum Aa = A; DreStep Ss = S; int cc = cur;
+      void* a_pre[] = {&Aa, &Ss, &cc, &cq};
+      CK(cudaLaunchCooperativeKernel((const void*)k_step_pre_coop, dim3(e->sm_count), dim3(SCAN_THREADS), a_pre, 0, e->st));
+      launch_split(e, A, S, false);
+      void* a_post[] = {&Ss, &cc, &cq};
+      CK(cudaLaunchCooperativeKernel((const void*)k_step_post_coop, dim3(e->sm_count), dim3(SCAN_THREADS), a_post, 0, e->st));
+      CK(cudaMemcpyAsync(e->h_ctl, S.ctl, sizeof(DreCtl), cudaMemcpyDeviceToHost, e->st));
+      CK(cudaMemcpyAsync(e->h_err, S.err, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+      e->n_launch += 2;
+    } else if (e->opt_graphs) {
       step_graphs<MODE>(e, A, S, cur);
       CK(cudaGraphLaunch(e->sgraph[MODE == MODE_DEP ? 1 : 0][cur].pre, e->st));
       launch_trace<MODE>(e, A, S);
       CK(cudaGraphLaunch(e->sgraph[MODE == MODE_DEP ? 1 : 0][cur].post, e->st));
-      e->n_launch += 16;
+      e->n_launch += (MODE == MODE_DEP && e->opt_split) ? 15 : 16;
     } else {
       e->n_launch += enqueue_pre<MODE>(e, A, S, cur, e->st);
       launch_trace<MODE>(e, A, S);
-      e->n_launch += enqueue_post(e, S, cur, e->st);
+      e->n_launch += enqueue_post(e, S, cur, e->st, MODE == MODE_DEP && e->opt_split);
     }
     const auto t_1 = std::chrono::steady_clock::now();
     CK(cudaStreamSynchronize(e->st));
@@ -937,19 +959,20 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known in advance.
   // The wavefront buffers hold `cap` entries per list (HIGH and LOW double-buffered, outcomes, tasks, packets, index arrays);
   // cap comes from the entries per unit seen so far (high-water mark per rt_type, kept across passes) and is bounded by
-  // half of the memory left after configuration.  A step that would overflow is refused on the device and repeated after
+  // 60 % of the memory left after configuration.  A step that would overflow is refused on the device and repeated after
   // the buffers have grown (run_batch_mode), so an estimate that is too low costs time, not correctness.
   if (e->list_budget == 0) {     // once per configuration: cudaMemGetInfo costs ~10 ms, and the list buffers are kept afterwards
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
-    e->list_budget = free_b / 2;
+    e->list_budget = (size_t)(0.6 * (double)free_b);
+    e->ftab_budget = std::min(e->ftab_budget, e->ftab_bytes + (size_t)(0.15 * (double)free_b));
   }
   const int L = e->g.L;
   const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0);
   const double max_cap = std::min(2.0e9, std::max(1.0e6, (double)e->list_budget / bytes_per_cap));
   double& est = e->per_unit_est[rt_type % 16];   // max over steps of the per-list need / units
   double per_unit = 0;
-  long long U_next = est > 0 ? (long long)(max_cap / (1.5 * est)) : std::max<long long>(e->opt_batch_units / 4, 3072);
+  long long U_next = est > 0 ? (long long)(max_cap / (1.25 * est)) : std::max<long long>(e->opt_batch_units / 4, 3072);
   U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   for (long long u0 = 0; u0 < mine;) {
     const int U = (int)std::min<long long>(U_next, mine - u0);
@@ -962,7 +985,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries, per-list need %d / %d / %d (%.1f per unit), capacity %d\n",
                                        rt_type, u0, U, bs.peak, bs.maxH, bs.maxW, bs.maxT, per_unit, e->capH);
     u0 += U;
-    U_next = (long long)(max_cap / (1.5 * std::max(per_unit, est)));   // x1.5: headroom for units richer than those seen so far
+    U_next = (long long)(max_cap / (1.25 * std::max(per_unit, est)));   // x1.25: headroom for units richer than those seen so far
     U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   }
   est = std::max(est, per_unit);   // high-water mark (the scattering iterations share one rt_type and shrink)
@@ -1568,6 +1591,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "graphs") e->opt_graphs = value ? 1 : 0;
   else if (s == "cap0") e->opt_cap0 = std::max(0, (int)value);
   else if (s == "split") e->opt_split = value ? 1 : 0;
+  else if (s == "coop") e->opt_coop = value ? 1 : 0;
   else if (s == "scan_chained") { /* accepted for compatibility: every prefix sum is the chained single-launch scan */ }
   else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));

@@ -101,10 +101,10 @@ struct __align__(16) DreRay {
 };
 // A ray packet = [DreRay record (128 B) | direction (32 B) | launch luminosity of every wavelength (8 L B)], `pstride`
 // doubles apart: the march kernel fetches the packet of ray t+1 with ONE TMA bulk copy while it traces ray t.
-template <int MODE>
+template <int MODE, int NT>
 __device__ __forceinline__ void dre_prep_record(const DreDev& g, const DreUnits& u, const DreList& H, const DreList& W,
                                                 const DreTask* __restrict__ tasks, int t, double* __restrict__ pkts, int pstride,
-                                                int (*s_e)[128], int* s_mode, int* s_w, int* s_nc, int* s_dk, int* s_dip) {
+                                                int (*s_e)[NT], int* s_mode, int* s_w, int* s_nc, int* s_dk, int* s_dip) {
   const DreTask tk = tasks[t];
   const int un = tk.unit;
   DreRay q;
@@ -142,8 +142,9 @@ __device__ __forceinline__ void dre_prep_record(const DreDev& g, const DreUnits&
 }
 
 // luminosities of the packets of one block of rays, L consecutive threads per ray (coalesced rows)
+template <int NT>
 __device__ __forceinline__ void dre_prep_lum(const DreDev& g, const DreAccum& A, const DreList& H, const DreList& W, int t0, int nrays,
-                                             double* __restrict__ pkts, int pstride, const int (*s_e)[128], const int* s_mode,
+                                             double* __restrict__ pkts, int pstride, const int (*s_e)[NT], const int* s_mode,
                                              const int* s_w, const int* s_nc, const int* s_dk, const int* s_dip) {
   const int L = g.L;
   for (int idx = threadIdx.x; idx < nrays * L; idx += blockDim.x) {
@@ -172,9 +173,9 @@ __global__ void __launch_bounds__(128) k_prep_rays(DreAccum A, DreStep S, int cu
   const DreList H = S.H[cur], W = S.W[cur];
   for (int t0 = blockIdx.x * 128; t0 < nt; t0 += gridDim.x * 128) {
     const int t = t0 + threadIdx.x;
-    if (t < nt) dre_prep_record<MODE>(g, S.u, H, W, S.tasks, t, S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    if (t < nt) dre_prep_record<MODE, 128>(g, S.u, H, W, S.tasks, t, S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
     __syncthreads();
-    dre_prep_lum(g, A, H, W, t0, min(128, nt - t0), S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    dre_prep_lum<128>(g, A, H, W, t0, min(128, nt - t0), S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
     __syncthreads();
   }
 }

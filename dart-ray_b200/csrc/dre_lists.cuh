@@ -71,17 +71,17 @@ struct ScanJobs { ScanJob j[2]; };
 // scans on the same descriptor region read as "not published", so the region is never cleared.  The ticket counters of a
 // step are cleared by its first kernel.  `skip` (DreCtl::abort) turns the scan into n = 0.
 #define SCAN_DESC(epoch, state, val) (((unsigned long long)(epoch) << 34) | ((unsigned long long)(state) << 32) | (unsigned long long)(unsigned)(val))
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* ctl, unsigned long long* desc_all, int desc_stride,
-                                                            unsigned epoch_off, int skip_on_abort) {
+// One job of the chained scan, run by every block of the calling kernel (blockDim.x == SCAN_THREADS, 1-D blocks).
+__device__ __forceinline__ void dre_scan_job(const ScanJob& jb, DreCtl* ctl, unsigned long long* desc_all, int desc_stride,
+                                             unsigned epoch_off, int skip_on_abort) {
   __shared__ int wsum[SCAN_THREADS / 32];
   __shared__ int s_prefix, s_tile;
-  const ScanJob jb = J.j[blockIdx.y];
   if (jb.out == nullptr) return;
   int n = jb.n_ptr ? *jb.n_ptr : jb.n_const;
   if (skip_on_abort && ctl->abort) return;
   if (n < 0) n = 0;
   const int ntiles = n > 0 ? (n + SCAN_TILE - 1) / SCAN_TILE : 1;
-  unsigned epoch = (ctl->scan_epoch + epoch_off + (unsigned)blockIdx.y) % 0x3fffffffu + 1u;   // never 0: a cleared word reads as unpublished
+  unsigned epoch = (ctl->scan_epoch + epoch_off) % 0x3fffffffu + 1u;   // never 0: a cleared word reads as unpublished
   volatile unsigned long long* d = desc_all + (size_t)jb.slot * desc_stride;
   int* ticket = &ctl->tickets[jb.slot];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -142,13 +142,17 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* 
     __syncthreads();       // wsum / s_tile are reused by the next tile
   }
 }
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* ctl, unsigned long long* desc_all, int desc_stride,
+                                                            unsigned epoch_off, int skip_on_abort) {
+  dre_scan_job(J.j[blockIdx.y], ctl, desc_all, desc_stride, epoch_off + blockIdx.y, skip_on_abort);
+}
 
 // ---------------------------------------------------------------------------------------
 // step kernels
 // ---------------------------------------------------------------------------------------
 // Start of a step: mode of each unit -- extract from HIGH if it has entries, else from LOW (ray_list.f90:120,167) -- and the
 // selection flags of extract_ray_list: HIGH entries with nside == nside/2, LOW entries with nside == 2*nside.
-__global__ void __launch_bounds__(STEP_THREADS) k_step_select(DreStep S, int cur) {
+__device__ __forceinline__ void ph_select(const DreStep& S, int cur) {
   const DreList H = S.H[cur], W = S.W[cur];
   const DreUnits u = S.u;
   const int U = S.ctl->U, nH = H.seg[U], nW = W.seg[U];
@@ -172,7 +176,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_select(DreStep S, int cur
   }
 }
 
-__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_ext(DreStep S, int cur) {
+__device__ __forceinline__ void ph_unit_ext(const DreStep& S, int cur) {
   const DreList H = S.H[cur], W = S.W[cur];
   const DreUnits u = S.u;
   GRID_LOOP(i, S.ctl->U) {
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_unit_ext(DreStep S, int c
 
 // EXT[x] = index of the extracted entry in its old list; for LOW-mode units also the parent
 // pixel at the current nside (ang2pix_nest(nside, theta, phi), ray_list.f90:218) and gone = 0.
-__global__ void __launch_bounds__(STEP_THREADS) k_step_fill_ext(DreStep S, int cur) {
+__device__ __forceinline__ void ph_fill_ext(const DreStep& S, int cur) {
   const DreUnits u = S.u;
   for (int which = 1; which <= 2; which++) {
     const DreList l = (which == 1) ? S.H[cur] : S.W[cur];
@@ -206,7 +210,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_fill_ext(DreStep S, int c
 // sibling search of extract_ray_list (ray_list.f90:237-253): the first <= 3 later entries of the
 // same unit with the same parent pixel, the same isel and dplane within 0.001 (relative to the
 // leader).  `gone` is NOT consulted for the members, as in the reference (SURVEY A.3 note).
-__global__ void __launch_bounds__(STEP_THREADS) k_step_cand(DreStep S, int cur) {
+__device__ __forceinline__ void ph_cand(const DreStep& S, int cur) {
   const DreList w = S.W[cur];
   const DreUnits u = S.u;
   GRID_LOOP(x, S.ext_seg[S.ctl->U]) {
@@ -237,7 +241,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_cand(DreStep S, int cur) 
 // walks each chain in list order (the head is the entry no earlier entry links to).
 //   HIGH-mode entry: 4 child rays, or 1 for a ray_type_reco entry (rt_routines.f90:1389-1403)
 //   LOW-mode leader: 1 merged ray when it has 3 siblings, else the group is re-queued on HIGH (ray_list.f90:255-291)
-__global__ void __launch_bounds__(STEP_THREADS) k_step_resolve(DreStep S, int cur) {
+__device__ __forceinline__ void ph_resolve(const DreStep& S, int cur) {
   const DreList h = S.H[cur];
   const DreUnits u = S.u;
   GRID_LOOP(x0, S.ext_seg[S.ctl->U]) {
@@ -256,7 +260,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_resolve(DreStep S, int cu
 
 // Per-unit task segments (ray ordinal = task index - task_seg[unit]) and reco counts, the capacity check of the step, and
 // the tasks themselves: one per ray_tracing call, in the reference's processing order.
-__global__ void __launch_bounds__(STEP_THREADS) k_step_tasks(DreStep S, int cur) {
+__device__ __forceinline__ void ph_tasks(const DreStep& S, int cur) {
   const DreUnits u = S.u;
   const int U = S.ctl->U, nExt = S.ext_seg[U], nT = S.task_off[nExt], nR = S.reco_off[nExt];
   const int nH = S.H[cur].seg[U], nW = S.W[cur].seg[U];
@@ -288,7 +292,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_tasks(DreStep S, int cur)
   }
 }
 
-__global__ void __launch_bounds__(STEP_THREADS) k_step_out_flags(DreStep S) {
+__device__ __forceinline__ void ph_out_flags(const DreStep& S) {
   if (S.ctl->abort) return;
   GRID_LOOP(t, S.ctl->nT) {
     const int ty = META_TYPE(S.OUT.meta[t]);
@@ -298,7 +302,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_out_flags(DreStep S) {
 }
 
 // sizes of the rebuilt lists: HIGH' = kept ++ reco ++ go_high outcomes ; LOW' = kept ++ go_low outcomes
-__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_new(DreStep S, int cur) {
+__device__ __forceinline__ void ph_unit_new(const DreStep& S, int cur) {
   if (S.ctl->abort) return;
   const DreList H = S.H[cur], W = S.W[cur];
   const DreUnits u = S.u;
@@ -335,7 +339,7 @@ __device__ __forceinline__ int dre_dst_out(const DreStep& S, const DreList& Hn, 
 // Rebuild of both lists in one launch: kept entries (stable), failed merges re-queued on HIGH as ray_type_reco with the
 // current nside (ray_list.f90:276-291, add_to_high_ray_list :463-521), and the go_high / go_low outcomes of the ray-march
 // kernel in task (= processing) order.  The luminosity rows are copied by L consecutive threads per entry (coalesced).
-__global__ void __launch_bounds__(STEP_THREADS) k_step_build(DreStep S, int cur, int L) {
+__device__ __forceinline__ void ph_build(const DreStep& S, int cur, int L) {
   if (S.ctl->abort) return;
   const DreList Hc = S.H[cur], Wc = S.W[cur], Hn = S.H[1 - cur], Wn = S.W[1 - cur];
   const DreUnits u = S.u;
@@ -395,7 +399,7 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_build(DreStep S, int cur,
 }
 
 // define_next_level rt_routines.f90:2745-2770 on the rebuilt lists; the last kernel of a step
-__global__ void __launch_bounds__(STEP_THREADS) k_step_next(DreStep S, int cur) {
+__device__ __forceinline__ void ph_next(const DreStep& S, int cur) {
   DreCtl* c = S.ctl;
   if (blockIdx.x == 0 && threadIdx.x == 0) c->scan_epoch += 16u;
   if (c->abort) return;
@@ -415,3 +419,15 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_next(DreStep S, int cur) 
     atomicOr(&c->nkmask, 1 << u.nk[i]);
   }
 }
+
+// ---- one kernel per phase (the launch sequence of enqueue_pre / enqueue_post, replayed from CUDA graphs)
+__global__ void __launch_bounds__(STEP_THREADS) k_step_select(DreStep S, int cur) { ph_select(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_ext(DreStep S, int cur) { ph_unit_ext(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_fill_ext(DreStep S, int cur) { ph_fill_ext(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_cand(DreStep S, int cur) { ph_cand(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_resolve(DreStep S, int cur) { ph_resolve(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_tasks(DreStep S, int cur) { ph_tasks(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_out_flags(DreStep S) { ph_out_flags(S); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_unit_new(DreStep S, int cur) { ph_unit_new(S, cur); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_build(DreStep S, int cur, int L) { ph_build(S, cur, L); }
+__global__ void __launch_bounds__(STEP_THREADS) k_step_next(DreStep S, int cur) { ph_next(S, cur); }

@@ -18,6 +18,7 @@
 // The geometry costs 1/32 of the issue slots it took when every lane of the ray's warp evaluated it redundantly, and the
 // deposit warps no longer wait for cell records or carry the geometry in registers.
 #pragma once
+#include <cooperative_groups.h>
 #include "dre_kernels.cuh"
 
 struct __align__(8) DreEvt { double length, psel; int cc; unsigned info; };   // info = clvl | kind << 4 | wall_hit << 6
@@ -179,45 +180,108 @@ __device__ __forceinline__ int dre_geom_march(const DreDev& g, const DreAccum& A
     const DreList& out = S.OUT;
     out.unit[t] = un; out.dir_ipix[t] = dip; out.meta[t] = dre_meta(dk, nk, o_isel_old, ty);
     out.cc_old[t] = o_cc; out.dplane[t] = o_dplane; out.prev[t] = o_prev;
+    S.fH[t] = 0; S.fW[t] = (term == TERM_LOW) ? 1 : 0;      // outcome flags of the list rebuild (k_deposit sets fH for a split)
   }
   return nev;
 }
 
-// pass 0: nev[t] = events of ray t.  pass 1: events written at evoff[t] (prefix sum of nev), or the whole step refused
-// when they do not fit the event buffer.
-template <int WRITE>
-__global__ void __launch_bounds__(128) k_geom(DreAccum A, DreStep S, DreEvt* __restrict__ evt, int* __restrict__ nev,
-                                              const int* __restrict__ evoff, int capE) {
+// Ray packets of a step (k_prep_rays) and pass 0 of the march together: the thread that resolves a ray's record walks it
+// at once and leaves the number of its events in nev[t].  NT = threads per block of the calling kernel.
+template <int NT>
+__device__ __forceinline__ void ph_prep_geom(const DreAccum& A, const DreStep& S, int cur, int* __restrict__ nev) {
+  const DreDev& g = c_g;
+  __shared__ int s_e[4][NT], s_mode[NT], s_w[NT], s_nc[NT], s_dk[NT], s_dip[NT];
+  if (S.ctl->abort) return;
+  const int nt = S.ctl->nT;
+  const DreList H = S.H[cur], W = S.W[cur];
+  for (int t0 = blockIdx.x * NT; t0 < nt; t0 += gridDim.x * NT) {
+    const int t = t0 + threadIdx.x;
+    if (t < nt) dre_prep_record<MODE_DEP, NT>(g, S.u, H, W, S.tasks, t, S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    __syncthreads();
+    dre_prep_lum<NT>(g, A, H, W, t0, min(NT, nt - t0), S.pkts, S.pstride, s_e, s_mode, s_w, s_nc, s_dk, s_dip);
+    if (t < nt) { GeomCnt gc; gc.isect = gc.desc = gc.hash = 0; nev[t] = dre_geom_march<0>(g, A, S, t, S.pkts + (size_t)t * S.pstride, nullptr, gc); }
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(128) k_prep_geom(DreAccum A, DreStep S, int cur, int* __restrict__ nev) { ph_prep_geom<128>(A, S, cur, nev); }
+
+// Pass 1 of the march: events written at evoff[t] (prefix sum of nev), or the whole step refused when they do not fit the
+// event buffer.
+__device__ __forceinline__ void ph_geom_write(const DreAccum& A, const DreStep& S, DreEvt* __restrict__ evt, const int* __restrict__ evoff, int capE) {
   const DreDev& g = c_g;
   DreCtl* c = S.ctl;
   const int nt = c->nT;
   if (nt <= 0 || c->abort) return;
-  if (WRITE) {
-    const int nE = evoff[nt];
-    if (nE > capE || nE < 0) {
-      if (blockIdx.x == 0 && threadIdx.x == 0) { c->needE = nE < 0 ? 0x7fffffff : nE; c->abort = 1; c->nT = 0; }
-      return;
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) c->needE = nE;
+  const int nE = evoff[nt];
+  if (nE > capE || nE < 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->needE = nE < 0 ? 0x7fffffff : nE; c->abort = 1; c->nT = 0; }
+    return;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0) c->needE = nE;
   GeomCnt gc; gc.isect = gc.desc = gc.hash = 0;
   unsigned long long rays = 0;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nt; t += gridDim.x * blockDim.x) {
     double* pk = S.pkts + (size_t)t * S.pstride;
-    const int n = dre_geom_march<WRITE>(g, A, S, t, pk, WRITE ? evt + evoff[t] : nullptr, gc);
-    if (WRITE) { reinterpret_cast<int*>(pk)[PKT_EVOFF] = evoff[t]; rays++; }
-    else nev[t] = n;
+    dre_geom_march<1>(g, A, S, t, pk, evt + evoff[t], gc);
+    reinterpret_cast<int*>(pk)[PKT_EVOFF] = evoff[t]; rays++;
   }
-  if (WRITE) {
-    for (int o = 16; o > 0; o >>= 1) {
-      gc.isect += __shfl_xor_sync(0xffffffffu, gc.isect, o); gc.desc += __shfl_xor_sync(0xffffffffu, gc.desc, o);
-      gc.hash += __shfl_xor_sync(0xffffffffu, gc.hash, o); rays += __shfl_xor_sync(0xffffffffu, rays, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-      atomicAdd(&A.counters[CNT_ISECT], gc.isect); atomicAdd(&A.counters[CNT_DESC], gc.desc);
-      atomicAdd(&A.counters[CNT_HASH], gc.hash); atomicAdd(&A.counters[CNT_RAYS], rays);
-    }
+  for (int o = 16; o > 0; o >>= 1) {
+    gc.isect += __shfl_xor_sync(0xffffffffu, gc.isect, o); gc.desc += __shfl_xor_sync(0xffffffffu, gc.desc, o);
+    gc.hash += __shfl_xor_sync(0xffffffffu, gc.hash, o); rays += __shfl_xor_sync(0xffffffffu, rays, o);
   }
+  if ((threadIdx.x & 31) == 0 && rays != 0) {
+    atomicAdd(&A.counters[CNT_ISECT], gc.isect); atomicAdd(&A.counters[CNT_DESC], gc.desc);
+    atomicAdd(&A.counters[CNT_HASH], gc.hash); atomicAdd(&A.counters[CNT_RAYS], rays);
+  }
+}
+__global__ void __launch_bounds__(128) k_geom_write(DreAccum A, DreStep S, DreEvt* __restrict__ evt, const int* __restrict__ evoff, int capE) {
+  ph_geom_write(A, S, evt, evoff, capE);
+}
+
+// ---- the whole list side of a step in two cooperative launches (grid-wide barriers between the phases instead of kernel
+// boundaries): a small step is bound by the latency of its chain of launches, not by work.
+//   k_step_pre_coop : select, scans, extraction, sibling search, leader resolution, tasks, ray packets + march pass 0, event
+//                     offsets, march pass 1      (then k_deposit, which needs its own shared-memory configuration)
+//   k_step_post_coop: outcome scans, new list sizes, scans, rebuild, define_next_level
+struct DreCoop { DreEvt* evt; int* nev; int* evoff; int capE; int L; };
+__global__ void __launch_bounds__(SCAN_THREADS, 1) k_step_pre_coop(DreAccum A, DreStep S, int cur, DreCoop q) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  DreCtl* c = S.ctl;
+  unsigned long long* D = S.scan_desc; const int ds = S.desc_stride;
+  ScanJob j; j.n_const = 0; j.total_out = nullptr;
+  ph_select(S, cur); grid.sync();
+  j.in = S.selH; j.out = S.posH; j.n_ptr = &c->nH; j.slot = 0; dre_scan_job(j, c, D, ds, 0u, 0);
+  j.in = S.selW; j.out = S.posW; j.n_ptr = &c->nW; j.slot = 1; dre_scan_job(j, c, D, ds, 1u, 0);
+  grid.sync();
+  ph_unit_ext(S, cur); grid.sync();
+  j.in = S.extcnt; j.out = S.ext_seg; j.n_ptr = &c->U; j.slot = 2; j.total_out = &c->nExt; dre_scan_job(j, c, D, ds, 2u, 0); j.total_out = nullptr;
+  grid.sync();
+  ph_fill_ext(S, cur); grid.sync();
+  ph_cand(S, cur); grid.sync();
+  ph_resolve(S, cur); grid.sync();
+  j.in = S.ntask; j.out = S.task_off; j.n_ptr = &c->nExt; j.slot = 3; dre_scan_job(j, c, D, ds, 3u, 0);
+  j.in = S.nreco; j.out = S.reco_off; j.n_ptr = &c->nExt; j.slot = 4; dre_scan_job(j, c, D, ds, 4u, 0);
+  grid.sync();
+  ph_tasks(S, cur); grid.sync();
+  ph_prep_geom<SCAN_THREADS>(A, S, cur, q.nev); grid.sync();
+  j.in = q.nev; j.out = q.evoff; j.n_ptr = &c->nT; j.slot = 10; dre_scan_job(j, c, D, ds, 10u, 1);
+  grid.sync();
+  ph_geom_write(A, S, q.evt, q.evoff, q.capE);
+}
+__global__ void __launch_bounds__(SCAN_THREADS, 1) k_step_post_coop(DreStep S, int cur, DreCoop q) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  DreCtl* c = S.ctl;
+  unsigned long long* D = S.scan_desc; const int ds = S.desc_stride;
+  ScanJob j; j.n_const = 0; j.total_out = nullptr;
+  j.in = S.fH; j.out = S.posOH; j.n_ptr = &c->nT; j.slot = 5; dre_scan_job(j, c, D, ds, 5u, 1);
+  j.in = S.fW; j.out = S.posOW; j.n_ptr = &c->nT; j.slot = 6; dre_scan_job(j, c, D, ds, 6u, 1);
+  grid.sync();
+  ph_unit_new(S, cur); grid.sync();
+  j.in = S.newHcnt; j.out = S.H[1 - cur].seg; j.n_ptr = &c->U; j.slot = 7; dre_scan_job(j, c, D, ds, 7u, 1);
+  j.in = S.newWcnt; j.out = S.W[1 - cur].seg; j.n_ptr = &c->U; j.slot = 8; dre_scan_job(j, c, D, ds, 8u, 1);
+  grid.sync();
+  ph_build(S, cur, q.L); grid.sync();
+  ph_next(S, cur);
 }
 
 // per-ray inputs of the deposit walk
@@ -465,6 +529,12 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_deposit(DreAccum A, Dr
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nt = S.ctl->nT;
   if (nt <= 0 || S.ctl->abort) return;
+  // a small step: the warps of the first CTAs cover every ray, the other CTAs leave before they set up shared memory
+  if ((long long)blockIdx.x * (blockDim.x >> 5) >= nt) return;
+  __shared__ unsigned long long s_cnt[8];
+  __shared__ double s_lost[32 * DRE_KL];
+  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x < 32 * DRE_KL) s_lost[threadIdx.x] = 0;
   const double* __restrict__ pkts = S.pkts;
   const int pstride = S.pstride;
   const DreList out = S.OUT;
@@ -525,7 +595,7 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_deposit(DreAccum A, Dr
       atomicAdd(&A.psel_sum[sid], st.psel);
       atomicAdd((unsigned long long*)&A.ipsel[sid], (unsigned long long)st.npsel);
     }
-    if (okind == OUT_HIGH && lane == 0) out.meta[t] = (out.meta[t] & 0x00ffffffu) | ((unsigned)RT_HIGH << 24);
+    if (okind == OUT_HIGH && lane == 0) { out.meta[t] = (out.meta[t] & 0x00ffffffu) | ((unsigned)RT_HIGH << 24); S.fH[t] = 1; }
     if (okind != OUT_NONE) {
 #pragma unroll
       for (int k = 0; k < KL; k++) {
@@ -538,16 +608,22 @@ __global__ void __launch_bounds__(DRE_TRACE_THREADS, 1) k_deposit(DreAccum A, Dr
   }
   if (ws.fwait) { mbar_wait(ws.mbar, ws.fphase); ws.fwait = 0; }
   if (lane == 0) bulk_wait_all();
+  // lum_lost and the event counters are reduced per CTA in shared memory, then added to the device totals once
+  // (rays / intersections / descent loads / checksum are counted by k_geom)
 #pragma unroll
   for (int k = 0; k < KL; k++) {
     const int l = lane + 32 * k;
-    if (k < g.KLn && l < L && lost[k] != 0) atomicAdd(&A.lum_lost[l], lost[k]);
+    if (k < g.KLn && l < L && lost[k] != 0) atomicAdd(&s_lost[l], lost[k]);
   }
-  // rays / intersections / descent loads / checksum are counted by k_geom
   if (lane == 0) {
-    atomicAdd(&A.counters[CNT_DEP], st.dep); atomicAdd(&A.counters[CNT_BEAM], st.beam);
-    atomicAdd(&A.counters[CNT_SPLIT], st.split); atomicAdd(&A.counters[CNT_MERGE], st.merge);
-    atomicAdd(&A.counters[CNT_SCA], st.sca); atomicAdd(&A.counters[CNT_ACT], st.act);
-    atomicAdd(&A.counters[CNT_ACTDEP], st.actdep);
+    atomicAdd(&s_cnt[0], st.dep); atomicAdd(&s_cnt[1], st.beam); atomicAdd(&s_cnt[2], st.split); atomicAdd(&s_cnt[3], st.merge);
+    atomicAdd(&s_cnt[4], st.sca); atomicAdd(&s_cnt[5], st.act); atomicAdd(&s_cnt[6], st.actdep);
   }
+  __syncthreads();
+  if (threadIdx.x < 7 && s_cnt[threadIdx.x] != 0) {
+    const int idx = (threadIdx.x == 0) ? CNT_DEP : (threadIdx.x == 1) ? CNT_BEAM : (threadIdx.x == 2) ? CNT_SPLIT : (threadIdx.x == 3) ? CNT_MERGE
+                  : (threadIdx.x == 4) ? CNT_SCA : (threadIdx.x == 5) ? CNT_ACT : CNT_ACTDEP;
+    atomicAdd(&A.counters[idx], s_cnt[threadIdx.x]);
+  }
+  if (threadIdx.x < L && s_lost[threadIdx.x] != 0) atomicAdd(&A.lum_lost[threadIdx.x], s_lost[threadIdx.x]);
 }
