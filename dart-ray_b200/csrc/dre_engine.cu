@@ -10,6 +10,7 @@
 #include "dre_kernels.cuh"
 #include "dre_split.cuh"
 #include "dre_maps.cuh"
+#include "dre_dust.cuh"
 
 namespace {
 
@@ -92,7 +93,7 @@ struct dre_engine {
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 1, opt_det = 0;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_det = 0;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -1211,6 +1212,42 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   if (iterations > 1) (e->n_launch++, k_add_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->tot.p, e->acc.p, g.N, g.ROW, g.L);
   (e->n_launch++, k_zero_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->acc.p, g.N, g.ROW, g.L);
   CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
+int dre_dust_emission(dre_engine* e, int32_t ls, int32_t ld, const double* kabs_stars, const double* kabs_dust, const double* lambda_si_dust,
+                      const double* dl_stars, const double* dl_dust, double kext_ref, const double* dens_ref, const double* rf_stars,
+                      const double* rf_dust, int32_t iterations_dustem, double* dens_stars, double* t_dust, int32_t to_lumcell) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_grid && e->have_opacity, "dre_dust_emission: grid / opacity not set");
+  const DreDev& g = e->g;
+  DRE_REQUIRE(ls >= 1 && ld >= 1 && ld <= 4096, "dre_dust_emission: bad wavelength counts");
+  DRE_REQUIRE(kabs_stars && kabs_dust && lambda_si_dust && dl_stars && dl_dust && dens_ref && rf_stars && dens_stars, "dre_dust_emission: null input");
+  DRE_REQUIRE(kext_ref != 0, "dre_dust_emission: kext_ref is zero");
+  const bool resident = (rf_dust == nullptr) && iterations_dustem > 0;
+  DRE_REQUIRE(!(resident || to_lumcell) || g.L == ld, "dre_dust_emission: the engine is not configured for the dust-emission wavelengths (lnum != lnum_dust)");
+  const size_t N = g.N;
+  DBuf<double> d_ks, d_kd, d_lam, d_dls, d_dld, d_ref, d_rfs, d_rfd, d_out, d_t;
+  d_ks.upload(kabs_stars, ls, e->st); d_kd.upload(kabs_dust, ld, e->st); d_lam.upload(lambda_si_dust, ld, e->st);
+  d_dls.upload(dl_stars, ls, e->st); d_dld.upload(dl_dust, ld, e->st); d_ref.upload(dens_ref, N, e->st);
+  d_rfs.upload(rf_stars, N * ls, e->st);
+  if (rf_dust && iterations_dustem > 0) d_rfd.upload(rf_dust, N * ld, e->st);
+  d_out.ensure(N * ld); d_t.zero(N, e->st);
+  e->errflag.zero(1, e->st);
+  DreDust q; memset(&q, 0, sizeof(q));
+  q.N = g.N; q.ls = ls; q.ld = ld; q.kabs_s = d_ks.p; q.kabs_d = d_kd.p; q.lam_d = d_lam.p; q.dl_s = d_dls.p; q.dl_d = d_dld.p;
+  q.dens_ref = d_ref.p; q.cchild = e->cchild.p; q.csize = e->csize.p; q.rf_s = d_rfs.p; q.rf_d = d_rfd.p; q.rows = e->acc.p; q.ROW = g.ROW;
+  q.kext_ref = kext_ref; q.iterations_dustem = iterations_dustem; q.dens_stars = d_out.p; q.t_dust = d_t.p;
+  q.lumcell = to_lumcell ? e->lumcell.p : nullptr; q.err = e->errflag.p;
+  (e->n_launch++, k_dust_emission)<<<cdiv(N, 128), 128, (size_t)3 * ld * sizeof(double), e->st>>>(q);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(dens_stars, d_out.p, N * ld * 8, cudaMemcpyDeviceToHost, e->st));
+  if (t_dust) CK(cudaMemcpyAsync(t_dust, d_t.p, N * 8, cudaMemcpyDeviceToHost, e->st));
+  const int herr = read_int(e, e->errflag.p);
+  DRE_REQUIRE(herr == 0, herr == 6 ? "calc_t_dust_equil: negative absorbed energy (sed_routines.f90:865)"
+                                   : (herr == 7 ? "zbrent_tdust: root not bracketed (sed_routines.f90:1005)" : "zbrent_tdust: too many iterations (sed_routines.f90:1071)"));
+  if (to_lumcell) e->have_sources = e->have_sources;   // lumcell now holds the dust emission; point sources are untouched
   DRE_CATCH(e)
 }
 

@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("DARTRAY_ENGINE_LIB", os.path.join(_HERE, "libdartray_
 SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
-    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
+    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_dust_emission", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
     "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_get_quanta", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
@@ -254,6 +254,21 @@ class Engine:
         self._ck(self.l.dre_prepare_scatt(self.h, C.c_int(iterations), C.c_double(self.scene.conv_en_lim),
                                           abi.dptr(tot_rad_en), C.byref(flag)))
         return bool(flag.value)
+
+    def dust_emission(self, kabs_stars, kabs_dust, lambda_si_dust, dl_stars, dl_dust, kext_ref, dens_ref, rf_stars, rf_dust=None,
+                      iterations_dustem=0, to_lumcell=False):
+        """set_dust_emission, 'eff' mode (sed_routines.f90:249-276, 377-430): returns (dens_stars (N, lnum_dust), t_dust (N)).
+        rf_dust None with iterations_dustem > 0: the device-resident u_final of the last dust pass is used."""
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        ks, kd, lam, dls, dld, ref, rfs = map(f, (kabs_stars, kabs_dust, lambda_si_dust, dl_stars, dl_dust, dens_ref, rf_stars))
+        rfd = None if rf_dust is None else f(rf_dust)
+        N = self.scene.grid.ncell
+        out = np.zeros((N, len(kd))); t = np.zeros(N)
+        self._ck(self.l.dre_dust_emission(self.h, C.c_int32(len(ks)), C.c_int32(len(kd)), abi.dptr(ks), abi.dptr(kd), abi.dptr(lam),
+                                          abi.dptr(dls), abi.dptr(dld), C.c_double(kext_ref), abi.dptr(ref), abi.dptr(rfs),
+                                          abi.dptr(rfd) if rfd is not None else None, C.c_int32(iterations_dustem), abi.dptr(out),
+                                          abi.dptr(t), C.c_int32(1 if to_lumcell else 0)))
+        return out, t
 
     # ---- separate small kernels -----------------------------------------------------------
     def build_source_list(self, rt_type):

@@ -554,3 +554,15 @@ def galaxy_scene(max_lvl=4, min_lvl=2, lnum=None, kp_sca_max=1, max_dtau=0.01, m
                  cell_src=np.zeros(0, dtype=np.int32), bm_par=5, bm_par_sca=5, bm_par_max=200, rad_lim=0.1,
                  accuracy=0.3, conv_en_lim=0.01, wall_on=(0, 0, 1),
                  wall_coord=(0.0, 0.0, 0.0, 0.0, 0.3 * ms - ms / 2.0, 0.7 * ms - ms / 2.0))
+
+
+def delta_lambda_bins(lambda_si):
+    """delta_lambda_bin of set_lambda_arr_si (sed_routines.f90:974-978): bin edges at the logarithmic mid-points of the
+    wavelength list, first / last bin closed at the first / last wavelength."""
+    lam = np.asarray(lambda_si, dtype=np.float64)
+    edges = 10.0 ** ((np.log10(lam[1:]) + np.log10(lam[:-1])) / 2.0)
+    d = np.empty_like(lam)
+    d[1:-1] = edges[1:] - edges[:-1]
+    d[0] = edges[0] - lam[0]
+    d[-1] = lam[-1] - edges[-1]
+    return d

@@ -15,6 +15,7 @@
  *   dre_allreduce  <- rt_mpi + reduce_*  io_routines.f90:3667-3881
  *   dre_prepare_scatt <- rt_prepare(rtt_scatt) + calc_total_luminosity_sca
  *                                        dartray_hub.f90:432-457, rt_routines.f90:663-758
+ *   dre_dust_emission <- set_dust_emission ('eff')  sed_routines.f90:249-276, 377-430
  *
  * Return value: 0 on success, non-zero on error (message via dre_last_error);
  * the Fortran wrapper calls stop_prc (smooth_grid_routines.f90:869) on non-zero.
@@ -168,6 +169,22 @@ int dre_make_maps(dre_engine*, int npixel_maps, double map_size_factor, int unit
  * nside 2**kp_maps.  maps_in is map_in_arr_out(0:12*4**kp_maps-1, 0:lnum-1, 0:tot_ndir_in-1), column-major, MJy/sr. */
 int dre_make_maps_in(dre_engine*, int32_t ndir_in, const double* ccoord_obs /*(3,ndir_in)*/, int kp_maps, int units,
                      const double* lambda_si /*(L) or NULL*/, double* maps_in /*(npix_maps,L,ndir_in) out*/);
+
+/* set_dust_emission, dust_heating_type 'eff' (sed_routines.f90:249-276: calc_dens_dustem :377-430, calc_t_dust_equil :846-874,
+ * zbrent_tdust :993-1078, bplanck :939-948, set_units_dens_stars_arr :904-914): the dust-emission luminosity density of every
+ * dusty leaf cell from the radiation field it absorbs.  The engine must be configured for the dust-emission wavelengths
+ * (dre_set_opacity with lnum = lnum_dust).
+ *   kabs_stars (lnum_stars) = kabs_arr(0:lnum_stars-1), kabs_dust (lnum_dust) = kabs_arr(i0:), lambda_si_dust = lambda_arr_SI(i0:),
+ *   dl_stars / dl_dust = delta_lambda_bin_stars / _dust, rf_stars (lnum_stars, N) = u_final_uv_opt after convert_ufield_ifield,
+ *   rf_dust (lnum_dust, N) = u_final_arr/parsec^3*cspeed, or NULL to read the device-resident u_final of the last dust pass
+ *   (ignored when iterations_dustem == 0, sed_routines.f90:857).
+ * Out: dens_stars (lnum_dust, N) [W/m/pc^3], t_dust (N) or NULL; to_lumcell != 0 also leaves lumcell = dens_stars * csize^3 on the
+ * device (calc_total_luminosity rt_routines.f90:605-660), ready for the next rtt_precalc_cell / rtt_dir_cell pass. */
+int dre_dust_emission(dre_engine*, int32_t lnum_stars, int32_t lnum_dust, const double* kabs_stars, const double* kabs_dust,
+                      const double* lambda_si_dust, const double* dl_stars, const double* dl_dust, double kext_ref,
+                      const double* dens_ref /*(N)*/, const double* rf_stars /*(lnum_stars,N)*/, const double* rf_dust /*(lnum_dust,N) or NULL*/,
+                      int32_t iterations_dustem, double* dens_stars /*(lnum_dust,N) out*/, double* t_dust /*(N) out or NULL*/,
+                      int32_t to_lumcell);
 
 /* ---- separate small kernels (north star: cell-list and bounding-box kernels) */
 /* leaf && sum(lum)>0 gate of rt_loop rt_routines.f90:1016; returns the list length */

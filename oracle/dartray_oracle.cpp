@@ -1169,6 +1169,84 @@ int orc_run_iobs(orc_ctx* o, int rt_type, const double* const* scaspe_tot, int32
 
 // rt_prepare(rtt_scatt) dartray_hub.f90:432-457 + calc_total_luminosity_sca rt_routines.f90:663-758
 // (no_communications + sequential_scattering).  lumcell is stored in the context for the next pass.
+// ---- N4: set_dust_emission, dust_heating_type 'eff' (sed_routines.f90:249-276) ---------------------------------------
+namespace dustem {
+const double parsec = (double)3.08567758E16f, cspeed = (double)2.99792458E8f;       // smooth_grid_routines.f90:373-377
+const double hplanck = (double)6.62606957E-34f, kboltz = (double)1.3806488E-23f;   // :440-443
+// bplanck sed_routines.f90:939-948
+double bplanck(double t_source, double la) {
+  double a1 = 2 * hplanck * pow(cspeed, 2.) / pow(la, 5.);
+  double a2 = exp(hplanck * cspeed / (la * kboltz * t_source)) - 1;
+  return a1 * pow(a2, -1.);
+}
+// abs_en_diff :917-936 (em_int is the caller's work array)
+double abs_en_diff(double t_dust, const double* kabs_arr_planck, double abs_en, std::vector<double>& em_int, const double* lambda_si_dust,
+                   const double* delta_lambda_bin_dust) {
+  const int lnum = (int)em_int.size();
+  for (int i = 0; i < lnum; i++) em_int[i] = (kabs_arr_planck[i] * bplanck(t_dust, lambda_si_dust[i]));
+  double em_en = 0;
+  for (int i = 0; i < lnum; i++) em_en += em_int[i] * delta_lambda_bin_dust[i];
+  em_en = 4 * PI * em_en;
+  return em_en - abs_en;
+}
+// ZBRENT_tdust :993-1078.  t0 = 0, t1 = 1E4 (sed_routines.f90:9-11); EPS = 3.E-16 (default real); TOL is implicitly typed and
+// never assigned in the reference (undefined there; 0 here).  Returns false on the reference's two STOP conditions.
+bool zbrent_tdust(const double* kabs_arr_planck, double abs_en, int lnum, const double* lambda_si_dust, const double* dl_dust, double& root) {
+  const int ITMAX = 100; const double EPS = (double)3.E-16f, TOL = 0.0;
+  std::vector<double> em_int(lnum);
+  double A = 0.0, B = (double)1E4f, C = 0, D = 0, E = 0;
+  double FA = abs_en_diff(A, kabs_arr_planck, abs_en, em_int, lambda_si_dust, dl_dust);
+  double FB = abs_en_diff(B, kabs_arr_planck, abs_en, em_int, lambda_si_dust, dl_dust);
+  if (FB * FA > 0.) return false;
+  double FC = FB;
+  for (int ITER = 1; ITER <= ITMAX; ITER++) {
+    if (FB * FC > 0.) { C = A; FC = FA; D = B - A; E = D; }
+    if (fabs(FC) < fabs(FB)) { A = B; B = C; C = A; FA = FB; FB = FC; FC = FA; }
+    double TOL1 = 2. * EPS * fabs(B) + 0.5 * TOL;
+    double XM = .5 * (C - B);
+    if (fabs(XM) <= TOL1 || FB == 0.) { root = B; return true; }
+    if (fabs(E) >= TOL1 && fabs(FA) > fabs(FB)) {
+      double P, Q, R, S = FB / FA;
+      if (A == C) { P = 2. * XM * S; Q = 1. - S; }
+      else { Q = FA / FC; R = FB / FC; P = S * (2. * XM * Q * (Q - R) - (B - A) * (R - 1.)); Q = (Q - 1.) * (R - 1.) * (S - 1.); }
+      if (P > 0.) Q = -Q;
+      P = fabs(P);
+      if (2. * P < std::min(3. * XM * Q - fabs(TOL1 * Q), fabs(E * Q))) { E = D; D = P / Q; }
+      else { D = XM; E = D; }
+    } else { D = XM; E = D; }
+    A = B; FA = FB;
+    if (fabs(D) > TOL1) B = B + D; else B = B + copysign(TOL1, XM);
+    FB = abs_en_diff(B, kabs_arr_planck, abs_en, em_int, lambda_si_dust, dl_dust);
+  }
+  return false;
+}
+}  // namespace dustem
+
+// calc_dens_dustem sed_routines.f90:377-430 + set_units_dens_stars_arr :904-914.  rf_dust may be null when iterations_dustem == 0.
+int orc_dust_emission(orc_ctx* o, int32_t lnum_stars, int32_t lnum_dust, const double* kabs_stars, const double* kabs_dust,
+                      const double* lambda_si_dust, const double* dl_stars, const double* dl_dust, double kext_ref, const double* dens_ref,
+                      const double* rf_stars, const double* rf_dust, int32_t iterations_dustem, double* dens_stars, double* t_dust_out) {
+  Ctx& c = o->c;
+  int bad = 0;
+  for (int i = 0; i < c.N; i++) {
+    for (int j = 0; j < lnum_dust; j++) dens_stars[(size_t)lnum_dust * i + j] = 0;
+    if (t_dust_out) t_dust_out[i] = 0;
+    if (c.cchild[i] != -1 || dens_ref[i] == 0) continue;
+    // calc_t_dust_equil :846-874
+    double abs_en = 0;
+    { double s = 0; for (int l = 0; l < lnum_stars; l++) s += (kabs_stars[l] * rf_stars[(size_t)lnum_stars * i + l]) * dl_stars[l]; abs_en = s; }
+    { double s = 0; if (iterations_dustem > 0) for (int l = 0; l < lnum_dust; l++) s += (kabs_dust[l] * rf_dust[(size_t)lnum_dust * i + l]) * dl_dust[l]; abs_en = abs_en + s; }
+    if (abs_en < 0) { bad = 1; continue; }
+    double t_dust = 0;
+    if (!dustem::zbrent_tdust(kabs_dust, abs_en, lnum_dust, lambda_si_dust, dl_dust, t_dust)) { bad = 2; continue; }
+    for (int j = 0; j < lnum_dust; j++)
+      dens_stars[(size_t)lnum_dust * i + j] = 4 * PI * kabs_dust[j] / kext_ref * dens_ref[i] * dustem::bplanck(t_dust, lambda_si_dust[j]) * pow(dustem::parsec, 2.);
+    if (t_dust_out) t_dust_out[i] = t_dust;
+  }
+  if (bad) { c.err = bad == 1 ? "calc_t_dust_equil: negative absorbed energy" : "zbrent_tdust: root not bracketed / too many iterations"; return 2; }
+  return 0;
+}
+
 int orc_prepare_scatt(orc_ctx* o, int iterations, double conv_en_lim, double* u_fest, const double* u_final,
                       double* lum_lost_prev, const double* lum_lost, double* const* scaspe, double* const* scaspe_prev,
                       double* const* scaspe_tot, double* tot_rad_en, int32_t* cnflag) {

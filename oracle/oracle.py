@@ -183,6 +183,21 @@ class Oracle:
                                C.c_int(level), abi.dptr(prof), C.c_int(nt * nt), info.ctypes.data_as(C.c_void_p), abi.dptr(axes))
         return prof, int(info[0]), int(info[1]), axes
 
+    def dust_emission(self, kabs_stars, kabs_dust, lambda_si_dust, dl_stars, dl_dust, kext_ref, dens_ref, rf_stars, rf_dust=None,
+                      iterations_dustem=0):
+        """set_dust_emission 'eff' (sed_routines.f90:249-276, 377-430): (dens_stars (N, lnum_dust), t_dust (N))."""
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        ks, kd, lam, dls, dld, ref, rfs = map(f, (kabs_stars, kabs_dust, lambda_si_dust, dl_stars, dl_dust, dens_ref, rf_stars))
+        rfd = None if rf_dust is None else f(rf_dust)
+        N = self.scene.grid.ncell
+        out = np.zeros((N, len(kd))); t = np.zeros(N)
+        rc = self.l.orc_dust_emission(self.h, C.c_int32(len(ks)), C.c_int32(len(kd)), abi.dptr(ks), abi.dptr(kd), abi.dptr(lam), abi.dptr(dls),
+                                      abi.dptr(dld), C.c_double(kext_ref), abi.dptr(ref), abi.dptr(rfs),
+                                      abi.dptr(rfd) if rfd is not None else None, C.c_int32(iterations_dustem), abi.dptr(out), abi.dptr(t))
+        if rc != 0:
+            raise RuntimeError(self.l.orc_last_error(self.h).decode())
+        return out, t
+
     def prepare_scatt(self, iterations, st):
         flag = C.c_int32(0)
         self.l.orc_prepare_scatt(self.h, C.c_int(iterations), C.c_double(self.scene.conv_en_lim), abi.dptr(st.u_fest),

@@ -58,8 +58,8 @@ OPTION_SETS = {
     "stage_quarters": (("stage_split", 4), ("warps", 8)),
     "whole_row_stage": (("stage_split", 1), ("warps", 4)),
     "fused_march": (("split", 0),),                     # geometry and deposits in one warp-per-ray kernel (the round-1 form) instead of k_geom + k_deposit
-    "no_coop": (("coop", 0),),                          # list kernels replayed from CUDA graphs instead of the two cooperative launches
-    "no_graphs": (("graphs", 0), ("coop", 0)),                      # the kernels of a step launched one by one instead of replayed from CUDA graphs
+    "coop_lists": (("coop", 1),),                       # the list side of a step as two cooperative launches (grid-wide barriers) instead of graph-replayed kernels
+    "no_graphs": (("graphs", 0),),                      # the kernels of a step launched one by one instead of replayed from CUDA graphs
     "refused_steps": (("cap0", 64), ("batch_units", 960)),   # list buffers start at 64 entries: steps are refused on the device and repeated after growth
     "one_ray_chunks": (("chunk", 1), ("ctas_per_sm", 2)),
 }
