@@ -47,6 +47,10 @@ def load_scene(name):
     if name == "magtar":
         sc = scenes.magtar_scene()
         return sc, f"MAGTAR ellipsoidal shell (input_shell.in): {sc.grid.ncell} cells, {sc.lnum} wavelengths, 1 point source"
+    if name == "nbody":
+        sc = scenes.nbody_scene()
+        return sc, (f"N-body/SPH-shaped grid (input_nbody_example1.in parameters, seeded synthetic particles): {sc.grid.ncell} cells, "
+                    f"{int((sc.lumcell.sum(axis=1) > 0).sum())} emitting leaf cells, {sc.lnum} wavelengths")
     fn = getattr(scenes, name + "_scene", None)
     if fn is None:
         raise SystemExit(f"unknown workload {name}")
@@ -55,26 +59,64 @@ def load_scene(name):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md).  Sampled in-process through NVML (the library
+    nvidia-smi itself uses): spawning nvidia-smi every 200 ms steals host time from the rank that enqueues the solve, which shows
+    up as load imbalance at 8 GPUs.  Falls back to the nvidia-smi command line when the NVML binding is missing."""
+
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         self.index = index
-        self.rows = []
+        self.rows = []           # (sm_mhz, sm_max_mhz, [active reason names])
         self.stop = threading.Event()
         self.th = None
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.bits = [(pynvml.nvmlClocksEventReasonHwSlowdown, "hw_slowdown"), (pynvml.nvmlClocksEventReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                         (pynvml.nvmlClocksEventReasonSwThermalSlowdown, "sw_thermal_slowdown"), (pynvml.nvmlClocksEventReasonSwPowerCap, "sw_power_cap")]
+        except Exception:
+            self.nvml = None
 
-    def _run(self):
+    @staticmethod
+    def _physical_index(i):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[i])
+            except Exception:
+                return i
+        return i
+
+    def _sample_nvml(self):
+        n = self.nvml
+        sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+        r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+        self.rows.append((sm, self.sm_max, [name for bit, name in self.bits if r & bit]))
+
+    def _sample_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        if out:
+            r = [x.strip() for x in out.split(",")]
+            self.rows.append((float(r[0]), float(r[1]), [n for i, n in enumerate(self.NAMES) if len(r) > 2 + i and r[2 + i] == "Active"]))
+
+    def _run(self):
         while not self.stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                if self.nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self.stop.wait(0.2)
+            self.stop.wait(0.1 if self.nvml is not None else 0.5)
 
     def __enter__(self):
         self.th = threading.Thread(target=self._run, daemon=True)
@@ -88,11 +130,10 @@ class ClockSampler:
     def summary(self):
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i] == "Active" for r in self.rows if len(r) > 2 + i)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = sorted({n for r in self.rows for n in r[2]})
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.rows[0][1], "reasons": reasons, "samples": len(self.rows),
+                "source": "NVML (in-process)" if self.nvml is not None else "nvidia-smi"}
 
 
 def algorithmic_bytes(c):
@@ -315,16 +356,15 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="trustI")
     ap.add_argument("--no-also", action="store_true", help="skip the secondary workloads (galaxy-shaped grid, MAGTAR)")
-    ap.add_argument("--also", default="galaxy,magtar", help="comma-separated secondary workloads")
+    ap.add_argument("--also", default="galaxy,magtar,nbody", help="comma-separated secondary workloads")
     ap.add_argument("--ref-budget-s", type=float, default=150.0, help="reference arm: stop starting new solves after this many seconds")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--option", action="append", default=[], help="engine option name=value")
     args = ap.parse_args()
 
-    # NCCL's log goes to stderr so that stdout stays ONE JSON line; the level is left to the caller (the driver counts the
-    # communicator's ranks from the INFO lines)
-    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    # NCCL's log goes to stderr so that stdout stays ONE JSON line; the level (NCCL_DEBUG) is left to the caller -- the driver
+    # counts the communicator's ranks from the INFO lines; unset, NCCL prints nothing (NCCL_DEBUG=WARN puts a version banner on stdout)
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

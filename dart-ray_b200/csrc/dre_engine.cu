@@ -1196,15 +1196,14 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
     CK(cudaMemcpyAsync(e->tot.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));
   CK(cudaMemcpyAsync(e->prev.p, e->acc.p, e->rows_elems() * 8, cudaMemcpyDeviceToDevice, e->st));  // scaspe_prev <- scaspe
   e->red_d.ensure((size_t)2 * g.L);
-  if (iterations == 1) {
-    (e->n_launch++, k_totrad)<<<g.L, 256, 0, e->st>>>(e->acc.p, e->red_d.p);
-    CK(cudaMemcpyAsync(tot_rad_en, e->red_d.p, g.L * 8, cudaMemcpyDeviceToHost, e->st));
-  }
   (e->n_launch++, k_lumcell_sca)<<<cdiv(NL, 256), 256, 0, e->st>>>(e->acc.p, e->lumcell.p, 0);
   (e->n_launch++, k_colsum)<<<g.L, 256, 0, e->st>>>(e->lumcell.p, g.N, g.L, e->red_d.p + g.L);
   std::vector<double> tl(g.L);
   CK(cudaMemcpyAsync(tl.data(), e->red_d.p + g.L, g.L * 8, cudaMemcpyDeviceToHost, e->st));
   CK(cudaStreamSynchronize(e->st));
+  // tot_rad_en(l) = sum over ALL cells of the HEALPix part of scaspe (rt_routines.f90:690-698): only leaf cells are ever
+  // deposited into, so it is the column sum of lumcell just computed (k_totrad re-read every row for the same number)
+  if (iterations == 1) for (int l = 0; l < g.L; l++) tot_rad_en[l] = tl[l];
   double sum_tot = 0; for (int l = 0; l < g.L; l++) sum_tot += tot_rad_en[l];
   int flag = 1;
   if (sum_tot > 0) for (int l = 0; l < g.L; l++) if (!(tl[l] / tot_rad_en[l] < conv_en_lim)) flag = 0;

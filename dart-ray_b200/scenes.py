@@ -566,3 +566,217 @@ def delta_lambda_bins(lambda_si):
     d[0] = edges[0] - lam[0]
     d[-1] = lam[-1] - edges[-1]
     return d
+
+
+# --------------------------------------------------------------------------------------
+# C4: 2DTO3D_GRIDS/input_2dto3d_example.in -- an axisymmetric (R, z) model on the 3-D grid
+# --------------------------------------------------------------------------------------
+class _Table2D:
+    """The 2-D tables of the example (read_grid_2d user_routines_2dto3d.f90:168-323) and the cell average of a tabulated
+    quantity, av_dens_2dto3d (:360-475): bilinear interpolation in (R, |z|) at the mid-points of an (np-1)^3 sub-grid of the cell,
+    np = cellsize / (modelsize / 1000) clamped to [2, 200], zero beyond the last R / z of the table.  The bilinear weights separate
+    in R and z, so the triple sum is evaluated as a_R^T F a_z for all tables at once (the reference adds the same terms point by
+    point: agreement to rounding, this is input generation)."""
+
+    def __init__(self, modelsize):
+        t = _load_table("twod3d_ex1")
+        R = np.asarray(t["R"]); z = np.asarray(t["z"])
+        self.nz = int(np.argmax(R != R[0]))            # z varies fastest (:236-244)
+        self.nr = len(R) // self.nz
+        self.R = R[::self.nz].copy(); self.Z = z[:self.nz].copy()
+        self.lambda_um = np.asarray(t["lambda_um"])
+        self.F = np.stack([np.asarray(a).reshape(self.nr, self.nz) for a in t["j"]] +
+                          [np.asarray(a).reshape(self.nr, self.nz) for a in t["krho"]])     # (2 L, nr, nz)
+        self.pos_obs = np.asarray(t["pos_obs"], dtype=np.float64).reshape(-1, 3)
+        self.modelsize = float(modelsize)
+        self.memo = {}
+
+    @staticmethod
+    def _weights(v, grid):
+        """Per-node sums of the linear-interpolation weights of the points v (those beyond the last node are skipped);
+        the lower node is the largest index >= 0 with v > grid[index], searched as at :409-419."""
+        v = v[v <= grid[-1]]
+        i = np.clip(np.searchsorted(grid, v, side="left") - 1, 0, len(grid) - 2)
+        d = grid[i + 1] - grid[i]
+        w = np.zeros(len(grid))
+        np.add.at(w, i, (grid[i + 1] - v) / d)
+        np.add.at(w, i + 1, (v - grid[i]) / d)
+        return w
+
+    def cell_average(self, x, y, z, cs):
+        """(j(L), krho(L)) averaged over the cell; the model is symmetric under x <-> -x, y <-> -y, z <-> -z and x <-> y."""
+        ax, ay = sorted((abs(x), abs(y)))
+        key = (round(ax, 6), round(ay, 6), round(abs(z), 6), round(cs, 6))
+        hit = self.memo.get(key)
+        if hit is not None:
+            return hit
+        npt = min(max(int(cs / (self.modelsize / 1000.0)), 2), 200)
+        step = cs / (npt - 1)
+        off = (np.arange(npt - 1) + 0.5) * step
+        xp = (ax - cs / 2.0) + off; yp = (ay - cs / 2.0) + off; zp = (abs(z) - cs / 2.0) + off
+        rp = np.sqrt(xp[:, None] ** 2 + yp[None, :] ** 2).ravel()
+        a_r = self._weights(rp, self.R); a_z = self._weights(np.abs(zp), self.Z)
+        v = np.einsum("r,qrz,z->q", a_r, self.F, a_z) * step ** 3 / cs ** 3
+        L = len(self.lambda_um)
+        out = (v[:L].copy(), v[L:].copy())
+        self.memo[key] = out
+        return out
+
+
+def twod3d_grid(max_lvl=4, min_lvl=2, base=(3, 3), modelsize=28000.0, max_dtau=0.01, max_dlum=0.5e-6, z_subd_lim=50.0,
+                r_subd_lim=4000.0):
+    """The main grid of 2DTO3D_GRIDS/input_grid_2dto3d_example.in: dust density and emissivity of the reference wavelength
+    (lambda_ref = 12 um, the first table) averaged per cell, subdivision criterion 'standard' of create_adap_grid_2dto3d.f90:163-185.
+    lnu_tot in that criterion is a module variable of user_routines_2dto3d.f90 that nothing assigns (:19-20): it is 0 there, so
+    every emitting cell is subdivided down to max_lvl."""
+    tab = _Table2D(modelsize)
+    lnu_tot = 0.0
+
+    def calc_dens(x, y, z, cs):
+        j, k = tab.cell_average(x, y, z, cs)
+        return float(k[0]), float(j[0])
+
+    def crit(x, y, z, cs, nlevel, dens, dens_stars):
+        return (dens * cs > max_dtau) or (dens_stars * cs ** 3 > max_dlum * lnu_tot) or (nlevel < min_lvl) or \
+            (abs(z) < z_subd_lim and math.sqrt(x * x + y * y) < r_subd_lim)
+
+    tag = f"twod3d_b{base[0]}_{base[1]}_l{max_lvl}_m{min_lvl}"
+    g = _grid_cached(tag, lambda: build_grid(modelsize, base, max_lvl, calc_dens, crit))
+    return g, tab
+
+
+def twod3d_scene(max_lvl=4, name="2dto3d") -> Scene:
+    """C4: 2DTO3D_GRIDS/input_2dto3d_example.in -- rt_algorithm 'i_obs', only_direct_rt: the emission of the nine shipped tables
+    (12 - 850 um, dust opacity zero in all of them) seen by one internal observer at (8000, 0, 0) pc, no external directions
+    (use_dir_out false), use_lambda_grid (per-wavelength dens / dens_stars from the lambda grids), kp_maps = 8."""
+    g, tab = twod3d_grid(max_lvl=max_lvl)
+    L = len(tab.lambda_um)
+    dens_arr = np.zeros((g.ncell, L)); lumcell = np.zeros((g.ncell, L))
+    for i in np.nonzero(g.cchild == -1)[0]:
+        j, k = tab.cell_average(g.ccoord[i, 0], g.ccoord[i, 1], g.ccoord[i, 2], g.csize[i])
+        dens_arr[i] = k
+        lumcell[i] = j * g.csize[i] ** 3          # calc_total_luminosity rt_routines.f90:605-660
+    ms = g.modelsize
+    return Scene(name=name, grid=g, lambda_um=tab.lambda_um, dens_arr=np.ascontiguousarray(dens_arr), ksca_norm=np.zeros(L),
+                 gsca=np.zeros(L), kp_sca=np.full(L, -1, dtype=np.int32), dir_i_out=np.zeros((2, 0)),
+                 lumcell=np.ascontiguousarray(lumcell), ccoord_p_src=np.zeros((0, 3)), lum_p_src=np.zeros((0, L)),
+                 src_cell=np.full(g.ncell, -1, dtype=np.int32), cell_src=np.zeros(0, dtype=np.int32), bm_par=5, bm_par_sca=5,
+                 bm_par_max=2000, rad_lim=0.1, accuracy=0.10, conv_en_lim=0.01, wall_on=(0, 0, 1),
+                 wall_coord=(0.0, 0.0, 0.0, 0.0, 0.3 * ms - ms / 2.0, 0.7 * ms - ms / 2.0), ccoord_obs=tab.pos_obs.copy())
+
+
+# --------------------------------------------------------------------------------------
+# C5: NBODY_SPH_GRIDS/input_nbody_example1.in -- a particle snapshot binned onto the adaptive grid
+# --------------------------------------------------------------------------------------
+def nbody_particles(n_star=200_000, n_gas=200_000, seed=12345):
+    """The reference's snapshot (run708mainDiff.01000_unbar.h5) is not shipped.  Synthetic stand-in: 2e5 star and
+    2e5 gas particles from numpy's PCG64 generator, seed 12345 -- an exponential disc (h = 3 kpc, sech-like |z| scale 300 pc), a
+    compact bulge, and 40 star-forming clumps that hold a tenth of the gas and all the young stars.  Returns
+    (star xyz [pc], old-star luminosity, young-star luminosity, gas xyz, dust mass = metallicity-weighted gas mass)."""
+    rng = np.random.default_rng(seed)
+
+    def disc(n, h, zs):
+        r = rng.gamma(2.0, h, n)                       # surface density ~ exp(-R/h)
+        ph = rng.uniform(0.0, 2.0 * math.pi, n)
+        z = rng.laplace(0.0, zs, n)
+        return np.stack([r * np.cos(ph), r * np.sin(ph), z], axis=1)
+
+    n_bulge = n_star // 5
+    n_young = n_star // 10
+    n_disc = n_star - n_bulge - n_young
+    centres = disc(40, 3500.0, 60.0)
+    def clumps(n):
+        k = rng.integers(0, len(centres), n)
+        return centres[k] + rng.normal(0.0, 120.0, (n, 3))
+    star = np.concatenate([disc(n_disc, 3000.0, 300.0), rng.normal(0.0, 450.0, (n_bulge, 3)) * np.array([1.0, 1.0, 0.6]), clumps(n_young)])
+    lum_old = np.concatenate([np.full(n_disc, 1.0), np.full(n_bulge, 1.5), np.zeros(n_young)])
+    lum_young = np.concatenate([np.zeros(n_disc + n_bulge), rng.lognormal(0.0, 0.5, n_young)])
+    n_cl = n_gas // 10
+    gas = np.concatenate([disc(n_gas - n_cl, 4500.0, 120.0), clumps(n_cl)])
+    feh = -0.2 * np.sqrt(gas[:, 0] ** 2 + gas[:, 1] ** 2) / 4500.0 + rng.normal(0.0, 0.05, n_gas)   # [Fe/H] gradient
+    dust = 10.0 ** feh                                  # p_met * mgas with equal-mass gas particles (av_galaxy :562-564)
+    return star, lum_old / lum_old.sum(), lum_young / max(lum_young.sum(), 1e-300), gas, dust / dust.sum()
+
+
+def nbody_grid(base=(3, 3), max_lvl=4, min_lvl=1, max_dtau=0.01, max_dlum=0.10e-4, modelsize=20000.0, tau_face=1.5, young_frac=0.3):
+    """Main grid of NBODY_SPH_GRIDS/input_grid_nbody_example1.in: every cell holds the sums of the particles inside its half-open
+    box divided by its volume (av_galaxy user_routines_Nbody_SPH.f90:403-649), subdivision criterion 'standard' of
+    create_adap_grid_Nbody_SPH.f90:194-212 (relative to the root cell: luminosity fraction > max_dlum, optical depth >
+    max_dtau x the root's, level < min_lvl).  The particles are binned once on the finest level; a coarser cell is the sum of its
+    block.  dens is scaled so that the face-on central B-band optical depth of the disc is tau_face."""
+    star, l_old, l_young, gas, dust = nbody_particles()
+    nf = base[0] * base[1] ** (max_lvl - 1)
+    fine = modelsize / nf
+
+    def hist(xyz, w):
+        ijk = np.floor((xyz + modelsize / 2.0) / fine).astype(np.int64)
+        ok = ((ijk >= 0) & (ijk < nf)).all(axis=1)
+        flat = (ijk[ok, 2] * nf + ijk[ok, 1]) * nf + ijk[ok, 0]
+        return np.bincount(flat, weights=w[ok], minlength=nf ** 3).reshape(nf, nf, nf)     # [z][y][x]
+
+    H = {"old": hist(star, l_old), "young": hist(star, l_young), "dust": hist(gas, dust)}
+    lv = {}
+    for l in range(0, max_lvl + 1):
+        n = 1 if l == 0 else base[0] * base[1] ** (l - 1)
+        b = nf // n
+        lv[l] = {k: v.reshape(n, b, n, b, n, b).sum(axis=(1, 3, 5)) for k, v in H.items()}
+    # column through the centre, perpendicular to the disc: sum of dust mass / area  -> scale to tau_face
+    col = lv[max_lvl]["dust"][:, nf // 2, nf // 2].sum() / fine ** 2
+    kscale = tau_face / col
+
+    def lookup(x, y, z, cs):
+        l = int(round(math.log(modelsize / cs) / math.log(base[1]))) if cs < modelsize * 0.999 else 0
+        n = 1 if l == 0 else base[0] * base[1] ** (l - 1)
+        i = [min(max(int((c + modelsize / 2.0) / cs), 0), n - 1) for c in (x, y, z)]
+        vol = cs ** 3
+        return (lv[l]["dust"][i[2], i[1], i[0]] / vol, lv[l]["old"][i[2], i[1], i[0]] / vol, lv[l]["young"][i[2], i[1], i[0]] / vol)
+
+    def calc_dens(x, y, z, cs):
+        d, o, yv = lookup(x, y, z, cs)
+        return d * kscale, (1.0 - young_frac) * o + young_frac * yv
+
+    tot_dens0 = lv[0]["dust"][0, 0, 0] / modelsize ** 3 * kscale
+
+    def crit(x, y, z, cs, nlevel, dens, dens_stars):
+        # dens_stars(0) * modelsize^3 = 1 (luminosity fractions); tau relative to the root cell
+        return (dens_stars * cs ** 3 > max_dlum) or (dens * cs > max_dtau * tot_dens0 * modelsize) or (nlevel < min_lvl)
+
+    tag = f"nbody_b{base[0]}_{base[1]}_l{max_lvl}_m{min_lvl}_t{max_dtau}_d{max_dlum}_f{tau_face}_y{young_frac}"
+    g = _grid_cached(tag, lambda: build_grid(modelsize, base, max_lvl, calc_dens, crit))
+    w_old = np.zeros(g.ncell); w_young = np.zeros(g.ncell)
+    for i in np.nonzero(g.cchild == -1)[0]:
+        _, o, yv = lookup(g.ccoord[i, 0], g.ccoord[i, 1], g.ccoord[i, 2], g.csize[i])
+        w_old[i], w_young[i] = (1.0 - young_frac) * o, young_frac * yv
+    return g, w_old, w_young
+
+
+def nbody_scene(max_lvl=4, max_dlum=0.10e-4, lnum=None, kp_sca_max=1, name="nbody") -> Scene:
+    """C5: NBODY_SPH_GRIDS/input_nbody_example1.in -- rt_algorithm 'main', every luminous leaf emits, 28 stellar wavelengths of
+    lambda_list_trustI_basic.dat (max_lambda_stars = 30) with the TRUST effective-grain opacities, 8 directions of
+    dir_out_galaxy.dat, bm_par 5, accuracy 0.2, no wall.  Old and young stars radiate as 4 000 K and 15 000 K black bodies
+    (the starburst99 library of the example is not shipped)."""
+    g, w_old, w_young = nbody_grid(max_lvl=max_lvl, max_dlum=max_dlum)
+    t = _load_table("magtar")
+    sel = np.arange(len(t["lambda_um"]))
+    if lnum is not None:
+        sel = np.unique(np.linspace(0, len(sel) - 1, lnum).round().astype(int))
+    L = len(sel)
+    lam = np.asarray(t["lambda_um"])[sel]
+    nu_shape = lambda T: (1.0 / lam ** 3) / np.expm1(14387.77 / (lam * T))      # B_nu shape, lambda in um
+    sed_old, sed_young = nu_shape(4000.0), nu_shape(15000.0)
+    sed_old = sed_old / sed_old.max(); sed_young = sed_young / sed_young.max()
+    vol = g.csize ** 3
+    lumcell = (w_old * vol)[:, None] * sed_old[None, :] + (w_young * vol)[:, None] * sed_young[None, :]
+    lumcell[g.cchild != -1] = 0.0
+    lumcell *= 1e30
+    kscale = np.asarray(t["kext_scale"])[sel]
+    kb = float(np.interp(0.44, np.asarray(t["lambda_um"]), np.asarray(t["kext_scale"])))
+    gsca = np.asarray(t["gsca"])[sel]
+    theta = np.array([0.0, 0.224399481500898, 0.448798963001796, 0.673198444502694, 0.897597926003592,
+                      1.12199740750449, 1.34639688900539, 1.57079637050629])
+    return Scene(name=name, grid=g, lambda_um=lam, dens_arr=np.ascontiguousarray(g.dens[:, None] * (kscale / kb)[None, :]),
+                 ksca_norm=np.asarray(t["ksca_norm"])[sel], gsca=gsca, kp_sca=set_kp_sca(gsca, kp_sca_max),
+                 dir_i_out=np.ascontiguousarray(np.stack([theta, np.zeros(8)])), lumcell=np.ascontiguousarray(lumcell),
+                 ccoord_p_src=np.zeros((0, 3)), lum_p_src=np.zeros((0, L)), src_cell=np.full(g.ncell, -1, dtype=np.int32),
+                 cell_src=np.zeros(0, dtype=np.int32), bm_par=5, bm_par_sca=5, bm_par_max=200, rad_lim=0.10, accuracy=0.20,
+                 conv_en_lim=0.01)

@@ -47,3 +47,13 @@ def test_c2_magtar_full_size():
     sc = scenes.magtar_scene()
     assert sc.lnum == 28
     run_sequence(sc, record=0, iterations=1, nthreads=NTH, maps=False)
+
+
+def test_c4_2dto3d_full_size():
+    """C4 = 2DTO3D_GRIDS/input_2dto3d_example.in at its own depth (max_lvl 4: 433 783 cells, 387 099 emitting leaves, 9 wavelengths):
+    rt_loop_iobs towards the internal observer at (8000, 0, 0) pc, then the kp_maps = 8 map (HEALPix nside 256)."""
+    from dartray_b200 import scenes
+    from test_gpu_parity import run_iobs_only
+    sc = scenes.twod3d_scene()
+    assert sc.grid.ncell == 433783
+    run_iobs_only(sc, kp_maps=8)

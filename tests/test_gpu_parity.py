@@ -236,3 +236,40 @@ def test_internal_observer_iobs(tiny_galaxy):
     sc = copy.copy(tiny_galaxy)
     sc.ccoord_obs = np.array([[8000.0, 0.0, 0.0], [-3000.0, 5000.0, 700.0]])
     run_sequence(sc, record=0, iterations=1)
+
+
+def run_iobs_only(sc, kp_maps, units=2):
+    """rt_algorithm 'i_obs' with only_direct_rt (dartray_hub.f90:128-146): rt_loop_iobs for the point sources and the emitting cells,
+    then the internal-observer maps.  Engine vs oracle."""
+    from dartray_b200 import abi
+    from oracle import oracle as O
+    eng = _engine(sc)
+    orc, st = _oracle(sc)
+    gst = O.State(sc)
+    c_o = orc.run_iobs(abi.RTT_I_OBS_DIR_CELL, st)
+    c_g = eng.rt_loop_iobs(abi.RTT_I_OBS_DIR_CELL, gst)
+    assert_counters_equal(c_g, c_o, keys=("sources", "rays", "intersections", "isect_hash"))
+    assert c_o.rays == int((sc.lumcell.sum(axis=1) > 0).sum()) * len(sc.ccoord_obs)
+    assert_fields_close(gst.i_obs_in, st.i_obs_in, "i_obs_in")
+    lam_si = np.asarray(sc.lambda_um) * 1e-6
+    m_g, m_o = eng.make_maps_in(kp_maps, units, lam_si), orc.make_maps_in(st, kp_maps, units, lam_si)
+    assert m_o.max() > 0
+    assert_fields_close(m_g, m_o, f"internal-observer maps kp_maps {kp_maps}")
+    eng.close()
+
+
+def test_c4_2dto3d_internal_observer():
+    """C4 = 2DTO3D_GRIDS/input_2dto3d_example.in on the shipped 2-D tables (9 wavelengths 12-850 um, observer at (8000, 0, 0) pc),
+    one level coarser than the example (max_lvl 3: 16 066 cells)."""
+    from dartray_b200 import scenes
+    sc = scenes.twod3d_scene(max_lvl=3)
+    assert sc.lnum == 9 and sc.ndir == 0 and len(sc.ccoord_obs) == 1
+    run_iobs_only(sc, kp_maps=6)
+
+
+def test_c5_nbody_small_sequence():
+    """C5 = NBODY_SPH_GRIDS/input_nbody_example1.in on the seeded synthetic particle set, reduced (max_lvl 3, 4 wavelengths,
+    2 341 emitting leaves): the whole sequence of dartray_main, every leaf with particles emitting."""
+    from dartray_b200 import scenes
+    sc = scenes.nbody_scene(max_lvl=3, lnum=4, max_dlum=1e-3)
+    run_sequence(sc, record=0, iterations=1)
