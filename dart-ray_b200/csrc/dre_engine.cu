@@ -821,7 +821,7 @@ struct BatchStats { long long peak = 0; int maxH = 0, maxW = 0, maxT = 0; };
 
 // one batch of units through all its resolution steps (main_dir_loop rt_routines.f90:1366-1442 for every unit at once)
 template <int MODE>
-BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0, int capW0, int capT0) {
+BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0, int capW0, int capT0, double max_cap) {
   BatchStats bs; bs.peak = U;
   const DreDev& g = e->g;
   unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
@@ -870,6 +870,10 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
     if (*e->h_err != 0) throw DreError{err_text(*e->h_err)};
     if (c.abort) {          // a buffer was too small: the step changed nothing; grow and repeat it
       const int nh = std::max(c.needH, c.nH), nw = std::max(c.needW, c.nW);
+      // the lists of this batch outgrow the memory budget: the units seen so far under-estimated the later ones by more
+      // than the head-room.  Nothing of this step was deposited, but earlier steps of the batch were: stop with a message.
+      if (std::max(std::max(nh, nw), c.needT) > 1.5 * max_cap)
+        throw DreError{"the ray lists of a unit batch exceed the memory budget: lower option batch_units"};
       if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] step refused: need H %d W %d T %d E %d (have %d %d %d %d)\n", c.needH, c.needW, c.needT, c.needE, e->capH, e->capW, e->capT, e->capE);
       ensure_step(e, U, nh > e->capH ? (int)std::min<long long>(2147483000ll, (long long)nh * 3 / 2) : e->capH,
                   nw > e->capW ? (int)std::min<long long>(2147483000ll, (long long)nw * 3 / 2) : e->capW,
@@ -969,18 +973,19 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     e->ftab_budget = std::min(e->ftab_budget, e->ftab_bytes + (size_t)(0.15 * (double)free_b));
   }
   const int L = e->g.L;
-  const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0);
+  const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0) + 12.0 * 24.0 * 1.5;   // + ~12 events of 24 B per ray
   const double max_cap = std::min(2.0e9, std::max(1.0e6, (double)e->list_budget / bytes_per_cap));
   double& est = e->per_unit_est[rt_type % 16];   // max over steps of the per-list need / units
   double per_unit = 0;
-  long long U_next = est > 0 ? (long long)(max_cap / (1.25 * est)) : std::max<long long>(e->opt_batch_units / 4, 3072);
+  // nothing known about this pass type yet: a probe batch of 16 384 units measures the entries per unit first
+  long long U_next = est > 0 ? (long long)(max_cap / (1.25 * est)) : 16384;
   U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   for (long long u0 = 0; u0 < mine;) {
     const int U = (int)std::min<long long>(U_next, mine - u0);
     int cap0 = (int)std::min(max_cap, std::max(4.0 * U, 1.25 * std::max(per_unit, est) * U) + 1024.0);
     if (e->opt_cap0 > 0) cap0 = e->opt_cap0;   // test hook: start small so that steps are refused and the buffers grow
-    const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0)
-                                                 : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0);
+    const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap)
+                                                 : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap);
     e->peak_entries = std::max(e->peak_entries, bs.peak);
     per_unit = std::max(per_unit, (double)std::max(bs.maxH, std::max(bs.maxW, bs.maxT)) / U);
     if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries, per-list need %d / %d / %d (%.1f per unit), capacity %d\n",
