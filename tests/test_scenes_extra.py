@@ -75,3 +75,20 @@ def test_c5_scene_bins_every_particle_once():
     # the refinement criterion holds on every leaf that is not at the deepest level
     coarse = leaf & (g.lvl < g.max_lvl)
     assert np.all((w_old + w_young)[coarse] * g.csize[coarse] ** 3 <= 1e-3 * (1 + 1e-12))
+
+
+def test_grid_files_round_trip(tmp_path, tiny_galaxy):
+    """The reference's grid datasets (io_routines.f90:189-197, 397-498) in the raw-array container of dartray_b200/gridfile.py:
+    main grid + one lambda grid per wavelength, written and read back bit for bit; csize_arr rebuilt by the make_csize_arr rule."""
+    from dartray_b200 import gridfile
+    sc = tiny_galaxy
+    gridfile.write_scene_grids(str(tmp_path), "m", sc)
+    g, dens_arr, lumcell = gridfile.read_scene_grids(str(tmp_path), "m", sc.lambda_um)
+    for k in ("cchild", "lvl", "cindex", "ccoord", "csize", "dens", "dens_stars", "csize_arr", "carea_arr", "cvol_arr"):
+        assert np.array_equal(getattr(g, k), getattr(sc.grid, k)), k
+    assert g.base == sc.grid.base and g.max_lvl == sc.grid.max_lvl and g.modelsize == sc.grid.modelsize
+    assert np.array_equal(dens_arr, sc.dens_arr)
+    assert np.abs(lumcell - sc.lumcell).max() <= 1e-15 * np.abs(sc.lumcell).max()      # x / V * V
+    import pytest
+    with pytest.raises(ValueError):
+        gridfile.read_lambda_grid(str(tmp_path / gridfile.lambda_grid_name("m", float(sc.lambda_um[0]))), g.ncell + 1)
