@@ -964,12 +964,12 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   // Batch size: the ray lists of a batch grow with the angular refinement of its units, which is not known in advance.
   // The wavefront buffers hold `cap` entries per list (HIGH and LOW double-buffered, outcomes, tasks, packets, index arrays);
   // cap comes from the entries per unit seen so far (high-water mark per rt_type, kept across passes) and is bounded by
-  // 60 % of the memory left after configuration.  A step that would overflow is refused on the device and repeated after
+  // half of the memory left after configuration, 32 GiB at most.  A step that would overflow is refused on the device and repeated after
   // the buffers have grown (run_batch_mode), so an estimate that is too low costs time, not correctness.
   if (e->list_budget == 0) {     // once per configuration: cudaMemGetInfo costs ~10 ms, and the list buffers are kept afterwards
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
-    e->list_budget = (size_t)(0.6 * (double)free_b);
+    e->list_budget = std::min((size_t)(0.5 * (double)free_b), (size_t)32 << 30);   // larger batches gain nothing: 32 GiB at most
     e->ftab_budget = std::min(e->ftab_budget, e->ftab_bytes + (size_t)(0.15 * (double)free_b));
   }
   const int L = e->g.L;

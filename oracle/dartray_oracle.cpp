@@ -184,6 +184,7 @@ struct Ctx {
   // checks (every update atomic, exact) and switched ON by the timing legs of bench.py only, so that the CPU baseline runs
   // the reference's fast path (orc_set_option "lock_cell").
   int use_lock_cell = 0;
+  int i2d = -1;      // 2D mode (rt_loop_2D rt_routines.f90:1061-1140): -1 off, 0 = positive-octant sources only, 1 = sources on the Cartesian planes only
   mutable std::vector<int> lock_cell;
 };
 
@@ -977,6 +978,7 @@ int orc_set_params(orc_ctx* o, const dre_params* p) { o->c.par = *p; return 0; }
 int orc_set_record(orc_ctx* o, int64_t n) { o->c.max_records = n; return 0; }
 int orc_set_option(orc_ctx* o, const char* name, double value) {
   if (!strcmp(name, "lock_cell")) { o->c.use_lock_cell = value != 0; o->c.lock_cell.assign(o->c.N, 0); return 0; }
+  if (!strcmp(name, "i2d")) { o->c.i2d = (int)value; return 0; }
   return 1;
 }
 int orc_get_records(orc_ctx* o, dre_isect* out, int64_t cap, int64_t* n) {
@@ -984,6 +986,14 @@ int orc_get_records(orc_ctx* o, dre_isect* out, int64_t cap, int64_t* n) {
   if (out && m > 0) memcpy(out, o->c.records.data(), m * sizeof(dre_isect));
   *n = (int64_t)o->c.records.size();
   return 0;
+}
+
+// skip_cell_2D_rt_loop rt_routines.f90:1174-1187
+bool skip_cell_2D_rt_loop(const Ctx& c, int i) {
+  if (c.i2d < 0) return false;
+  const double* cc = &c.ccoord[3 * (size_t)i];
+  if (c.i2d == 0) return (cc[0] <= 0.) || (cc[1] <= 0.) || (cc[2] <= 0.);      // only positive cells in the first loop
+  return (cc[0] != 0.) && (cc[1] != 0.) && (cc[2] != 0.);                     // only cells on the Cartesian planes in the second
 }
 
 // rt_loop rt_routines.f90:985-1058.  psel_sum/ipsel (N+S): per-source sums (the reference stores
@@ -1008,6 +1018,7 @@ int orc_run_pass(orc_ctx* o, int rt_type, int iterations, const double* u_fest, 
       src_lum_value(t0, i, sl);
       double s = 0; for (int l = 0; l < L; l++) s += sl[l];
       if (c.cchild[i] != -1 || s == 0) continue;
+      if (skip_cell_2D_rt_loop(c, i)) continue;
       src_ord[i] = n++;
     }
     tot.sources = n;
@@ -1769,6 +1780,195 @@ int orc_make_maps_in(orc_ctx* o, int32_t ndir_in, const double* ccoord_obs, cons
         maps_in[((size_t)idir * L + il) * npix + p] = v;
       }
   }
+  return 0;
+}
+
+}  // extern "C"
+
+// =========================================================================================================================
+// N5: the 2D mode.  rt_loop_2D (rt_routines.f90:1061-1140) = rt_loop with the source filter skip_cell_2D_rt_loop, run twice
+// (i2d = 0, 1); after the first run fix_symmetry (:3605-3635) adds what the seven mirror images of every positive cell received
+// and copies the result back to them.  The reference's scratch arrays are sized by the HEALPix part of the scaspe rows only and
+// assigned from whole rows (:3720-3750), which conforms only when there are no observer directions (dartray_main_2D computes no
+// i_obs, dartray_hub.f90:69): tot_ndir_scaspe = 0 is required here.
+// =========================================================================================================================
+namespace sym2d {
+
+// find_linked_cells rt_routines.f90:3364-3578: the cells at the mirrored tree coordinates, in the order X, Y, Z, XY, XZ, YZ, XYZ
+bool find_linked_cells(const Ctx& c, int nc, int link_list[7]) {
+  const int nlevel = c.lvl[nc];
+  int ccindd[3][MAXL + 1];
+  memset(ccindd, 0, sizeof(ccindd));
+  cindex_to_ccindd(c, nc, nlevel, ccindd);
+  static const int flip[7][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {1, 1, 0}, {1, 0, 1}, {0, 1, 1}, {1, 1, 1}};
+  for (int s = 0; s < 7; s++) {
+    int nw[3][MAXL + 1];
+    memcpy(nw, ccindd, sizeof(nw));
+    for (int i = 1; i <= nlevel; i++) {
+      const int b = c.base[i > 1 ? 1 : 0];
+      for (int a = 0; a < 3; a++) if (flip[s][a]) nw[a][i] = b - 1 - ccindd[a][i];
+    }
+    // ccindd_to_cc descends all max_lvl levels; the digits below nlevel are zero as in the reference's (3, nlevel) arrays
+    int cc = -1, clvl = -1;
+    int l = 1; bool found = false;
+    for (int i = 1; i <= nlevel; i++) {
+      const int b = c.base[i > 1 ? 1 : 0];
+      l += (nw[2][i] * b + nw[1][i]) * b + nw[0][i];
+      if (c.cchild[l] == -1) { cc = l; clvl = i; found = true; break; }
+      l = c.cchild[l];
+    }
+    if (!found || clvl != nlevel) return false;      // 'something wrong here: find_linked_cells'
+    link_list[s] = cc;
+  }
+  return true;
+}
+
+// minloc(abs(arr - x0), mask) - 1: first index of the smallest masked value (Fortran MINLOC)
+int minloc_masked(const std::vector<double>& arr, double x0, const std::vector<char>* mask) {
+  int best = -1; double bv = 0;
+  for (int i = 0; i < (int)arr.size(); i++) {
+    if (mask && !(*mask)[i]) continue;
+    const double v = fabs(arr[i] - x0);
+    if (best < 0 || v < bv) { best = i; bv = v; }
+  }
+  return best;
+}
+
+struct Idx { std::vector<int> ix, iy, iz, ixy, ixz, iyz, ixyz; };
+
+// calc_scaspe_indices rt_routines.f90:4083-4217 for one resolution class: theta / phi of the HEALPix centres of nside 2^kp
+Idx calc_scaspe_indices(int kp) {
+  const int n = 12 * (1 << (2 * kp));
+  std::vector<double> th(n), ph(n);
+  for (int j = 0; j < n; j++) pix2ang_nest(1 << kp, j, th[j], ph[j]);
+  Idx q;
+  q.ix.assign(n, 0); q.iy.assign(n, 0); q.iz.assign(n, 0); q.ixy.assign(n, 0); q.ixz.assign(n, 0); q.iyz.assign(n, 0); q.ixyz.assign(n, 0);
+  std::vector<char> mask(n);
+  auto mask_eq = [&](const std::vector<double>& a, double v) { for (int j = 0; j < n; j++) mask[j] = (a[j] == v); };
+  const double pi = PI;
+  for (int i = 0; i < n; i++) {
+    double phi0, theta0; int is;
+    // X symmetry
+    if (ph[i] >= 0 && ph[i] <= pi / 2) { phi0 = pi - ph[i]; mask_eq(th, th[i]); is = minloc_masked(ph, phi0, &mask); q.ix[i] = is; q.ix[is] = i; }
+    if (ph[i] > pi && ph[i] <= (double)(3.f / 2.f) * pi) { phi0 = 2 * pi - (ph[i] - pi); mask_eq(th, th[i]); is = minloc_masked(ph, phi0, &mask); q.ix[i] = is; q.ix[is] = i; }
+    // Y symmetry
+    if (ph[i] >= 0 && ph[i] <= pi) { phi0 = 2 * pi - ph[i]; if (phi0 == 2 * pi) phi0 = 0; mask_eq(th, th[i]); is = minloc_masked(ph, phi0, &mask); q.iy[i] = is; q.iy[is] = i; }
+    // Z symmetry
+    if (th[i] >= 0 && th[i] <= pi / 2) { theta0 = pi - th[i]; mask_eq(ph, ph[i]); is = minloc_masked(th, theta0, &mask); q.iz[i] = is; q.iz[is] = i; }
+    // XY symmetry
+    if (ph[i] >= 0 && ph[i] < pi) { phi0 = ph[i] + pi; mask_eq(th, th[i]); is = minloc_masked(ph, phi0, &mask); q.ixy[i] = is; q.ixy[is] = i; }
+    // XZ symmetry
+    if (ph[i] >= 0 && ph[i] <= pi / 2) {
+      phi0 = pi - ph[i]; theta0 = pi - th[i]; is = minloc_masked(th, theta0, nullptr); theta0 = th[is];
+      mask_eq(th, theta0); is = minloc_masked(ph, phi0, &mask); q.ixz[i] = is; q.ixz[is] = i;
+    }
+    if (ph[i] > pi && ph[i] <= (double)(3.f / 2.f) * pi) {
+      phi0 = 2 * pi - (ph[i] - pi); theta0 = pi - th[i]; is = minloc_masked(th, theta0, nullptr); theta0 = th[is];
+      mask_eq(th, theta0); is = minloc_masked(ph, phi0, &mask); q.ixz[i] = is; q.ixz[is] = i;
+    }
+    // YZ symmetry
+    if (ph[i] >= 0 && ph[i] <= pi) {
+      phi0 = 2 * pi - ph[i]; if (phi0 == 2 * pi) phi0 = 0; theta0 = pi - th[i]; is = minloc_masked(th, theta0, nullptr); theta0 = th[is];
+      mask_eq(th, theta0); is = minloc_masked(ph, phi0, &mask); q.iyz[i] = is; q.iyz[is] = i;
+    }
+    // XYZ symmetry
+    if (ph[i] >= 0 && ph[i] < pi) {
+      phi0 = ph[i] + pi; theta0 = pi - th[i]; is = minloc_masked(th, theta0, nullptr); theta0 = th[is];
+      mask_eq(th, theta0); is = minloc_masked(ph, phi0, &mask); q.ixyz[i] = is; q.ixyz[is] = i;
+    }
+  }
+  return q;
+}
+
+}  // namespace sym2d
+
+extern "C" {
+
+// the index arrays of calc_scaspe_indices for resolution class kp; which = 0..6 = X, Y, Z, XY, XZ, YZ, XYZ
+int orc_scaspe_symmetry_index(int kp, int which, int32_t* out) {
+  hp_init();
+  const sym2d::Idx q = sym2d::calc_scaspe_indices(kp);
+  const std::vector<int>* v[7] = {&q.ix, &q.iy, &q.iz, &q.ixy, &q.ixz, &q.iyz, &q.ixyz};
+  for (size_t i = 0; i < v[which]->size(); i++) out[i] = (*v[which])[i];
+  return (int)v[which]->size();
+}
+int orc_linked_cells(orc_ctx* o, int32_t nc, int32_t* link_list) {
+  int ll[7];
+  if (!sym2d::find_linked_cells(o->c, nc, ll)) return 1;
+  for (int i = 0; i < 7; i++) link_list[i] = ll[i];
+  return 0;
+}
+
+// fix_symmetry rt_routines.f90:3605-3635 with fix_symmetry_part1 (:3638-3670, rtt_precalc_cell), part2 (:3673-3810,
+// rtt_dir_cell with iterations_dustem <= 1) and part3 (:3813-4025, rtt_scatt; the sequential_scattering branches), then
+// lum_lost = (lum_lost - lum_lost_prev) * 8 + lum_lost_prev.  Arrays as in orc_run_pass (planes (P(l), N) pixel-fastest).
+// Isotropic wavelengths in part2 (:3789-3799): the reference adds scaspe(:, cc) seven times with a cc that the loop does not
+// set -- it is whatever the code above left in it, link_list(6) of this cell once any wavelength has been handled; that value is
+// used here for every wavelength (it is undefined in the reference when the very first wavelength of the first cell is isotropic).
+int orc_fix_symmetry(orc_ctx* o, int rt_type, double* u_fest, double* u_final, double* const* scaspe, double* lum_lost,
+                     const double* lum_lost_prev) {
+  Ctx& c = o->c;
+  const int L = c.L, N = c.N;
+  if (c.ndir != 0) { c.err = "fix_symmetry: the 2D mode needs tot_ndir_scaspe = 0"; return 3; }
+  hp_init();
+  std::vector<sym2d::Idx> idx(c.dim_npix_unique);
+  for (int i = 0; i < c.dim_npix_unique; i++) idx[i] = sym2d::calc_scaspe_indices(c.kp_unique[i]);
+  for (int i = 0; i < N; i++) {
+    if (c.cchild[i] != -1) continue;
+    const double* cc3 = &c.ccoord[3 * (size_t)i];
+    if (cc3[0] < 0. || cc3[1] < 0. || cc3[2] < 0.) continue;
+    int link[7];
+    if (!sym2d::find_linked_cells(c, i, link)) { c.err = "something wrong here: find_linked_cells"; return 2; }
+    for (int j = 0; j < L; j++) {
+      if (rt_type == DRE_RTT_PRECALC_CELL) {                                   // part1
+        double u_arr[7], s = 0;
+        for (int q = 0; q < 7; q++) u_arr[q] = u_fest[j + (size_t)L * link[q]];
+        for (int q = 0; q < 7; q++) s += u_arr[q];
+        u_fest[j + (size_t)L * i] = u_fest[j + (size_t)L * i] + s;
+        for (int q = 0; q < 7; q++) u_fest[j + (size_t)L * link[q]] = u_fest[j + (size_t)L * i];
+        continue;
+      }
+      double u_arr[7], s = 0;
+      if (rt_type == DRE_RTT_DIR_CELL) for (int q = 0; q < 7; q++) u_arr[q] = u_final[j + (size_t)L * link[q]];
+      else for (int q = 0; q < 7; q++) {                                       // part3: delta over u_fest, negatives removed
+        u_arr[q] = u_final[j + (size_t)L * link[q]] - u_fest[j + (size_t)L * link[q]];
+        if (u_arr[q] < 0) u_arr[q] = 0;
+      }
+      for (int q = 0; q < 7; q++) s += u_arr[q];
+      u_final[j + (size_t)L * i] = u_final[j + (size_t)L * i] + s;
+      for (int q = 0; q < 7; q++) u_final[j + (size_t)L * link[q]] = u_final[j + (size_t)L * i];
+      // scaspe
+      const int ik = c.ik_sca[j], np = c.npix_arr[j];
+      double* P = scaspe[j];
+      if (ik != -1) {
+        const sym2d::Idx& X = idx[ik];
+        const std::vector<int>* perm[7] = {&X.ix, &X.iy, &X.iz, &X.ixy, &X.ixz, &X.iyz, &X.ixyz};
+        std::vector<std::vector<double>> sx(7, std::vector<double>(np));
+        for (int q = 0; q < 7; q++) {
+          const double* src = P + (size_t)np * link[q];
+          std::vector<double> tmp(src, src + np);
+          for (int p = 0; p < np; p++) sx[q][p] = tmp[(*perm[q])[p]];
+        }
+        double* own = P + (size_t)np * i;
+        for (int p = 0; p < np; p++) own[p] = own[p] + sx[0][p] + sx[1][p] + sx[2][p] + sx[3][p] + sx[4][p] + sx[5][p] + sx[6][p];
+        std::vector<double> fix(own, own + np);
+        for (int q = 0; q < 7; q++) {
+          double* dst = P + (size_t)np * link[q];
+          for (int p = 0; p < np; p++) dst[p] = fix[(*perm[q])[p]];
+        }
+      } else {
+        double* own = P + (size_t)np * i;
+        if (rt_type == DRE_RTT_DIR_CELL) {                                     // part2 quirk: cc is not set by the loop
+          const int ccq = link[6];
+          for (int icc = 0; icc < 7; icc++) for (int p = 0; p < np; p++) own[p] = own[p] + P[(size_t)np * ccq + p];
+        } else {
+          for (int icc = 0; icc < 7; icc++) for (int p = 0; p < np; p++) own[p] = own[p] + P[(size_t)np * link[icc] + p];
+        }
+        for (int icc = 0; icc < 7; icc++) for (int p = 0; p < np; p++) P[(size_t)np * link[icc] + p] = own[p];
+      }
+    }
+  }
+  if (lum_lost) for (int l = 0; l < L; l++) lum_lost[l] = (lum_lost[l] - lum_lost_prev[l]) * 8 + lum_lost_prev[l];
   return 0;
 }
 

@@ -121,6 +121,39 @@ class Oracle:
             raise RuntimeError(self.l.orc_last_error(self.h).decode())
         return cnt
 
+    # ---- N5: 2D mode -----------------------------------------------------------------------------------------------
+    def fix_symmetry(self, rt_type, st):
+        """fix_symmetry (rt_routines.f90:3605-3635) on the state arrays after the first loop of rt_loop_2D."""
+        rc = self.l.orc_fix_symmetry(self.h, C.c_int(rt_type), abi.dptr(st.u_fest), abi.dptr(st.u_final), abi.plane_ptrs(st.scaspe),
+                                     abi.dptr(st.lum_lost), abi.dptr(st.lum_lost_prev))
+        if rc != 0:
+            raise RuntimeError(self.l.orc_last_error(self.h).decode())
+
+    def run_pass_2d(self, rt_type, iterations, st):
+        """rt_loop_2D (rt_routines.f90:1061-1140): positive-octant sources, fix_symmetry, then the sources on the Cartesian planes.
+        Returns the two pass counters."""
+        out = []
+        try:
+            for i2d in (0, 1):
+                self.set_option("i2d", i2d)
+                out.append(self.run_pass(rt_type, iterations, st))
+                if i2d == 0:
+                    self.fix_symmetry(rt_type, st)
+        finally:
+            self.set_option("i2d", -1)
+        return out
+
+    def linked_cells(self, nc):
+        out = np.zeros(7, dtype=np.int32)
+        if self.l.orc_linked_cells(self.h, C.c_int32(int(nc)), abi.iptr(out)) != 0:
+            raise RuntimeError("find_linked_cells failed")
+        return out
+
+    def scaspe_symmetry_index(self, kp, which):
+        out = np.zeros(12 * 4 ** kp, dtype=np.int32)
+        self.l.orc_scaspe_symmetry_index(C.c_int(kp), C.c_int(which), abi.iptr(out))
+        return out
+
     def run_iobs(self, rt_type, st, nthreads=None):
         p = abi.make_params(self.scene, rt_type)
         self.l.orc_set_params(self.h, C.byref(p))
