@@ -93,6 +93,7 @@ struct DreDev {
   // params
   dre_params par;
   int rt_type;
+  int i2d;                  // 2D mode source filter (skip_cell_2D_rt_loop rt_routines.f90:1174-1187): 0 off, 1 = first loop, 2 = second loop
 };
 
 // The static inputs of the current pass live in constant memory (one engine per device at a time).

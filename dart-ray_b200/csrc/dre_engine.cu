@@ -11,6 +11,7 @@
 #include "dre_split.cuh"
 #include "dre_maps.cuh"
 #include "dre_dust.cuh"
+#include "dre_sym2d.cuh"
 
 namespace {
 
@@ -88,7 +89,8 @@ struct dre_engine {
   DBuf<DreCtl> ctl; DreCtl* h_ctl = nullptr; int* h_err = nullptr;   // control block of the step and its pinned host mirror
   DBuf<unsigned long long> scan_desc; int desc_stride = 0;          // tile descriptors of the chained scans (10 job slots)
   int capH = 0, capW = 0, capT = 0, capU = 0;
-  DBuf<DreEvt> evt; DBuf<int> nev, evoff; int capE = 0;     // events of the rays of a step (dre_split.cuh)
+  DBuf<DreEvt> evt; DBuf<int> nev, evoff; int capE = 0;
+  DBuf<int> sym_perm[DRE_MAXCLASS]; bool have_sym = false;   // 2D mode: mirrored-pixel tables of the scattering classes     // events of the rays of a step (dre_split.cuh)
   // replayable launch sequences of one resolution step (before / after the ray-march kernel), per list parity
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
@@ -332,6 +334,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   for (double& x : e->per_unit_est) x = 0;
   e->list_budget = 0;
   e->capH = e->capW = e->capT = 0;     // the luminosity rows of the lists are lnum wide: re-sized by the next pass
+  e->have_sym = false;
   e->have_opacity = true; e->have_sources = false;
   e->det_e.clear(); e->h_qc.clear();
   DRE_CATCH(e)
@@ -821,14 +824,14 @@ struct BatchStats { long long peak = 0; int maxH = 0, maxW = 0, maxT = 0; };
 
 // one batch of units through all its resolution steps (main_dir_loop rt_routines.f90:1366-1442 for every unit at once)
 template <int MODE>
-BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0, int capW0, int capT0, double max_cap) {
+BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0, int capW0, int capT0, double max_cap, int pmul) {
   BatchStats bs; bs.peak = U;
   const DreDev& g = e->g;
   unsigned nkmask = 1u << DRE_NSIDE_MIN_K;
   ensure_step(e, U, std::max(capH0, U), std::max(capW0, 64), std::max(capT0, 64), -1, 0, 0);
   DreStep S = make_step(e, U);
   int cur = 0, nH = U, nW = 0;
-  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(S, U, e->srclist.p, unit0, e->nranks, e->rank);
+  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(S, U, e->srclist.p, unit0, e->nranks, e->rank, e->nsrc_list, pmul);
   static const int verbose = getenv("DRE_VERBOSE") ? atoi(getenv("DRE_VERBOSE")) : 0;
   for (;;) {
     const auto t_0 = std::chrono::steady_clock::now();
@@ -946,7 +949,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   // psel_av_arr(i0, iterations, :) is ONE slice for the direct-light phase -- rtt_dir_cell writes sid = cell, rtt_dir_src writes
   // sid = N + src, rt_mpi reduces once after both (rt_routines.f90:1456-1463, dartray_hub.f90:31-34) -- and a fresh slice in
   // every scattering iteration (expand_psel_av_arr, dartray_hub.f90:453).  A pass therefore clears only the sid range it writes.
-  if (mode == MODE_DEP) {
+  if (mode == MODE_DEP && e->g.i2d != 2) {      // (the second loop of rt_loop_2D continues the slice of the first)
     const size_t N0 = (size_t)e->g.N, NS = N0 + e->S;
     const size_t lo = (rt_type == DRE_RTT_DIR_SRC) ? N0 : 0, hi = (rt_type == DRE_RTT_DIR_CELL) ? N0 : NS;
     if (hi > lo) {
@@ -980,12 +983,19 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   // nothing known about this pass type yet: a probe batch of 16 384 units measures the entries per unit first
   long long U_next = est > 0 ? (long long)(max_cap / (1.25 * est)) : 16384;
   U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
+  // multiplier of the scrambled source order (k_seed): near nsrc / golden ratio, coprime to nsrc
+  int pmul = 1;
+  if (nsrc > 2) {
+    auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
+    pmul = std::max(1, (int)(nsrc * 0.6180339887));
+    while (gcd(pmul, nsrc) != 1) pmul++;
+  }
   for (long long u0 = 0; u0 < mine;) {
     const int U = (int)std::min<long long>(U_next, mine - u0);
     int cap0 = (int)std::min(max_cap, std::max(4.0 * U, 1.25 * std::max(per_unit, est) * U) + 1024.0);
     if (e->opt_cap0 > 0) cap0 = e->opt_cap0;   // test hook: start small so that steps are refused and the buffers grow
-    const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap)
-                                                 : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap);
+    const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap, pmul)
+                                                 : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap, pmul);
     e->peak_entries = std::max(e->peak_entries, bs.peak);
     per_unit = std::max(per_unit, (double)std::max(bs.maxH, std::max(bs.maxW, bs.maxT)) / U);
     if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries, per-list need %d / %d / %d (%.1f per unit), capacity %d\n",
@@ -1217,6 +1227,91 @@ int dre_prepare_scatt(dre_engine* e, int iterations, double conv_en_lim, double*
   (e->n_launch++, k_zero_sca)<<<cdiv(nsca, 256), 256, 0, e->st>>>(e->acc.p, g.N, g.ROW, g.L);
   CK(cudaStreamSynchronize(e->st));
   DRE_CATCH(e)
+}
+
+// Mirrored HEALPix pixel of every pixel of nside 2^kp under the reflections X, Y, Z, XY, XZ, YZ, XYZ (what calc_scaspe_indices
+// rt_routines.f90:4083-4217 finds by searching the ring for the nearest longitude): the centre direction is reflected and located
+// with ang2pix_nest.  which = 0..6.
+static void sym_index_host(int kp, int which, std::vector<int>& out) {
+  const int nside = 1 << kp, n = 12 * nside * nside;
+  static const int flip[7][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {1, 1, 0}, {1, 0, 1}, {0, 1, 1}, {1, 1, 1}};
+  out.resize(n);
+  for (int p = 0; p < n; p++) {
+    double th, ph; hp::pix2ang_nest(nside, p, th, ph);
+    double t2 = th, p2 = ph;
+    if (flip[which][2]) t2 = hp::PI_ - th;
+    if (flip[which][0] && flip[which][1]) p2 = ph + hp::PI_;
+    else if (flip[which][0]) p2 = hp::PI_ - ph;
+    else if (flip[which][1]) p2 = hp::TWOPI - ph;
+    out[p] = hp::ang2pix_nest(nside, t2, p2);
+  }
+}
+
+int dre_scaspe_symmetry_index(dre_engine* e, int32_t kp, int32_t which, int32_t* out) {
+  DRE_TRY(e)
+  DRE_REQUIRE(kp >= 0 && kp <= DRE_NSIDE_MIN_K && which >= 0 && which < 7 && out, "dre_scaspe_symmetry_index: bad arguments");
+  std::vector<int> v; sym_index_host(kp, which, v);
+  for (size_t i = 0; i < v.size(); i++) out[i] = v[i];
+  DRE_CATCH(e)
+}
+
+static int sym2d_prepare(dre_engine* e, int rt_type) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  check_ready(e);
+  DRE_REQUIRE(rt_type == DRE_RTT_PRECALC_CELL || rt_type == DRE_RTT_DIR_CELL || rt_type == DRE_RTT_SCATT,
+              "dre_run_pass_2d: rt_loop_2D runs rtt_precalc_cell, rtt_dir_cell and rtt_scatt (dartray_hub.f90:69-126)");
+  DRE_REQUIRE(e->g.ndir == 0, "dre_run_pass_2d: the 2D mode needs tot_ndir_scaspe = 0 (fix_symmetry mirrors only the HEALPix part of scaspe)");
+  if (!e->have_sym) {
+    for (int ic = 0; ic < e->g.nclass; ic++) {
+      std::vector<int> all, v;
+      for (int w = 0; w < 7; w++) { sym_index_host(e->g.class_kp[ic], w, v); all.insert(all.end(), v.begin(), v.end()); }
+      e->sym_perm[ic].upload(all.data(), all.size(), e->st);
+    }
+    CK(cudaStreamSynchronize(e->st));
+    e->have_sym = true;
+  }
+  DRE_CATCH(e)
+}
+// fix_symmetry rt_routines.f90:3605-3635 on the device-resident arrays
+static int sym2d_fix(dre_engine* e, int rt_type) {
+  DRE_TRY(e)
+  DreSym q; memset(&q, 0, sizeof(q));
+  for (int ic = 0; ic < e->g.nclass; ic++) q.perm[ic] = e->sym_perm[ic].p;
+  q.rows = e->acc.p; q.u_fest = e->u_fest.p;
+  q.part = (rt_type == DRE_RTT_PRECALC_CELL) ? 1 : (rt_type == DRE_RTT_DIR_CELL ? 2 : 3);
+  sync_g(e);
+  e->errflag.zero(1, e->st);
+  (e->n_launch++, k_fix_symmetry)<<<e->g.N, 128, 0, e->st>>>(q, e->errflag.p);
+  (e->n_launch++, k_lum_lost_x8)<<<cdiv(e->g.L, 128), 128, 0, e->st>>>(e->lum_lost.p, e->lum_lost_prev.p, e->g.L);
+  CK(cudaGetLastError());
+  DRE_REQUIRE(read_int(e, e->errflag.p) == 0, "find_linked_cells: the grid is not symmetric (rt_routines.f90:3394)");
+  DRE_CATCH(e)
+}
+
+int dre_run_pass_2d(dre_engine* e, int rt_type, int iterations, dre_counters* out) {
+  if (!e) return 1;
+  int rc = sym2d_prepare(e, rt_type);
+  if (rc) return rc;
+  dre_counters c0, c1; memset(&c0, 0, sizeof(c0)); memset(&c1, 0, sizeof(c1));
+  e->g.i2d = 1;                                    // first loop: sources of the positive octant
+  rc = dre_run_pass_resident(e, rt_type, iterations, &c0);
+  e->g.i2d = 0;
+  if (rc) return rc;
+  if ((rc = sym2d_fix(e, rt_type))) return rc;
+  e->g.i2d = 2;                                    // second loop: sources on the Cartesian planes
+  rc = dre_run_pass_resident(e, rt_type, iterations, &c1);
+  e->g.i2d = 0;
+  if (rc) return rc;
+  if (out) {
+    *out = c0;
+    out->sources += c1.sources; out->rays += c1.rays; out->intersections += c1.intersections; out->deposits += c1.deposits;
+    out->beam_tests += c1.beam_tests; out->splits += c1.splits; out->merges += c1.merges; out->sca_elems += c1.sca_elems;
+    out->active_lambda += c1.active_lambda; out->steps += c1.steps; out->kernel_ms += c1.kernel_ms; out->pass_ms += c1.pass_ms;
+    out->isect_hash += c1.isect_hash; out->active_lambda_dep += c1.active_lambda_dep; out->descent_loads += c1.descent_loads;
+    out->launches += c1.launches; out->trace_launches += c1.trace_launches;
+  }
+  return 0;
 }
 
 int dre_dust_emission(dre_engine* e, int32_t ls, int32_t ld, const double* kabs_stars, const double* kabs_dust, const double* lambda_si_dust,

@@ -381,7 +381,13 @@ __global__ void k_src_flags(int* __restrict__ flag) {
   if (i >= g.N) return;
   double s = 0;
   for (int l = 0; l < g.L; l++) s += dre_src_lum(g, i, l);
-  flag[i] = (g.cchild[i] == -1 && s != 0) ? 1 : 0;
+  bool on = (g.cchild[i] == -1 && s != 0);
+  if (on && g.i2d) {                       // skip_cell_2D_rt_loop :1174-1187
+    const double* c = g.ccoord + 3 * (size_t)i;
+    if (g.i2d == 1) on = !((c[0] <= 0.) || (c[1] <= 0.) || (c[2] <= 0.));      // only positive cells in the first loop
+    else on = !((c[0] != 0.) && (c[1] != 0.) && (c[2] != 0.));                 // only cells on the Cartesian planes in the second
+  }
+  flag[i] = on ? 1 : 0;
 }
 __global__ void k_src_compact(const int* __restrict__ flag, const int* __restrict__ pos, int N, int* __restrict__ list) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -389,7 +395,7 @@ __global__ void k_src_compact(const int* __restrict__ flag, const int* __restric
 }
 
 // seeds of a batch of units: create_high_ray_list ray_list.f90:71-106 (nside 2 pixel = sector)
-__global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int unit0, int stride, int rank_off) {
+__global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int unit0, int stride, int rank_off, int nsrc, int pmul) {
   const DreDev& g = c_g;
   const DreUnits u = S.u;
   const DreList H = S.H[0], W = S.W[0];
@@ -398,8 +404,14 @@ __global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int un
   if (i > U) return;
   H.seg[i] = i; W.seg[i] = 0;
   if (i == U) return;
-  const int gid = rank_off + (unit0 + i) * stride;     // global unit id = source_ordinal*48 + sector
-  const int nc = srclist[gid / 48], sector = gid % 48;
+  // Units are handed out in a scrambled source order -- source ordinal (s * pmul) mod nsrc, pmul coprime to nsrc -- so that every
+  // batch is a sample of the whole model (neighbouring cells have similar ray trees: in cell order the first batch says little
+  // about the list sizes of the later ones).  The global unit id (record / checksum key) stays source_ordinal*48 + sector.
+  const long long gq = (long long)rank_off + (long long)(unit0 + i) * stride;
+  const int sector = (int)(gq % 48);
+  const int sord = (int)(((gq / 48) * (long long)pmul) % nsrc);
+  const int gid = sord * 48 + sector;
+  const int nc = srclist[sord];
   u.nc[i] = nc; u.gid[i] = gid; u.nk[i] = DRE_NSIDE_MIN_K; u.step[i] = 0; u.mode[i] = 1;
   H.unit[i] = i; H.dir_ipix[i] = sector; H.meta[i] = dre_meta(1, 1, 0, RT_HIGH); H.cc_old[i] = nc;
   H.dplane[i] = 0; H.prev[i] = 0;

@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("DARTRAY_ENGINE_LIB", os.path.join(_HERE, "libdartray_
 SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
-    "dre_run_pass", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_dust_emission", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
+    "dre_run_pass", "dre_run_pass_2d", "dre_scaspe_symmetry_index", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_dust_emission", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
     "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_get_quanta", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
@@ -194,6 +194,18 @@ class Engine:
         cnt = abi.Counters()
         self._ck(self.l.dre_run_pass_resident(self.h, C.c_int(rt_type), C.c_int(iterations), C.byref(cnt)))
         return cnt
+
+    def rt_loop_2d(self, rt_type, iterations=0):
+        """rt_loop_2D (rt_routines.f90:1061-1140) on device-resident state: positive-octant sources, fix_symmetry, plane sources."""
+        self.set_params(rt_type)
+        cnt = abi.Counters()
+        self._ck(self.l.dre_run_pass_2d(self.h, C.c_int(rt_type), C.c_int(iterations), C.byref(cnt)))
+        return cnt
+
+    def scaspe_symmetry_index(self, kp, which):
+        out = np.zeros(12 * 4 ** kp, dtype=np.int32)
+        self._ck(self.l.dre_scaspe_symmetry_index(self.h, C.c_int32(kp), C.c_int32(which), abi.iptr(out)))
+        return out
 
     def rt_loop_host(self, rt_type, iterations, st):
         """rt_loop with HOST arrays (upload -> pass -> download): the drop-in call."""

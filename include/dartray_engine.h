@@ -16,6 +16,7 @@
  *   dre_prepare_scatt <- rt_prepare(rtt_scatt) + calc_total_luminosity_sca
  *                                        dartray_hub.f90:432-457, rt_routines.f90:663-758
  *   dre_dust_emission <- set_dust_emission ('eff')  sed_routines.f90:249-276, 377-430
+ *   dre_run_pass_2d   <- rt_loop_2D + fix_symmetry       rt_routines.f90:1061-1140, 3605-4025
  *
  * Return value: 0 on success, non-zero on error (message via dre_last_error);
  * the Fortran wrapper calls stop_prc (smooth_grid_routines.f90:869) on non-zero.
@@ -132,6 +133,15 @@ int dre_zero    (dre_engine*, int which);
 /* ---- passes -------------------------------------------------------------- */
 /* rt_loop on device-resident state; accumulates into u_fest (precalc) or u_final+scaspe+lum_lost. */
 int dre_run_pass_resident(dre_engine*, int rt_type, int iterations, dre_counters* out);
+/* rt_loop_2D (rt_routines.f90:1061-1140), the 2D mode for models with the three mirror symmetries (dartray_main_2D
+ * dartray_hub.f90:69-126; rt_type = rtt_precalc_cell, rtt_dir_cell or rtt_scatt): the sources of the positive octant
+ * (skip_cell_2D_rt_loop :1174-1187), fix_symmetry (:3605-4025: every non-negative leaf cell receives what its seven mirror images
+ * got -- find_linked_cells :3364-3578, scaspe rows mirrored pixel by pixel, calc_scaspe_indices :4083-4217 -- and lum_lost is
+ * scaled by 8), then the sources on the Cartesian planes.  Device-resident state; needs tot_ndir_scaspe = 0 (the reference's
+ * symmetrisation covers the HEALPix part of scaspe only; dartray_main_2D computes no i_obs).  Counters: both loops added. */
+int dre_run_pass_2d(dre_engine*, int rt_type, int iterations, dre_counters* out);
+/* the mirrored-pixel table of calc_scaspe_indices for nside 2^kp; which = 0..6 = X, Y, Z, XY, XZ, YZ, XYZ; out (12*4^kp) */
+int dre_scaspe_symmetry_index(dre_engine*, int32_t kp, int32_t which, int32_t* out);
 /* rt_loop with HOST arrays: upload -> pass -> download (the drop-in call). */
 int dre_run_pass(dre_engine*, int rt_type, int iterations,
                  const double* u_fest /*(L,N) in*/, double* u_accum /*(L,N) inout*/,

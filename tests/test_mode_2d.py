@@ -88,3 +88,67 @@ def test_2d_mode_equals_main_mode_on_a_symmetric_model(tiny_galaxy):
     for l in range(sc.lnum):
         close(st2.scaspe[l], st3.scaspe[l], f"scaspe[{l}]")
     close(st2.lum_lost, st3.lum_lost, "lum_lost")
+
+
+@pytest.mark.gpu
+def test_gpu_symmetry_tables_match_calc_scaspe_indices(tiny_galaxy):
+    """The engine reflects the pixel centre and locates it with ang2pix_nest; the oracle restates the reference's ring search."""
+    from dartray_b200 import engine
+    from oracle import oracle as O
+    sc = sym_scene(tiny_galaxy)
+    eng, orc = engine.Engine(sc), O.Oracle(sc)
+    for kp in (0, 1, 2):
+        for w in range(7):
+            assert np.array_equal(eng.scaspe_symmetry_index(kp, w), orc.scaspe_symmetry_index(kp, w)), (kp, w)
+    eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["galaxy_base3", "galaxy_base2", "galaxy_isotropic"])
+def test_gpu_2d_mode_matches_oracle(kind, tiny_galaxy):
+    """dre_run_pass_2d against the oracle's rt_loop_2D: precalculation, direct light and two scattering iterations on a symmetric
+    model; counters and the intersection checksum of both loops bit for bit, fields within 1e-5.  base (3,3) has cells on the
+    Cartesian planes (second loop, links that coincide with the cell); base (2,2) has none; the third case makes the last wavelength
+    isotropic."""
+    from dartray_b200 import abi, engine, scenes
+    from oracle import oracle as O
+    from test_gpu_parity import assert_counters_equal, assert_fields_close
+    sc = sym_scene(tiny_galaxy if kind != "galaxy_base2" else scenes.galaxy_scene(max_lvl=3, min_lvl=3, lnum=3, base=(2, 2), name="galaxy_b2"))
+    if kind == "galaxy_isotropic":       # the isotropic branches of fix_symmetry_part2 / part3 (incl. the stale-`cc` sum of part2)
+        k = sc.kp_sca.copy(); k[-1] = -1; sc.kp_sca = k
+    eng = engine.Engine(sc)
+    eng.set_option("hash", 1)
+    orc, st = O.Oracle(sc, nthreads=8), O.State(sc)
+    gst = O.State(sc)
+
+    def total(cs):
+        t = abi.Counters()
+        for k, _ in abi.Counters._fields_:
+            setattr(t, k, sum(getattr(c, k) for c in cs))
+        return t
+
+    def compare(tag):
+        eng.download_state(gst)
+        assert_fields_close(gst.u_fest, st.u_fest, f"u_fest {tag}")
+        assert_fields_close(gst.u_final, st.u_final, f"u_final {tag}")
+        for l in range(sc.lnum):
+            assert_fields_close(gst.scaspe[l], st.scaspe[l], f"scaspe[{l}] {tag}")
+        assert_fields_close(gst.lum_lost, st.lum_lost, f"lum_lost {tag}")
+
+    for rt in (abi.RTT_PRECALC_CELL, abi.RTT_DIR_CELL):
+        c_o = total(orc.run_pass_2d(rt, 0, st))
+        c_g = eng.rt_loop_2d(rt, 0)
+        assert_counters_equal(c_g, c_o)
+        compare(f"after 2D pass {rt}")
+    tot_g = np.zeros(sc.lnum)
+    for it in (1, 2):
+        f_o = orc.prepare_scatt(it, st)
+        assert f_o == eng.rt_prepare_scatt(it, tot_g)
+        if f_o:
+            break
+        orc.set_sources(st.lumcell)
+        c_o = total(orc.run_pass_2d(abi.RTT_SCATT, it, st))
+        c_g = eng.rt_loop_2d(abi.RTT_SCATT, it)
+        assert_counters_equal(c_g, c_o)
+        compare(f"after 2D scattering iteration {it}")
+    eng.close()
