@@ -84,6 +84,16 @@ module dartray_gpu
      integer(c_int) function dre_run_pass_resident(e, rt_type, iterations, cnt) bind(C, name='dre_run_pass_resident')
        import; type(c_ptr), value :: e; integer(c_int), value :: rt_type, iterations; type(dre_counters) :: cnt
      end function
+     integer(c_int) function dre_run_pass_2d(e, rt_type, iterations, cnt) bind(C, name='dre_run_pass_2d')
+       import; type(c_ptr), value :: e; integer(c_int), value :: rt_type, iterations; type(dre_counters) :: cnt
+     end function
+     integer(c_int) function dre_dust_emission(e, lnum_stars, lnum_dust, kabs_stars, kabs_dust, lambda_si_dust, dl_stars, dl_dust, &
+          kext_ref, dens_ref, rf_stars, rf_dust, iterations_dustem, dens_stars, t_dust, to_lumcell) bind(C, name='dre_dust_emission')
+       import; type(c_ptr), value :: e, rf_dust, t_dust; integer(c_int32_t), value :: lnum_stars, lnum_dust, iterations_dustem, to_lumcell
+       real(c_double) :: kabs_stars(*), kabs_dust(*), lambda_si_dust(*), dl_stars(*), dl_dust(*), dens_ref(*), rf_stars(lnum_stars,*), &
+                         dens_stars(lnum_dust,*)
+       real(c_double), value :: kext_ref
+     end function
      integer(c_int) function dre_run_pass(e, rt_type, iterations, u_fest, u_accum, scaspe, scaspe_prev, &
                                           lum_lost, psel_av, cnt) bind(C, name='dre_run_pass')
        import; type(c_ptr), value :: e, u_fest, u_accum, scaspe, scaspe_prev, lum_lost, psel_av

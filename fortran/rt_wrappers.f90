@@ -27,6 +27,34 @@ subroutine rt_loop
   call dre_check(dre_run_pass_resident(eng, rt_type, iterations, cnt), 'dre_run_pass_resident')
 end subroutine rt_loop
 
+!> rt_loop_2D  (rt_routines.f90:1061-1140; call sites dartray_hub.f90:80, 89, 105): both source loops and fix_symmetry on the device
+subroutine rt_loop_2D
+  use dartray_gpu
+  type(dre_counters) :: cnt
+  type(dre_params)   :: par
+  if (test_run) return
+  call fill_dre_params(par)
+  call dre_check(dre_set_params(eng, par), 'dre_set_params')
+  if (rt_type /= rtt_scatt) then
+     call dre_check(dre_set_sources(eng, c_loc(lumcell), tot_p_src, c_loc(ccoord_p_src), c_loc(lum_p_src_arr), &
+                                    c_loc(src_cell), c_loc(cell_src)), 'dre_set_sources')
+  end if
+  call dre_check(dre_run_pass_2d(eng, rt_type, iterations, cnt), 'dre_run_pass_2d')
+end subroutine rt_loop_2D
+
+!> set_dust_emission, dust_heating_type 'eff'  (sed_routines.f90:249-276; call site dartray_hub.f90:225): the emissivity of the next
+!! dust-heating iteration from the radiation fields; u_final of the last dust pass is read on the device, lumcell is left there.
+subroutine set_dust_emission_gpu
+  use dartray_gpu
+  integer :: i0
+  i0 = i_lambda_dust(0)
+  call dre_check(dre_dust_emission(eng, lnum_stars, lnum_dust, kabs_arr(0:lnum_stars-1), kabs_arr(i0:lnum_tot-1), &
+       lambda_arr_SI(i0:lnum_tot-1), delta_lambda_bin_stars, delta_lambda_bin_dust, kext_ref, dens_ref, u_final_uv_opt, &
+       c_null_ptr, iterations_dustem, dens_stars_arr, c_null_ptr, 1), 'dre_dust_emission')
+  call reduce_dens_stars_arr
+  call check_dens_stars_arr
+end subroutine set_dust_emission_gpu
+
 !> rt_mpi  (io_routines.f90:3667-3705 with reduce_u_fest_arr / reduce_u_final_arr / reduce_scaspe_arr / reduce_lum_lost /
 !! reduce_psel_av_arr :3708-3881; call sites dartray_hub.f90:25, 34, 50): NCCL all-reduce of the device arrays.
 subroutine rt_mpi
