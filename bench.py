@@ -531,6 +531,22 @@ def main():
                            "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
             "rt_mpi_ms_per_step": m["mpi_ms"], "rank_pass_ms_min_max": m["pass_minmax"], "roofline": roof}
 
+    # the smaller kernels of the path, once, on the state the last solve left on the device (device time of the pass from the
+    # engine's CUDA events; host wall clock around the calls that return host arrays)
+    if not args.no_e2e and scene.ndir > 0:
+        prod = {}
+        eng.zero(abi.ARR_I_OBS)
+        has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
+        eng.set_sources(scene.lumcell)
+        for nm, rt, on in (("i_obs_dir_cell", abi.RTT_I_OBS_DIR_CELL, has_cell), ("i_obs_dir_src", abi.RTT_I_OBS_DIR_SRC, has_src), ("i_obs", abi.RTT_I_OBS, True)):
+            if on:
+                c = eng.rt_loop_iobs(rt)
+                prod[nm] = {"ms": round(c.pass_ms, 3), "kernel_ms": round(c.kernel_ms, 3), "rays": c.rays, "intersections": c.intersections}
+        lam_si = np.asarray(scene.lambda_um) * 1e-6
+        t0 = time.perf_counter(); eng.calc_sed(1.0e4, 2, lam_si); prod["calc_sed_ms"] = round((time.perf_counter() - t0) * 1e3, 3)
+        t0 = time.perf_counter(); eng.make_maps(200, 1.0, 2, lam_si); prod["make_maps_200px_ms"] = round((time.perf_counter() - t0) * 1e3, 3)
+        line["products"] = prod
+
     # the other workloads the metric is quoted on (north star: galaxy-shaped grid, MAGTAR shell), same engine options
     if not args.no_also:
         also = {}

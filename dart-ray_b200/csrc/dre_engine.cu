@@ -66,7 +66,8 @@ struct dre_engine {
   DBuf<DreDir> class_dir[DRE_MAXCLASS], dirtab[DRE_MAXK + 1], obs_dir;
   DBuf<double> ftab[DRE_MAXK + 1];
   std::vector<int> h_npix, h_npix_hp, h_off, h_ik, h_cell_src;
-  std::vector<double> h_dir_i_out;
+  std::vector<double> h_dir_i_out, h_gsca;
+  std::vector<double> det_peak;   // deterministic mode: largest phase-function value an observer slot can take, per wavelength
   double h_csize0 = 0;      // csize(0): the root cell
   std::vector<double> h_ccoord, h_csize, h_ccoord_p_src; std::vector<int> h_cchild;   // host copies for the map geometry
   int S = 0;
@@ -95,7 +96,7 @@ struct dre_engine {
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_det = 0;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_coop_work = 131072, opt_det = 0;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -318,6 +319,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   e->ik_sca.upload(e->h_ik.data(), L, e->st); e->npix_hp.upload(e->h_npix_hp.data(), L, e->st);
   e->npix.upload(e->h_npix.data(), L, e->st); e->off.upload(e->h_off.data(), L, e->st);
   e->h_dir_i_out.assign(dir_i_out, dir_i_out + 2 * (size_t)ndir);
+  e->h_gsca.assign(gsca_arr, gsca_arr + L); e->det_peak.clear();
   std::vector<DreDir> od(std::max(ndir, 1));
   for (int j = 0; j < ndir; j++) od[j] = hp::make_dir(dir_i_out[j], dir_i_out[ndir + j]);
   e->obs_dir.upload(od.data(), od.size(), e->st);
@@ -523,7 +525,7 @@ const char* err_text(int code) {
     case 1: return "ray_tracing: negative path length (rt_routines.f90:1714)";
     case 2: return "ray_tracing: next cell not found (rt_routines.f90:1849)";
     case 3: return "find_cc_new2: host cell not found (rt_routines.f90:2037)";
-    case 4: return "angular resolution exceeds the direction tables: raise option dir_kmax";
+    case 4: return "angular resolution exceeds nside 8192, the limit of the HEALPix routines (healpix_routines.f90:9)";
     case 5: return "define_next_level: nside fell below 2";
   }
   return "unknown device error";
@@ -651,6 +653,39 @@ void launch_trace(dre_engine* e, const DreAccum& A, const DreStep& S) {
 // exact up to 2x the bound; beyond that only bit-reproducibility degrades, not the value.  The price is dynamic range:
 // an element keeps an absolute accuracy of ~sqrt(n) q / 2 after n contributions, i.e. elements below ~1e-10 of the bound
 // of their wavelength no longer meet 1e-5 relative (deeply shadowed cells of an optically thick model).
+// max(1, largest F of an observer slot): Henyey-Greenstein peak (1+|g|)/((1-|g|)^2 npix_hp) over the smallest normaliser
+// sum_hp f, the latter sampled for ray directions at the centres of nside 8 (calc_ffn_arr rt_routines.f90:2186-2281)
+double det_peak_factor(dre_engine* e, int l) {
+  const DreDev& g = e->g;
+  if (g.ndir == 0 || e->h_ik[l] < 0) return 1.0;
+  if ((int)e->det_peak.size() != g.L) {
+    e->det_peak.assign(g.L, 1.0);
+    for (int w = 0; w < g.L; w++) {
+      const int ic = e->h_ik[w];
+      if (ic < 0) continue;
+      const double gg = std::fabs(e->h_gsca[w]);
+      const int kp = g.class_kp[ic], nhp = g.class_nhp[ic];
+      std::vector<DreDir> cd(nhp);
+      for (int j = 0; j < nhp; j++) { double th, ph; hp::pix2ang_nest(1 << kp, j, th, ph); cd[j] = hp::make_dir(th, ph); }
+      double tot_min = 1e300;
+      for (int r = 0; r < 768; r++) {
+        double th, ph; hp::pix2ang_nest(8, r, th, ph);
+        const DreDir rd = hp::make_dir(th, ph);
+        double tot = 0;
+        for (int j = 0; j < nhp; j++) {
+          const double ads = cd[j].ct * rd.ct + cd[j].st * rd.st * (cd[j].cp * rd.cp + cd[j].sp * rd.sp);
+          const double x = 1.0 + gg * gg - 2.0 * gg * ads;
+          tot += (1.0 - gg * gg) / nhp / (x * std::sqrt(x));
+        }
+        tot_min = std::min(tot_min, tot);
+      }
+      const double fpeak = (1.0 + gg) / ((1.0 - gg) * (1.0 - gg) * nhp);
+      e->det_peak[w] = std::max(1.0, fpeak / tot_min);
+    }
+  }
+  return e->det_peak[l];
+}
+
 void det_prepare(dre_engine* e, int rt_type, int mode) {
   const DreDev& g = e->g;
   const int L = g.L, Lq = dre_lq(L), nq = 3 * Lq + 2;
@@ -675,7 +710,9 @@ void det_prepare(dre_engine* e, int rt_type, int mode) {
     // scaspe is zero at the start of a scattering iteration (rt_routines.f90:747-756): its grid follows the
     // luminosity of the iteration instead of the running maximum
     if (rt_type == DRE_RTT_SCATT && lt[l] > 0) e->det_e[l] = INT_MIN;
-    bump(l, 2.0 * lt[l]);
+    // an element of a HEALPix slot is at most Lt (the row is normalised over those slots); an observer-direction slot
+    // shares the normaliser but not the sum: its phase-function value reaches f_peak / min(normaliser) for forward-peaked g
+    bump(l, 2.0 * lt[l] * det_peak_factor(e, l));
     bump(Lq + l, 2.0 * std::sqrt(3.0) * lt[l] / (g.par.cs * csmin * csmin));
     bump(2 * Lq + l, 2.0 * lt[l]);
   }
@@ -740,7 +777,7 @@ DreStep make_step(dre_engine* e, int U) {
   S.reco_cnt = e->reco_cnt.p; S.keptH = e->keptH.p; S.keptW = e->keptW.p; S.newHcnt = e->newHcnt.p; S.newWcnt = e->newWcnt.p;
   S.fH = e->fH.p; S.fW = e->fW.p; S.posOH = e->posOH.p; S.posOW = e->posOW.p; S.tasks = e->tasks.p; S.pkts = e->pkts.p;
   S.pstride = dre_pkt_stride(e->g.L); S.capH = e->capH; S.capW = e->capW; S.capT = e->capT; S.ctl = e->ctl.p;
-  S.scan_desc = e->scan_desc.p; S.desc_stride = e->desc_stride; S.err = e->errflag.p; S.steps = e->counters.p + CNT_N; S.kmax = e->g.dir_kmax;
+  S.scan_desc = e->scan_desc.p; S.desc_stride = e->desc_stride; S.err = e->errflag.p; S.steps = e->counters.p + CNT_N; S.kmax = DRE_MAXK;
   return S;
 }
 
@@ -835,16 +872,25 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
   static const int verbose = getenv("DRE_VERBOSE") ? atoi(getenv("DRE_VERBOSE")) : 0;
   for (;;) {
     const auto t_0 = std::chrono::steady_clock::now();
+    // direction tables are built up to nside 512 at the start of a pass; a unit that refines further (the reference allows
+    // nside <= 8192, healpix_routines.f90:9) gets its table here, before the step that uses it
+    for (int k = e->g.dir_kmax + 1; k <= DRE_MAXK && (nkmask >> k); k++) { build_dir_table(e, k); sync_g(e); }
     if (MODE == MODE_DEP) ensure_ftab(e, nkmask);
-    if (MODE == MODE_DEP && e->opt_split && e->opt_coop) {
-      // the list side of the step as two cooperative launches around the deposit kernel
+    // Option coop (off by default; A/B switch): the list side of a step as two cooperative launches with grid-wide barriers
+    // between the phases -- 1: on one CTA per SM, 2: on 4-32 CTAs for steps with little work.  Both measured SLOWER than the
+    // graph-replayed kernels on B200 (TRUST-I rtt_dir_src, 37 small steps: 7.1 ms graphs, 7.7 ms coop=1, 9.6 ms coop=2):
+    // a grid barrier costs more than a graph-node boundary here.
+    const long long step_work = (long long)U / 8 + 5ll * ((long long)nH + nW);      // rays <= 4 x extracted entries
+    const bool coop_step = MODE == MODE_DEP && e->opt_split && (e->opt_coop == 1 || (e->opt_coop == 2 && step_work <= e->opt_coop_work));
+    if (coop_step) {
+      const int cgrid = (e->opt_coop == 1) ? e->sm_count : (int)std::max<long long>(4, std::min<long long>(32, (step_work + 4095) / 4096));
       DreCoop cq; cq.evt = e->evt.p; cq.nev = e->nev.p; cq.evoff = e->evoff.p; cq.capE = e->capE; cq.L = e->g.L;
       DreAccum Aa = A; DreStep Ss = S; int cc = cur;
       void* a_pre[] = {&Aa, &Ss, &cc, &cq};
-      CK(cudaLaunchCooperativeKernel((const void*)k_step_pre_coop, dim3(e->sm_count), dim3(SCAN_THREADS), a_pre, 0, e->st));
+      CK(cudaLaunchCooperativeKernel((const void*)k_step_pre_coop, dim3(cgrid), dim3(SCAN_THREADS), a_pre, 0, e->st));
       launch_split(e, A, S, false);
       void* a_post[] = {&Ss, &cc, &cq};
-      CK(cudaLaunchCooperativeKernel((const void*)k_step_post_coop, dim3(e->sm_count), dim3(SCAN_THREADS), a_post, 0, e->st));
+      CK(cudaLaunchCooperativeKernel((const void*)k_step_post_coop, dim3(cgrid), dim3(SCAN_THREADS), a_post, 0, e->st));
       CK(cudaMemcpyAsync(e->h_ctl, S.ctl, sizeof(DreCtl), cudaMemcpyDeviceToHost, e->st));
       CK(cudaMemcpyAsync(e->h_err, S.err, sizeof(int), cudaMemcpyDeviceToHost, e->st));
       e->n_launch += 2;
@@ -1727,7 +1773,8 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "graphs") e->opt_graphs = value ? 1 : 0;
   else if (s == "cap0") e->opt_cap0 = std::max(0, (int)value);
   else if (s == "split") e->opt_split = value ? 1 : 0;
-  else if (s == "coop") e->opt_coop = value ? 1 : 0;
+  else if (s == "coop") e->opt_coop = std::max(0, std::min(2, (int)value));
+  else if (s == "coop_work") e->opt_coop_work = std::max(0, (int)value);
   else if (s == "scan_chained") { /* accepted for compatibility: every prefix sum is the chained single-launch scan */ }
   else if (s == "ring_slots") e->opt_ring_slots = (value >= 2) ? 2 : 1;
   else if (s == "chunk") e->opt_chunk = std::max(1, std::min(64, (int)value));

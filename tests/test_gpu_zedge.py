@@ -59,7 +59,8 @@ OPTION_SETS = {
     "whole_row_stage": (("stage_split", 1), ("warps", 4)),
     "fused_march": (("split", 0),),                     # geometry and deposits in one warp-per-ray kernel (the round-1 form) instead of k_geom + k_deposit
     "coop_lists": (("coop", 1),),                       # the list side of a step as two cooperative launches (grid-wide barriers) instead of graph-replayed kernels
-    "no_graphs": (("graphs", 0),),                      # the kernels of a step launched one by one instead of replayed from CUDA graphs
+    "no_coop": (("coop", 0),),                          # small steps through the graph-replayed kernels too
+    "no_graphs": (("graphs", 0), ("coop", 0)),                      # the kernels of a step launched one by one instead of replayed from CUDA graphs
     "refused_steps": (("cap0", 64), ("batch_units", 960)),   # list buffers start at 64 entries: steps are refused on the device and repeated after growth
     "one_ray_chunks": (("chunk", 1), ("ctas_per_sm", 2)),
 }
@@ -78,15 +79,10 @@ def test_unit_batches_point_source(small_trusti):
     run_sequence(small_trusti, record=0, iterations=1, options=(("batch_units", 48),))
 
 
-def test_direction_table_limit_is_reported(tiny_trusti):
-    """A ray tree that needs a finer HEALPix resolution than the direction tables hold ends the pass with an error
-    (no silent truncation): tables up to nside 8, the slab needs more."""
-    from dartray_b200 import abi, engine
-    eng = _engine(tiny_trusti, (("dir_kmax", 3),))
-    eng.rt_loop(abi.RTT_PRECALC_SRC, 0)
-    with pytest.raises(engine.EngineError, match="direction tables"):
-        eng.rt_loop(abi.RTT_DIR_SRC, 0)
-    eng.close()
+def test_direction_tables_grow_on_demand(tiny_trusti):
+    """The direction tables are built up to nside 2^dir_kmax at the start of a pass and extended when a ray tree refines further
+    (the reference allows nside <= 8192): with tables up to nside 8 only, the slab's direct light still matches the oracle."""
+    run_sequence(tiny_trusti, record=0, iterations=1, options=(("dir_kmax", 3),))
 
 
 GRIDS = {
