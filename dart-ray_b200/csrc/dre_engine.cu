@@ -608,7 +608,7 @@ void launch_split_kl(dre_engine* e, const DreAccum& A, const DreStep& S, bool wi
     ScanJobs J; memset(&J, 0, sizeof(J));
     J.j[0].in = e->nev.p; J.j[0].out = e->evoff.p; J.j[0].n_ptr = &S.ctl->nT; J.j[0].slot = 10;
     k_scan_jobs<<<dim3(e->sm_count, 1), SCAN_THREADS, 0, e->st>>>(J, S.ctl, S.scan_desc, S.desc_stride, 10u, 1);
-    k_geom_write<<<e->sm_count * 8, 128, 0, e->st>>>(A, S, e->evt.p, e->evoff.p, e->capE);
+    k_geom_write<<<e->sm_count * 2 * DRE_GEOM_MINB, 128, 0, e->st>>>(A, S, e->evt.p, e->evoff.p, e->capE);
     e->n_launch += 2;
   }
   CK(cudaEventRecord(e->ev[2], e->st));
@@ -804,7 +804,7 @@ int enqueue_pre(dre_engine* e, const DreAccum& A, const DreStep& S, int cur, cud
   k_step_resolve<<<G, STEP_THREADS, 0, st>>>(S, cur);
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.ntask, S.task_off, &S.ctl->nExt, 0, 3, S.nreco, S.reco_off, &S.ctl->nExt, 0, 4), S.ctl, S.scan_desc, S.desc_stride, 3u, 0);
   k_step_tasks<<<G, STEP_THREADS, 0, st>>>(S, cur);
-  if (MODE == MODE_DEP && e->opt_split) k_prep_geom<<<e->sm_count * 8, 128, 0, st>>>(A, S, cur, e->nev.p);   // packets + pass 0 of the march
+  if (MODE == MODE_DEP && e->opt_split) k_prep_geom<<<e->sm_count * 2 * DRE_GEOM_MINB, 128, 0, st>>>(A, S, cur, e->nev.p);   // packets + pass 0 of the march
   else k_prep_rays<MODE><<<e->sm_count * 8, 128, 0, st>>>(A, S, cur);
   return 10;
 }

@@ -203,7 +203,10 @@ __device__ __forceinline__ void ph_prep_geom(const DreAccum& A, const DreStep& S
     __syncthreads();
   }
 }
-__global__ void __launch_bounds__(128) k_prep_geom(DreAccum A, DreStep S, int cur, int* __restrict__ nev) { ph_prep_geom<128>(A, S, cur, nev); }
+#ifndef DRE_GEOM_MINB
+#define DRE_GEOM_MINB 4     // resident 128-thread CTAs per SM the march kernels are compiled for (register cap 65536 / (128 * n))
+#endif
+__global__ void __launch_bounds__(128, DRE_GEOM_MINB) k_prep_geom(DreAccum A, DreStep S, int cur, int* __restrict__ nev) { ph_prep_geom<128>(A, S, cur, nev); }
 
 // Pass 1 of the march: events written at evoff[t] (prefix sum of nev), or the whole step refused when they do not fit the
 // event buffer.
@@ -234,7 +237,7 @@ __device__ __forceinline__ void ph_geom_write(const DreAccum& A, const DreStep& 
     atomicAdd(&A.counters[CNT_HASH], gc.hash); atomicAdd(&A.counters[CNT_RAYS], rays);
   }
 }
-__global__ void __launch_bounds__(128) k_geom_write(DreAccum A, DreStep S, DreEvt* __restrict__ evt, const int* __restrict__ evoff, int capE) {
+__global__ void __launch_bounds__(128, DRE_GEOM_MINB) k_geom_write(DreAccum A, DreStep S, DreEvt* __restrict__ evt, const int* __restrict__ evoff, int capE) {
   ph_geom_write(A, S, evt, evoff, capE);
 }
 
