@@ -204,7 +204,7 @@ __device__ __forceinline__ void ph_prep_geom(const DreAccum& A, const DreStep& S
   }
 }
 #ifndef DRE_GEOM_MINB
-#define DRE_GEOM_MINB 4     // resident 128-thread CTAs per SM the march kernels are compiled for (register cap 65536 / (128 * n))
+#define DRE_GEOM_MINB 6     // (A/B on B200: 4 -> 93.6, 6 -> 92.5, 8 -> 93.1 ms per TRUST-I solve) resident 128-thread CTAs per SM the march kernels are compiled for (register cap 65536 / (128 * n))
 #endif
 __global__ void __launch_bounds__(128, DRE_GEOM_MINB) k_prep_geom(DreAccum A, DreStep S, int cur, int* __restrict__ nev) { ph_prep_geom<128>(A, S, cur, nev); }
 
