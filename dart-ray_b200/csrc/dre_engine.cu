@@ -84,7 +84,8 @@ struct dre_engine {
   ListStore H[2], W[2], OUT;
   DBuf<int> u_nc, u_gid, u_nk, u_step, u_mode, u_task_seg;
   DBuf<int> selH, posH, selW, posW, extcnt, ext_seg, ext, ipx, gone, cand, ncand, nxt, hasprev, unit_of_ext, ntask, nreco,
-      task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt;
+      task_off, reco_off, reco_cnt, fH, fW, posOH, posOW, keptH, keptW, newHcnt, newWcnt, hhead, hlink;
+  DBuf<unsigned long long> hkey;   // sibling table of a step (dre_lists.cuh ph_fill_ext / ph_cand)
   DBuf<DreTask> tasks;
   DBuf<double> pkts;     // ray packets of the current step
   DBuf<DreCtl> ctl; DreCtl* h_ctl = nullptr; int* h_err = nullptr;   // control block of the step and its pinned host mirror
@@ -752,6 +753,7 @@ void ensure_step(dre_engine* e, int U, int capH, int capW, int capT, int keep_cu
     const size_t nx = (size_t)capH + capW;
     e->ext.ensure(nx); e->ipx.ensure(nx); e->gone.ensure(nx); e->cand.ensure(3 * nx); e->ncand.ensure(nx); e->nxt.ensure(nx); e->hasprev.ensure(nx);
     e->unit_of_ext.ensure(nx); e->ntask.ensure(nx); e->nreco.ensure(nx); e->task_off.ensure(nx + 1); e->reco_off.ensure(nx + 1);
+    e->hlink.ensure(nx); e->hkey.ensure(2 * (size_t)capW + 64); e->hhead.ensure(2 * (size_t)capW + 64);
     e->capH = capH; e->capW = capW;
   }
   if (capT > e->capT) {
@@ -776,6 +778,8 @@ DreStep make_step(dre_engine* e, int U) {
   S.unit_of_ext = e->unit_of_ext.p; S.ntask = e->ntask.p; S.nreco = e->nreco.p; S.task_off = e->task_off.p; S.reco_off = e->reco_off.p;
   S.reco_cnt = e->reco_cnt.p; S.keptH = e->keptH.p; S.keptW = e->keptW.p; S.newHcnt = e->newHcnt.p; S.newWcnt = e->newWcnt.p;
   S.fH = e->fH.p; S.fW = e->fW.p; S.posOH = e->posOH.p; S.posOW = e->posOW.p; S.tasks = e->tasks.p; S.pkts = e->pkts.p;
+  S.hkey = e->hkey.p; S.hhead = e->hhead.p; S.hlink = e->hlink.p;
+  S.hcap = (int)std::min<size_t>(std::min(e->hkey.cap, e->hhead.cap), 2 * (size_t)e->capW + 64 > 2147483000ull ? 2147483000ull : 2 * (size_t)e->capW + 64);
   S.pstride = dre_pkt_stride(e->g.L); S.capH = e->capH; S.capW = e->capW; S.capT = e->capT; S.ctl = e->ctl.p;
   S.scan_desc = e->scan_desc.p; S.desc_stride = e->desc_stride; S.err = e->errflag.p; S.steps = e->counters.p + CNT_N; S.kmax = DRE_MAXK;
   return S;
@@ -816,7 +820,7 @@ int enqueue_post(dre_engine* e, const DreStep& S, int cur, cudaStream_t st, bool
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.fH, S.posOH, &S.ctl->nT, 0, 5, S.fW, S.posOW, &S.ctl->nT, 0, 6), S.ctl, S.scan_desc, S.desc_stride, 5u, 1);
   k_step_unit_new<<<G, STEP_THREADS, 0, st>>>(S, cur);
   k_scan_jobs<<<dim3(Gs, 2), SCAN_THREADS, 0, st>>>(scan_jobs(S.newHcnt, S.H[1 - cur].seg, Un, 0, 7, S.newWcnt, S.W[1 - cur].seg, Un, 0, 8), S.ctl, S.scan_desc, S.desc_stride, 7u, 1);
-  k_step_build<<<e->sm_count * 4, STEP_THREADS, 0, st>>>(S, cur, e->g.L);
+  k_step_build<<<e->sm_count * 6, STEP_THREADS, 0, st>>>(S, cur, e->g.L);
   k_step_next<<<G, STEP_THREADS, 0, st>>>(S, cur);
   CK(cudaMemcpyAsync(e->h_ctl, S.ctl, sizeof(DreCtl), cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(e->h_err, S.err, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -839,6 +843,7 @@ void step_graphs(dre_engine* e, const DreAccum& A, const DreStep& S, int cur) {
   kp(S.selH); kp(S.posH); kp(S.selW); kp(S.posW); kp(S.extcnt); kp(S.ext_seg); kp(S.ext); kp(S.ipx); kp(S.gone); kp(S.cand); kp(S.ncand);
   kp(S.nxt); kp(S.hasprev); kp(S.unit_of_ext); kp(S.ntask); kp(S.nreco); kp(S.task_off); kp(S.reco_off); kp(S.reco_cnt); kp(S.keptH);
   kp(S.keptW); kp(S.newHcnt); kp(S.newWcnt); kp(S.fH); kp(S.fW); kp(S.posOH); kp(S.posOW); kp(S.tasks); kp(S.pkts); kp(S.pstride);
+  kp(S.hkey); kp(S.hhead); kp(S.hlink); kp(S.hcap);
   kp(S.capH); kp(S.capW); kp(S.capT); kp(S.ctl); kp(S.scan_desc); kp(S.desc_stride); kp(S.err); kp(S.steps); kp(S.kmax);
   const int mode = MODE, L = e->g.L, smc = e->sm_count, split = e->opt_split;
   kp(mode); kp(L); kp(smc); kp(split); kp(e->nev.p);
@@ -1022,7 +1027,7 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     e->ftab_budget = std::min(e->ftab_budget, e->ftab_bytes + (size_t)(0.15 * (double)free_b));
   }
   const int L = e->g.L;
-  const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0) + 12.0 * 24.0 * 1.5;   // + ~12 events of 24 B per ray
+  const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0 + 2.0 * 12.0 + 8.0) + 12.0 * 24.0 * 1.5;   // + ~12 events of 24 B per ray
   const double max_cap = std::min(2.0e9, std::max(1.0e6, (double)e->list_budget / bytes_per_cap));
   double& est = e->per_unit_est[rt_type % 16];   // max over steps of the per-list need / units
   double per_unit = 0;

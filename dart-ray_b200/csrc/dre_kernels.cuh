@@ -146,22 +146,36 @@ template <int NT>
 __device__ __forceinline__ void dre_prep_lum(const DreDev& g, const DreAccum& A, const DreList& H, const DreList& W, int t0, int nrays,
                                              double* __restrict__ pkts, int pstride, const int (*s_e)[NT], const int* s_mode,
                                              const int* s_w, const int* s_nc, const int* s_dk, const int* s_dip) {
-  const int L = g.L;
-  for (int idx = threadIdx.x; idx < nrays * L; idx += blockDim.x) {
-    const int i = idx / L, l = idx - i * L;
-    const int mode = s_mode[i];
-    const double* lumS = s_w[i] ? W.lum : H.lum;
-    double v;
-    if (mode == 2) {                                            // assign_src_lum :3043-3071
-      const int ik = g.ik_sca[l];
-      const int ip = (ik >= 0) ? (s_dip[i] >> (2 * (s_dk[i] - g.class_kp[ik]))) : 0;
-      v = A.prev[(size_t)s_nc[i] * g.ROW + g.off[l] + ip] * g.npix_hp[l];
-    } else if (mode == 1) {                                     // merged siblings: ray_list.f90:261-264
-      v = lumS[(size_t)s_e[0][i] * L + l];
-      v = v + lumS[(size_t)s_e[1][i] * L + l]; v = v + lumS[(size_t)s_e[2][i] * L + l]; v = v + lumS[(size_t)s_e[3][i] * L + l];
-      v = v / 4;
-    } else v = lumS[(size_t)s_e[0][i] * L + l];
-    pkts[(size_t)(t0 + i) * pstride + DRE_PKT_HDR + l] = v;
+  const int L = g.L, n = nrays * L;
+  // element idx = ray i, wavelength l; four elements per round (loads first, then stores: four gathers in flight per
+  // thread), (i, l) advanced without divisions
+  const int di = NT / L, dl = NT - di * L;
+  int i = (int)threadIdx.x / L, l = (int)threadIdx.x - i * L;
+  for (int idx = threadIdx.x; idx < n;) {
+    double v[4]; size_t dst[4]; int cnt = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (idx < n) {
+        const int mode = s_mode[i];
+        const double* lumS = s_w[i] ? W.lum : H.lum;
+        double x;
+        if (mode == 2) {                                            // assign_src_lum :3043-3071
+          const int ik = g.ik_sca[l];
+          const int ip = (ik >= 0) ? (s_dip[i] >> (2 * (s_dk[i] - g.class_kp[ik]))) : 0;
+          x = A.prev[(size_t)s_nc[i] * g.ROW + g.off[l] + ip] * g.npix_hp[l];
+        } else if (mode == 1) {                                     // merged siblings: ray_list.f90:261-264
+          const double a0 = lumS[(size_t)s_e[0][i] * L + l], a1 = lumS[(size_t)s_e[1][i] * L + l];
+          const double a2 = lumS[(size_t)s_e[2][i] * L + l], a3 = lumS[(size_t)s_e[3][i] * L + l];
+          x = a0; x = x + a1; x = x + a2; x = x + a3;
+          x = x / 4;
+        } else x = lumS[(size_t)s_e[0][i] * L + l];
+        v[k] = x; dst[k] = (size_t)(t0 + i) * pstride + DRE_PKT_HDR + l; cnt = k + 1;
+      }
+      idx += NT; i += di; l += dl;
+      if (l >= L) { l -= L; i++; }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) if (k < cnt) pkts[dst[k]] = v[k];
   }
 }
 

@@ -45,6 +45,8 @@ struct DreStep {
   int *ext, *ipx, *gone, *cand, *ncand, *nxt, *hasprev, *unit_of_ext, *ntask, *nreco, *task_off, *reco_off;   // [capH + capW (+1)]
   int *reco_cnt, *keptH, *keptW, *newHcnt, *newWcnt;   // [U]
   int *fH, *fW, *posOH, *posOW;      // [capT (+1)]
+  unsigned long long* hkey; int* hhead; int hcap;   // [hcap] open-addressing table of the step: (unit, parent pixel) -> chain of extracted LOW entries
+  int* hlink;                        // [capH + capW] next entry of the chain
   DreTask* tasks;                    // [capT]
   double* pkts; int pstride;         // [capT] ray packets
   int capH, capW, capT;
@@ -150,6 +152,14 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* 
 // ---------------------------------------------------------------------------------------
 // step kernels
 // ---------------------------------------------------------------------------------------
+// Sibling table of a step: slots in use for a LOW list of nW entries (at most nW entries are extracted: load <= 1/2)
+#define DRE_HEMPTY 0xffffffffffffffffull
+__device__ __forceinline__ int dre_hsize(const DreStep& S, int nW) { return min(S.hcap, 2 * nW + 64); }
+__device__ __forceinline__ unsigned dre_hslot(unsigned long long key, int hsize) {
+  key ^= key >> 30; key *= 0xbf58476d1ce4e5b9ull; key ^= key >> 27; key *= 0x94d049bb133111ebull; key ^= key >> 31;
+  return __umulhi((unsigned)key, (unsigned)hsize);
+}
+
 // Start of a step: mode of each unit -- extract from HIGH if it has entries, else from LOW (ray_list.f90:120,167) -- and the
 // selection flags of extract_ray_list: HIGH entries with nside == nside/2, LOW entries with nside == 2*nside.
 __device__ __forceinline__ void ph_select(const DreStep& S, int cur) {
@@ -165,6 +175,7 @@ __device__ __forceinline__ void ph_select(const DreStep& S, int cur) {
     const int nh = H.seg[i + 1] - H.seg[i], nw = W.seg[i + 1] - W.seg[i];
     u.mode[i] = nh > 0 ? 1 : (nw > 0 ? 2 : 0);
   }
+  GRID_LOOP(q, dre_hsize(S, nW)) { S.hkey[q] = DRE_HEMPTY; S.hhead[q] = -1; }   // sibling table of this step (ph_fill_ext, ph_cand)
   GRID_LOOP(i, nH) {                     // a unit with HIGH entries is in mode 1
     const int un = H.unit[i];
     S.selH[i] = (META_NSK(H.meta[i]) == u.nk[un] - 1) ? 1 : 0;
@@ -201,8 +212,22 @@ __device__ __forceinline__ void ph_fill_ext(const DreStep& S, int cur) {
       const int x = S.ext_seg[un] + (pos[i] - pos[l.seg[un]]);
       S.ext[x] = i; S.unit_of_ext[x] = un;
       S.gone[x] = 0; S.hasprev[x] = 0;
-      if (which == 2) S.ipx[x] = l.dir_ipix[i] >> (2 * (META_DIRK(l.meta[i]) - u.nk[un]));
-      else S.ipx[x] = -1;
+      if (which == 2) {
+        const int ip = l.dir_ipix[i] >> (2 * (META_DIRK(l.meta[i]) - u.nk[un]));
+        S.ipx[x] = ip;
+        // chain of the extracted entries of this (unit, parent pixel): ph_cand finds the siblings there instead of
+        // scanning the rest of the unit's segment
+        const unsigned long long key = ((unsigned long long)(unsigned)un << 32) | (unsigned)ip;
+        const int hs = dre_hsize(S, l.seg[S.ctl->U]);
+        unsigned q = dre_hslot(key, hs);
+        for (;;) {
+          const unsigned long long o = atomicCAS(&S.hkey[q], DRE_HEMPTY, key);
+          if (o == DRE_HEMPTY || o == key) break;
+          q = (q + 1 == (unsigned)hs) ? 0u : q + 1;
+        }
+        S.hlink[x] = atomicExch(&S.hhead[q], x);
+        S.ncand[x] = (int)q;            // slot, read back by ph_cand before it writes the candidate count
+      } else S.ipx[x] = -1;
     }
   }
 }
@@ -217,17 +242,39 @@ __device__ __forceinline__ void ph_cand(const DreStep& S, int cur) {
     const int un = S.unit_of_ext[x];
     if (u.mode[un] != 2) { S.ncand[x] = 0; S.nxt[x] = -1; continue; }
     const int i = S.ext[x];
-    const int end = S.ext_seg[un + 1];
     const int ip = S.ipx[x], isel = META_ISEL(w.meta[i]);
     const double dpl = w.dplane[i];
+    // the later entries of the chain, in list order (a chain holds the <= 4 rays of one parent pixel; longer chains take
+    // the scan below)
+    int later[8], nl = 0;
+    bool scan = false;
+    for (int y = S.hhead[S.ncand[x]]; y >= 0; y = S.hlink[y]) {
+      if (y <= x) continue;
+      if (nl == 8) { scan = true; break; }
+      int k = nl++;
+      while (k > 0 && later[k - 1] > y) { later[k] = later[k - 1]; k--; }
+      later[k] = y;
+    }
     int n = 0, first = -1;
-    for (int y = x + 1; y < end && (n < 3 || first < 0); y++) {
-      if (S.ipx[y] != ip) continue;
-      if (first < 0) first = y;
-      if (n == 3) break;
-      const int j = S.ext[y];
-      if (META_ISEL(w.meta[j]) != isel) continue;
-      if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) S.cand[3 * (size_t)x + n++] = y;
+    if (!scan) {
+      for (int q = 0; q < nl && (n < 3 || first < 0); q++) {
+        const int y = later[q];
+        if (first < 0) first = y;
+        if (n == 3) break;
+        const int j = S.ext[y];
+        if (META_ISEL(w.meta[j]) != isel) continue;
+        if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) S.cand[3 * (size_t)x + n++] = y;
+      }
+    } else {
+      const int end = S.ext_seg[un + 1];
+      for (int y = x + 1; y < end && (n < 3 || first < 0); y++) {
+        if (S.ipx[y] != ip) continue;
+        if (first < 0) first = y;
+        if (n == 3) break;
+        const int j = S.ext[y];
+        if (META_ISEL(w.meta[j]) != isel) continue;
+        if (fabs(dpl - w.dplane[j]) / fabs(dpl) < (double)0.001f) S.cand[3 * (size_t)x + n++] = y;
+      }
     }
     S.ncand[x] = n;
     S.nxt[x] = first;                 // chain of the entries of this unit with the same parent pixel
@@ -338,16 +385,39 @@ __device__ __forceinline__ int dre_dst_out(const DreStep& S, const DreList& Hn, 
 
 // Rebuild of both lists in one launch: kept entries (stable), failed merges re-queued on HIGH as ray_type_reco with the
 // current nside (ray_list.f90:276-291, add_to_high_ray_list :463-521), and the go_high / go_low outcomes of the ray-march
-// kernel in task (= processing) order.  The luminosity rows are copied by L consecutive threads per entry (coalesced).
+// kernel in task (= processing) order.  A group of G consecutive lanes moves one entry: its destination slot is looked up
+// once, lane 0 copies the header and the lanes copy the luminosity row as 16-byte pieces (two entries per round, so that
+// the two index chains overlap).
+__device__ __forceinline__ void dre_copy_lum(double* __restrict__ d, const double* __restrict__ s, int L, int sub, int G) {
+  if ((L & 1) == 0) {
+    const double2* s2 = reinterpret_cast<const double2*>(s); double2* d2 = reinterpret_cast<double2*>(d);
+    for (int l = sub; l < (L >> 1); l += G) d2[l] = s2[l];
+  } else for (int l = sub; l < L; l += G) d[l] = s[l];
+}
 __device__ __forceinline__ void ph_build(const DreStep& S, int cur, int L) {
   if (S.ctl->abort) return;
   const DreList Hc = S.H[cur], Wc = S.W[cur], Hn = S.H[1 - cur], Wn = S.W[1 - cur];
   const DreUnits u = S.u;
   const int U = S.ctl->U, nH = Hc.seg[U], nW = Wc.seg[U], nExt = S.ext_seg[U], nT = S.ctl->nT;
-  // ---- headers
-  GRID_LOOP(i, nH) { const int di = dre_dst_kept(Hn, Hc, S.selH, S.posH, i); if (di >= 0) dre_copy_entry_hdr(Hn, di, Hc, i, Hc.unit[i]); }
-  GRID_LOOP(i, nW) { const int di = dre_dst_kept(Wn, Wc, S.selW, S.posW, i); if (di >= 0) dre_copy_entry_hdr(Wn, di, Wc, i, Wc.unit[i]); }
-  GRID_LOOP(x, nExt) {
+  const int Lv = (L & 1) ? L : (L >> 1);
+  const int G = Lv <= 4 ? 4 : (Lv <= 8 ? 8 : (Lv <= 16 ? 16 : 32));
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int sub = tid & (G - 1), gid = tid / G, ng = (gridDim.x * blockDim.x) / G;
+  // ---- kept entries of the two old lists
+  for (int w = 0; w < 2; w++) {
+    const DreList& src = w ? Wc : Hc; const DreList& dst = w ? Wn : Hn;
+    const int* sel = w ? S.selW : S.selH; const int* pos = w ? S.posW : S.posH;
+    const int n = w ? nW : nH;
+    for (int i = gid; i < n; i += 2 * ng) {
+      const int i1 = i + ng;
+      const int d0 = dre_dst_kept(dst, src, sel, pos, i);
+      const int d1 = (i1 < n) ? dre_dst_kept(dst, src, sel, pos, i1) : -1;
+      if (d0 >= 0) { if (sub == 0) dre_copy_entry_hdr(dst, d0, src, i, src.unit[i]); dre_copy_lum(dst.lum + (size_t)d0 * L, src.lum + (size_t)i * L, L, sub, G); }
+      if (d1 >= 0) { if (sub == 0) dre_copy_entry_hdr(dst, d1, src, i1, src.unit[i1]); dre_copy_lum(dst.lum + (size_t)d1 * L, src.lum + (size_t)i1 * L, L, sub, G); }
+    }
+  }
+  // ---- groups whose merge failed: leader and members go to HIGH as ray_type_reco
+  for (int x = gid; x < nExt; x += ng) {
     const int nr = S.nreco[x];
     if (nr == 0) continue;
     const int un = S.unit_of_ext[x];
@@ -355,46 +425,24 @@ __device__ __forceinline__ void ph_build(const DreStep& S, int cur, int L) {
     for (int m = 0; m < nr; m++) {
       const int si = (m == 0) ? S.ext[x] : S.ext[S.cand[3 * (size_t)x + m - 1]];
       const int di = base + m;
-      dre_copy_entry_hdr(Hn, di, Wc, si, un);
-      const unsigned mt = Wc.meta[si];
-      const int isel = META_ISEL(mt);
-      Hn.meta[di] = dre_meta(META_DIRK(mt), u.nk[un], isel, RT_RECO);
-      if (isel == 0) { Hn.dplane[di] = 0.; Hn.prev[di] = 0.; }
+      if (sub == 0) {
+        dre_copy_entry_hdr(Hn, di, Wc, si, un);
+        const unsigned mt = Wc.meta[si];
+        const int isel = META_ISEL(mt);
+        Hn.meta[di] = dre_meta(META_DIRK(mt), u.nk[un], isel, RT_RECO);
+        if (isel == 0) { Hn.dplane[di] = 0.; Hn.prev[di] = 0.; }
+      }
+      dre_copy_lum(Hn.lum + (size_t)di * L, Wc.lum + (size_t)si * L, L, sub, G);
     }
   }
-  GRID_LOOP(t, nT) {
-    int toH = 0;
-    const int di = dre_dst_out(S, Hn, Wn, t, toH);
-    if (di >= 0) dre_copy_entry_hdr(toH ? Hn : Wn, di, S.OUT, t, S.tasks[t].unit);
-  }
-  // ---- luminosity rows
-  const long long gsz = (long long)gridDim.x * blockDim.x, g0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  for (long long q = g0; q < (long long)nH * L; q += gsz) {
-    const int i = (int)(q / L), l = (int)(q - (long long)i * L);
-    const int di = dre_dst_kept(Hn, Hc, S.selH, S.posH, i);
-    if (di >= 0) Hn.lum[(size_t)di * L + l] = Hc.lum[(size_t)i * L + l];
-  }
-  for (long long q = g0; q < (long long)nW * L; q += gsz) {
-    const int i = (int)(q / L), l = (int)(q - (long long)i * L);
-    const int di = dre_dst_kept(Wn, Wc, S.selW, S.posW, i);
-    if (di >= 0) Wn.lum[(size_t)di * L + l] = Wc.lum[(size_t)i * L + l];
-  }
-  for (long long q = g0; q < (long long)nExt * L; q += gsz) {
-    const int x = (int)(q / L), l = (int)(q - (long long)x * L);
-    const int nr = S.nreco[x];
-    if (nr == 0) continue;
-    const int un = S.unit_of_ext[x];
-    const int base = Hn.seg[un] + S.keptH[un] + (S.reco_off[x] - S.reco_off[S.ext_seg[un]]);
-    for (int m = 0; m < nr; m++) {
-      const int si = (m == 0) ? S.ext[x] : S.ext[S.cand[3 * (size_t)x + m - 1]];
-      Hn.lum[(size_t)(base + m) * L + l] = Wc.lum[(size_t)si * L + l];
-    }
-  }
-  for (long long q = g0; q < (long long)nT * L; q += gsz) {
-    const int t = (int)(q / L), l = (int)(q - (long long)t * L);
-    int toH = 0;
-    const int di = dre_dst_out(S, Hn, Wn, t, toH);
-    if (di >= 0) (toH ? Hn : Wn).lum[(size_t)di * L + l] = S.OUT.lum[(size_t)t * L + l];
+  // ---- outcomes of the ray-march kernel
+  for (int t = gid; t < nT; t += 2 * ng) {
+    const int t1 = t + ng;
+    int h0 = 0, h1 = 0;
+    const int d0 = dre_dst_out(S, Hn, Wn, t, h0);
+    const int d1 = (t1 < nT) ? dre_dst_out(S, Hn, Wn, t1, h1) : -1;
+    if (d0 >= 0) { const DreList& dst = h0 ? Hn : Wn; if (sub == 0) dre_copy_entry_hdr(dst, d0, S.OUT, t, S.tasks[t].unit); dre_copy_lum(dst.lum + (size_t)d0 * L, S.OUT.lum + (size_t)t * L, L, sub, G); }
+    if (d1 >= 0) { const DreList& dst = h1 ? Hn : Wn; if (sub == 0) dre_copy_entry_hdr(dst, d1, S.OUT, t1, S.tasks[t1].unit); dre_copy_lum(dst.lum + (size_t)d1 * L, S.OUT.lum + (size_t)t1 * L, L, sub, G); }
   }
 }
 
@@ -429,5 +477,5 @@ __global__ void __launch_bounds__(STEP_THREADS) k_step_resolve(DreStep S, int cu
 __global__ void __launch_bounds__(STEP_THREADS) k_step_tasks(DreStep S, int cur) { ph_tasks(S, cur); }
 __global__ void __launch_bounds__(STEP_THREADS) k_step_out_flags(DreStep S) { ph_out_flags(S); }
 __global__ void __launch_bounds__(STEP_THREADS) k_step_unit_new(DreStep S, int cur) { ph_unit_new(S, cur); }
-__global__ void __launch_bounds__(STEP_THREADS) k_step_build(DreStep S, int cur, int L) { ph_build(S, cur, L); }
+__global__ void __launch_bounds__(STEP_THREADS, 6) k_step_build(DreStep S, int cur, int L) { ph_build(S, cur, L); }
 __global__ void __launch_bounds__(STEP_THREADS) k_step_next(DreStep S, int cur) { ph_next(S, cur); }
