@@ -1426,6 +1426,46 @@ int dre_locate_points(dre_engine* e, int32_t npts, const double* xyz, const int3
   DRE_CATCH(e)
 }
 
+// ---- dre_locate_points without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: graph capture, serving loops, harnesses that forbid it).  The staging buffers of
+// k_locate -- the points, their cc_old and the located cells -- live in ONE file-scope device array that every GPU loading the
+// library holds until exit: DRE_NOALLOC_MAX_POINTS * 32 B = 2 MiB.  Layout: xyz (3 doubles per point) | cc_old | cell_out.
+// Host code must not use the symbol's name as a pointer (it is a host-side stand-in): the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.  All calls share the array and it keeps the last call's
+// contents: calls that overlap on one GPU (two engines, two host threads) race.
+#define DRE_NOALLOC_MAX_POINTS 65536
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)DRE_NOALLOC_MAX_POINTS * 32];
+static unsigned char* g_noalloc_ptr[64];     // device address of the array, per device
+
+int dre_locate_points_noalloc(dre_engine* e, int32_t npts, const double* xyz, const int32_t* cc_old, int32_t* cell_out) {
+  DRE_TRY(e)
+  CK(cudaSetDevice(e->device));
+  DRE_REQUIRE(e->have_grid && e->have_params, "dre_locate_points_noalloc: grid/params not set");
+  DRE_REQUIRE(npts <= DRE_NOALLOC_MAX_POINTS, "dre_locate_points_noalloc: more than 65536 points (the static scratch array holds no more; use dre_locate_points)");
+  DRE_REQUIRE(e->device >= 0 && e->device < 64, "dre_locate_points_noalloc: device index beyond 63");
+  if (npts <= 0) return 0;
+  DRE_REQUIRE(xyz && cc_old && cell_out, "dre_locate_points_noalloc: null argument");
+  unsigned char*& base = g_noalloc_ptr[e->device];
+  if (!base) {
+    void* p = nullptr;
+    const cudaError_t rc = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (rc != cudaSuccess || !p) throw DreError{std::string("dre_locate_points_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(rc)};
+    base = static_cast<unsigned char*>(p);
+  }
+  double* dx = reinterpret_cast<double*>(base);
+  int* dc = reinterpret_cast<int*>(base + (size_t)DRE_NOALLOC_MAX_POINTS * 24);
+  int* dout = reinterpret_cast<int*>(base + (size_t)DRE_NOALLOC_MAX_POINTS * 28);
+  sync_g(e);
+  CK(cudaMemcpyAsync(dx, xyz, (size_t)3 * npts * 8, cudaMemcpyHostToDevice, e->st));
+  CK(cudaMemcpyAsync(dc, cc_old, (size_t)npts * 4, cudaMemcpyHostToDevice, e->st));
+  CK(cudaMemsetAsync(dout, 0xff, (size_t)npts * 4, e->st));      // the previous call's cells must not survive a failed launch
+  (e->n_launch++, k_locate)<<<cdiv(npts, 128), 128, 0, e->st>>>(npts, dx, dc, dout);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(cell_out, dout, (size_t)npts * 4, cudaMemcpyDeviceToHost, e->st));
+  CK(cudaStreamSynchronize(e->st));
+  DRE_CATCH(e)
+}
+
 int dre_pix2vec(dre_engine* e, int32_t nside, int32_t npix, const int32_t* ipix, double* theta, double* phi, double* vec) {
   DRE_TRY(e)
   CK(cudaSetDevice(e->device));

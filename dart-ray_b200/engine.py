@@ -22,7 +22,7 @@ SYMBOLS = [
     "dre_get_unique_id", "dre_create", "dre_destroy", "dre_last_error", "dre_set_grid", "dre_set_opacity",
     "dre_set_sources", "dre_set_params", "dre_upload", "dre_download", "dre_zero", "dre_run_pass_resident",
     "dre_run_pass", "dre_run_pass_2d", "dre_scaspe_symmetry_index", "dre_run_iobs", "dre_allreduce", "dre_prepare_scatt", "dre_dust_emission", "dre_calc_sed", "dre_make_maps", "dre_make_maps_in", "dre_build_source_list",
-    "dre_locate_points", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_get_quanta", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
+    "dre_locate_points", "dre_locate_points_noalloc", "dre_pix2vec", "dre_set_record", "dre_get_records", "dre_set_option", "dre_get_quanta", "dre_eval_exp", "dre_mark", "dre_elapsed_ms", "dre_launch_count",
 ]
 
 
@@ -296,6 +296,15 @@ class Engine:
         cc_old = np.ascontiguousarray(cc_old, dtype=np.int32)
         out = np.zeros(len(cc_old), dtype=np.int32)
         self._ck(self.l.dre_locate_points(self.h, C.c_int32(len(cc_old)), abi.dptr(xyz), abi.iptr(cc_old), abi.iptr(out)))
+        return out
+
+    def locate_noalloc(self, xyz, cc_old):
+        """dre_locate_points_noalloc: the same locator through the library's static scratch array (<= 65 536 points, no allocation)."""
+        self.set_params(abi.RTT_DIR_CELL)
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+        cc_old = np.ascontiguousarray(cc_old, dtype=np.int32)
+        out = np.zeros(len(cc_old), dtype=np.int32)
+        self._ck(self.l.dre_locate_points_noalloc(self.h, C.c_int32(len(cc_old)), abi.dptr(xyz), abi.iptr(cc_old), abi.iptr(out)))
         return out
 
     def eval_exp(self, x):

@@ -202,6 +202,13 @@ int dre_build_source_list(dre_engine*, int rt_type, int32_t* n_sources, int32_t*
 /* find_cc_new2 rt_routines.f90:1962: locate points; cell_out=-1 when outside the model */
 int dre_locate_points(dre_engine*, int32_t npts, const double* xyz /*(3,npts)*/,
                       const int32_t* cc_old /*(npts)*/, int32_t* cell_out /*(npts)*/);
+/* dre_locate_points for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same arguments and results as
+ * dre_locate_points; the device staging lives in a static 2-MiB device array of the library, so npts <= 65536
+ * (DRE_NOALLOC_MAX_POINTS; larger calls are rejected with an error) and no cudaMalloc / cudaFree is called.  Every call on a
+ * GPU shares that array: calls that overlap on one GPU race. */
+int dre_locate_points_noalloc(dre_engine*, int32_t npts, const double* xyz /*(3,npts)*/,
+                              const int32_t* cc_old /*(npts)*/, int32_t* cell_out /*(npts)*/);
 /* pix2ang_nest + calc_cproj (healpix_routines.f90:30, rt_routines.f90:1945) */
 int dre_pix2vec(dre_engine*, int32_t nside, int32_t npix, const int32_t* ipix,
                 double* theta, double* phi, double* vec /*(3,npix)*/);
