@@ -107,6 +107,7 @@ struct dre_engine {
   size_t ftab_budget = (size_t)24 << 30, ftab_bytes = 0; unsigned ftab_skipped = 0;   // phase-function tables: at most 24 GiB or 15 % of the free memory
   size_t list_budget = 0;          // bytes the ray lists of a batch may take (half of the memory free after configuration)
   double per_unit_est[16] = {0};   // list entries per unit of the last pass, by rt_type
+  double per_unit_evt[16] = {0};   // march events per unit (largest step), by rt_type
   long long last_launches = 0, n_launch = 0, launch_mark = 0;
   cudaEvent_t marks[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
@@ -335,6 +336,7 @@ int dre_set_opacity(dre_engine* e, int32_t L, const double* dens_arr, const doub
   e->lumcell.zero(NL, e->st); g.lumcell = e->lumcell.p;
   CK(cudaStreamSynchronize(e->st));
   for (double& x : e->per_unit_est) x = 0;
+  for (double& x : e->per_unit_evt) x = 0;
   e->list_budget = 0;
   e->capH = e->capW = e->capT = 0;     // the luminosity rows of the lists are lnum wide: re-sized by the next pass
   e->have_sym = false;
@@ -862,7 +864,7 @@ void step_graphs(dre_engine* e, const DreAccum& A, const DreStep& S, int cur) {
   sg.key = key;
 }
 
-struct BatchStats { long long peak = 0; int maxH = 0, maxW = 0, maxT = 0; };
+struct BatchStats { long long peak = 0; int maxH = 0, maxW = 0, maxT = 0, maxE = 0; };
 
 // one batch of units through all its resolution steps (main_dir_loop rt_routines.f90:1366-1442 for every unit at once)
 template <int MODE>
@@ -941,7 +943,7 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
     }
     if (c.nT > 0) { float ms = 0; CK(cudaEventElapsedTime(&ms, e->ev[2], e->ev[3])); e->last_kernel_ms += ms; e->last_launches++; }
     bs.peak = std::max(bs.peak, (long long)nH + nW + c.nT + c.nH2 + c.nW2);
-    bs.maxH = std::max(bs.maxH, std::max(c.needH, c.nH2)); bs.maxW = std::max(bs.maxW, std::max(c.needW, c.nW2)); bs.maxT = std::max(bs.maxT, c.nT);
+    bs.maxH = std::max(bs.maxH, std::max(c.needH, c.nH2)); bs.maxW = std::max(bs.maxW, std::max(c.needW, c.nW2)); bs.maxT = std::max(bs.maxT, c.nT); bs.maxE = std::max(bs.maxE, c.needE);
     nH = c.nH2; nW = c.nW2; cur ^= 1;
     if (c.active == 0) break;
     nkmask = (unsigned)c.nkmask;
@@ -1030,7 +1032,8 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
   const double bytes_per_cap = 1.25 * (5.0 * (28.0 + 8.0 * L) + 8.0 * dre_pkt_stride(L) + 32.0 + 16.0 + 16.0 + 2.0 * 15.0 * 4.0 + 2.0 * 12.0 + 8.0) + 12.0 * 24.0 * 1.5;   // + ~12 events of 24 B per ray
   const double max_cap = std::min(2.0e9, std::max(1.0e6, (double)e->list_budget / bytes_per_cap));
   double& est = e->per_unit_est[rt_type % 16];   // max over steps of the per-list need / units
-  double per_unit = 0;
+  double& est_e = e->per_unit_evt[rt_type % 16];
+  double per_unit = 0, per_unit_e = 0;
   // nothing known about this pass type yet: a probe batch of 16 384 units measures the entries per unit first
   long long U_next = est > 0 ? (long long)(max_cap / (1.25 * est)) : 16384;
   U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
@@ -1045,16 +1048,24 @@ int dre_run_pass_resident(dre_engine* e, int rt_type, int iterations, dre_counte
     const int U = (int)std::min<long long>(U_next, mine - u0);
     int cap0 = (int)std::min(max_cap, std::max(4.0 * U, 1.25 * std::max(per_unit, est) * U) + 1024.0);
     if (e->opt_cap0 > 0) cap0 = e->opt_cap0;   // test hook: start small so that steps are refused and the buffers grow
+    // the event buffer of the march follows the same rule: sized before the batch from the events per unit seen so far, so
+    // that a larger batch than the last one does not have its largest step refused first
+    if (mode == MODE_DEP && e->opt_split && e->opt_cap0 <= 0) {
+      const double want = std::min(2147483000.0, 1.25 * std::max(per_unit_e, est_e) * U + 1024.0);
+      if (want > (double)e->capE) { e->evt.release(); e->evt.ensure((size_t)want, 1.0); e->capE = (int)want; }
+    }
     const BatchStats bs = (mode == MODE_PRECALC) ? run_batch_mode<MODE_PRECALC>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap, pmul)
                                                  : run_batch_mode<MODE_DEP>(e, A, (int)u0, U, cap0, cap0, cap0, max_cap, pmul);
     e->peak_entries = std::max(e->peak_entries, bs.peak);
     per_unit = std::max(per_unit, (double)std::max(bs.maxH, std::max(bs.maxW, bs.maxT)) / U);
+    per_unit_e = std::max(per_unit_e, (double)bs.maxE / U);
     if (getenv("DRE_VERBOSE")) fprintf(stderr, "[dre] rt_type %d batch at unit %lld: %d units, peak %lld list entries, per-list need %d / %d / %d (%.1f per unit), capacity %d\n",
                                        rt_type, u0, U, bs.peak, bs.maxH, bs.maxW, bs.maxT, per_unit, e->capH);
     u0 += U;
     U_next = (long long)(max_cap / (1.25 * std::max(per_unit, est)));   // x1.25: headroom for units richer than those seen so far
     U_next = std::max<long long>(48, std::min<long long>(U_next, e->opt_batch_units));
   }
+  est_e = std::max(est_e, per_unit_e);
   est = std::max(est, per_unit);   // high-water mark (the scattering iterations share one rt_type and shrink)
   CK(cudaEventRecord(e->ev[1], e->st));
   CK(cudaStreamSynchronize(e->st));

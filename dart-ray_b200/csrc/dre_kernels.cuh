@@ -422,7 +422,9 @@ __global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int un
   // batch is a sample of the whole model (neighbouring cells have similar ray trees: in cell order the first batch says little
   // about the list sizes of the later ones).  The global unit id (record / checksum key) stays source_ordinal*48 + sector.
   const long long gq = (long long)rank_off + (long long)(unit0 + i) * stride;
-  const int sector = (int)(gq % 48);
+  // the sector is rotated by the source position: with 48 % nranks == 0 a rank would otherwise trace the same sectors of every
+  // source (the up-looking ones of a disc, say) and the ranks would finish a pass at different times
+  const int sector = (int)((gq % 48 + gq / 48) % 48);
   const int sord = (int)(((gq / 48) * (long long)pmul) % nsrc);
   const int gid = sord * 48 + sector;
   const int nc = srclist[sord];
