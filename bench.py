@@ -97,6 +97,10 @@ class ClockSampler:
         sm = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
         r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
         self.rows.append((sm, self.sm_max, [name for bit, name in self.bits if r & bit]))
+        if os.environ.get("BENCH_DIAG"):
+            mem = float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_MEM))
+            pw = n.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+            print(f"[bench clocks] t={time.perf_counter():.3f} sm={sm:.0f} mem={mem:.0f} power_w={pw:.0f} reasons={r:#x}", file=sys.stderr)
 
     def _sample_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -116,23 +120,26 @@ class ClockSampler:
                     self._sample_smi()
             except Exception:
                 pass
-            self.stop.wait(0.1 if self.nvml is not None else 0.5)
+            self.stop.wait((0.05 if os.environ.get("BENCH_DIAG") else 0.25) if self.nvml is not None else 0.5)
 
     def __enter__(self):
+        if os.environ.get("BENCH_NO_CLOCKS"):      # A/B switch for diagnostics: does the sampling disturb the solve?
+            return self
         self.th = threading.Thread(target=self._run, daemon=True)
         self.th.start()
         return self
 
     def __exit__(self, *a):
         self.stop.set()
-        self.th.join(timeout=6)
+        if self.th is not None:
+            self.th.join(timeout=6)
 
     def summary(self):
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
         sm = sorted(r[0] for r in self.rows)
         reasons = sorted({n for r in self.rows for n in r[2]})
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.rows[0][1], "reasons": reasons, "samples": len(self.rows),
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": self.rows[0][1], "reasons": reasons, "samples": len(self.rows),
                 "source": "NVML (in-process)" if self.nvml is not None else "nvidia-smi"}
 
 
@@ -153,19 +160,31 @@ def deposit_bytes(c):
 
 def solve_resident(eng, scene, abi, max_iterations=30):
     """precalc -> direct -> scattering iterations on device-resident state; returns the pass counters."""
+    diag = [] if os.environ.get("BENCH_DIAG") else None      # wall-clock segments of the solve (diagnostics only)
+    t_seg = time.perf_counter()
+
+    def seg(name):
+        nonlocal t_seg
+        if diag is not None:
+            t = time.perf_counter(); diag.append((name, round((t - t_seg) * 1e3, 3))); t_seg = t
+
     for a in (abi.ARR_U_FEST, abi.ARR_U_FINAL, abi.ARR_SCASPE, abi.ARR_SCASPE_PREV, abi.ARR_SCASPE_TOT, abi.ARR_LUM_LOST,
               abi.ARR_PSEL_AV):
         eng.zero(a)
+    seg("zero")
     eng.set_sources(scene.lumcell)
+    seg("set_sources")
     has_src, has_cell = scene.nsrc > 0, bool(np.any(scene.lumcell))
     cs = []
     mpi_t = [0.0]
     _rt_mpi = eng.rt_mpi
 
     def rt_mpi(rt):
+        seg("pass")
         t0 = time.perf_counter()
         _rt_mpi(rt)
         mpi_t[0] += time.perf_counter() - t0
+        seg("rt_mpi")
 
     eng_rt_mpi = rt_mpi
     if has_cell:
@@ -180,11 +199,15 @@ def solve_resident(eng, scene, abi, max_iterations=30):
     eng_rt_mpi(abi.RTT_DIR_SRC)
     tot = np.zeros(scene.lnum)
     for it in range(1, max_iterations + 1):
-        if eng.rt_prepare_scatt(it, tot):
+        done = eng.rt_prepare_scatt(it, tot)
+        seg("rt_prepare")
+        if done:
             break
         cs.append((f"scatt{it}", eng.rt_loop(abi.RTT_SCATT, it)))
         eng_rt_mpi(abi.RTT_SCATT)
     solve_resident.last_mpi_ms = mpi_t[0] * 1e3
+    if diag is not None:
+        print(f"[bench diag] t={time.perf_counter():.3f} " + " ".join(f"{n}={v}" for n, v in diag), file=sys.stderr)
     return cs
 
 
@@ -357,6 +380,7 @@ def main():
     ap.add_argument("--workload", default="trustI")
     ap.add_argument("--no-also", action="store_true", help="skip the secondary workloads (galaxy-shaped grid, MAGTAR)")
     ap.add_argument("--also", default="galaxy,magtar,nbody", help="comma-separated secondary workloads")
+    ap.add_argument("--prewarm-s", type=float, default=1.5, help="untimed solves for about this many seconds before the warm-up steps")
     ap.add_argument("--ref-budget-s", type=float, default=150.0, help="reference arm: stop starting new solves after this many seconds")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -375,7 +399,8 @@ def main():
     metric, unit = "ray-cell intersections/s (direct+scatter solve)", "intersections/s"
     config = {"workload": desc, "solve": "precalc + direct + scattering iterations to conv_en_lim=%g" % scene.conv_en_lim,
               "l2_policy": "L2 flushed (256 MB written) before every timed step; accumulator rows %.0f MB" %
-                           (scene.grid.ncell * (scene.lnum + int(scene.npix.sum())) * 8 / 1e6)}
+                           (scene.grid.ncell * (scene.lnum + int(scene.npix.sum())) * 8 / 1e6),
+              "prewarm": "untimed solves for about %.1f s before the --warmup steps (GPU wake-up)" % args.prewarm_s}
 
     if args.impl == "reference":
         if rank != 0:
@@ -451,8 +476,16 @@ def main():
         flush_buf.zero_()
         torch.cuda.synchronize()
 
-    def measure(e_, sc_, steps, warmup):
+    def measure(e_, sc_, steps, warmup, prewarm_s=0.0):
         """`steps` timed solves (device time between two events on the engine's stream, max over ranks)."""
+        # GPU wake-up before the warm-up steps: untimed solves for about --prewarm-s seconds.  The first solves of a process
+        # run up to 25 % slower than the steady state on some boxes even after three warm-up solves (profiles/r02_sweeps.md);
+        # every rank does the same number (the solves contain collectives)
+        if prewarm_s > 0:
+            t0 = time.perf_counter(); solve_resident(e_, sc_, abi); torch.cuda.synchronize()
+            t1 = maxr(time.perf_counter() - t0)
+            for _ in range(int(min(40, max(0, np.ceil(prewarm_s / max(t1, 1e-3)) - 1)))):
+                solve_resident(e_, sc_, abi)
         for _ in range(warmup):
             solve_resident(e_, sc_, abi)
         barrier()
@@ -477,11 +510,11 @@ def main():
         mpi_ms = maxr(getattr(solve_resident, "last_mpi_ms", 0.0))
         psum = float(sum(c.pass_ms for _, c in last))
         pass_minmax = [-maxr(-psum), maxr(psum)]     # fastest / slowest rank: device time inside the passes
-        return {"pass_minmax": pass_minmax, "mpi_ms": mpi_ms, "ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "abytes_all": abytes_all, "kms": kms, "last": last, "launches": launches,
+        return {"step_ms": [round(x, 3) for x in step_ms], "pass_minmax": pass_minmax, "mpi_ms": mpi_ms, "ms": ms, "isect": isect, "deposits": deposits, "abytes": abytes, "abytes_all": abytes_all, "kms": kms, "last": last, "launches": launches,
                 "trace_launches": int(sum(c.trace_launches for c in dep))}
 
     with ClockSampler(local_rank) as clk:
-        m = measure(eng, scene, args.steps, args.warmup)
+        m = measure(eng, scene, args.steps, args.warmup, args.prewarm_s)
     clocks = clk.summary()
     ms, isect, last = m["ms"], m["isect"], m["last"]
     value = isect / (ms * 1e-3)
@@ -529,7 +562,7 @@ def main():
             "s_per_wavelength": ms * 1e-3 / scene.lnum, "intersections_per_step": isect, "deposits_per_step": m["deposits"],
             "passes": {n: {"ms": round(c.pass_ms, 3), "kernel_ms": round(c.kernel_ms, 3), "intersections": c.intersections,
                            "deposits": c.deposits, "rays": c.rays, "steps": c.steps} for n, c in last},
-            "rt_mpi_ms_per_step": m["mpi_ms"], "rank_pass_ms_min_max": m["pass_minmax"], "roofline": roof}
+            "rt_mpi_ms_per_step": m["mpi_ms"], "rank_pass_ms_min_max": m["pass_minmax"], "ms_of_each_step": m["step_ms"], "ms_per_step_median": float(np.median(m["step_ms"])), "roofline": roof}
 
     # the smaller kernels of the path, once, on the state the last solve left on the device (device time of the pass from the
     # engine's CUDA events; host wall clock around the calls that return host arrays)
@@ -562,7 +595,7 @@ def main():
             m2 = measure(e2, sc2, n2, w2)
             also[w] = {"workload": desc2, "value": m2["isect"] / (m2["ms"] * 1e-3), "ms_per_step": m2["ms"],
                        "s_per_wavelength": m2["ms"] * 1e-3 / sc2.lnum, "intersections_per_step": m2["isect"],
-                       "rt_mpi_ms_per_step": m2["mpi_ms"], "roofline": roof_block(m2, w), "steps": n2, "warmup": w2}
+                       "rt_mpi_ms_per_step": m2["mpi_ms"], "ms_of_each_step": m2["step_ms"], "rank_pass_ms_min_max": m2["pass_minmax"], "roofline": roof_block(m2, w), "steps": n2, "warmup": w2}
             e2.close()
         line["also"] = also
 

@@ -97,7 +97,7 @@ struct dre_engine {
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_coop_work = 131072, opt_det = 0;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_coop_work = 131072, opt_det = 0, opt_sector_rot = 1;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -875,7 +875,7 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
   ensure_step(e, U, std::max(capH0, U), std::max(capW0, 64), std::max(capT0, 64), -1, 0, 0);
   DreStep S = make_step(e, U);
   int cur = 0, nH = U, nW = 0;
-  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(S, U, e->srclist.p, unit0, e->nranks, e->rank, e->nsrc_list, pmul);
+  (e->n_launch++, k_seed)<<<cdiv((size_t)U + 1, 256), 256, 0, e->st>>>(S, U, e->srclist.p, unit0, e->nranks, e->rank, e->nsrc_list, pmul, e->opt_sector_rot);
   static const int verbose = getenv("DRE_VERBOSE") ? atoi(getenv("DRE_VERBOSE")) : 0;
   for (;;) {
     const auto t_0 = std::chrono::steady_clock::now();
@@ -1824,6 +1824,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "stage_split") e->opt_stage_split = std::max(1, std::min(8, (int)value));
   else if (s == "ftab_kmax") e->opt_ftab_kmax = std::max(0, std::min(8, (int)value));
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
+  else if (s == "sector_rotation") e->opt_sector_rot = value != 0 ? 1 : 0;
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
   else if (s == "graphs") e->opt_graphs = value ? 1 : 0;

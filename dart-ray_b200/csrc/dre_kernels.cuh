@@ -409,7 +409,7 @@ __global__ void k_src_compact(const int* __restrict__ flag, const int* __restric
 }
 
 // seeds of a batch of units: create_high_ray_list ray_list.f90:71-106 (nside 2 pixel = sector)
-__global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int unit0, int stride, int rank_off, int nsrc, int pmul) {
+__global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int unit0, int stride, int rank_off, int nsrc, int pmul, int rot) {
   const DreDev& g = c_g;
   const DreUnits u = S.u;
   const DreList H = S.H[0], W = S.W[0];
@@ -424,7 +424,7 @@ __global__ void k_seed(DreStep S, int U, const int* __restrict__ srclist, int un
   const long long gq = (long long)rank_off + (long long)(unit0 + i) * stride;
   // the sector is rotated by the source position: with 48 % nranks == 0 a rank would otherwise trace the same sectors of every
   // source (the up-looking ones of a disc, say) and the ranks would finish a pass at different times
-  const int sector = (int)((gq % 48 + gq / 48) % 48);
+  const int sector = rot ? (int)((gq % 48 + gq / 48) % 48) : (int)(gq % 48);
   const int sord = (int)(((gq / 48) * (long long)pmul) % nsrc);
   const int gid = sord * 48 + sector;
   const int nc = srclist[sord];
