@@ -24,6 +24,29 @@ def my_units(n_sources: int, rank: int, nranks: int) -> np.ndarray:
     return np.arange(rank, total, nranks, dtype=np.int64)
 
 
+def source_multiplier(n_sources: int) -> int:
+    """Multiplier of the scrambled source order of the engine (dre_run_pass_resident): near nsrc / golden ratio, coprime to nsrc."""
+    import math
+    if n_sources <= 2:
+        return 1
+    m = max(1, int(n_sources * 0.6180339887))
+    while math.gcd(m, n_sources) != 1:
+        m += 1
+    return m
+
+
+def engine_units(n_sources: int, rank: int, nranks: int, sector_rotation: bool = True) -> np.ndarray:
+    """The units the ENGINE gives to `rank`, as global unit ids source_ordinal*48 + sector, in processing order (k_seed,
+    csrc/dre_kernels.cuh): position gq = rank + i*nranks; source ordinal = (gq // 48 * multiplier) mod nsrc; sector =
+    (gq % 48 + gq // 48) mod 48 -- rotated by the source position, so that a rank does not trace the same sectors of every
+    source when 48 % nranks == 0."""
+    gq = my_units(n_sources, rank, nranks)
+    pos = gq // 48
+    sord = (pos * source_multiplier(n_sources)) % max(int(n_sources), 1)
+    sector = (gq % 48 + pos) % 48 if sector_rotation else gq % 48
+    return sord * 48 + sector
+
+
 def unit_count(n_sources: int, rank: int, nranks: int) -> int:
     total = int(n_sources) * 48
     return (total - rank + nranks - 1) // nranks if total > rank else 0

@@ -116,3 +116,19 @@ def test_unit_sharding_covers_every_unit_once():
             assert [len(p) for p in parts] == [hostmpi.unit_count(nsrc, r, n) for r in range(n)]
             allu = np.sort(np.concatenate(parts))
             assert np.array_equal(allu, np.arange(nsrc * 48))
+
+
+def test_engine_unit_order_is_a_permutation_and_balances_sectors():
+    """The engine's own unit order (scrambled sources, sectors rotated by the source position; k_seed) restated on the host:
+    every (source, sector) pair exactly once over the ranks, and with 8 ranks every rank sees every sector equally often."""
+    sys.path.insert(0, ROOT)
+    from dartray_b200 import hostmpi
+    for nsrc in (1, 2, 7, 48, 231):
+        for n in (1, 2, 3, 8):
+            for rot in (True, False):
+                parts = [hostmpi.engine_units(nsrc, r, n, rot) for r in range(n)]
+                assert np.array_equal(np.sort(np.concatenate(parts)), np.arange(nsrc * 48))
+    per_rank = [np.bincount(hostmpi.engine_units(48 * 5, r, 8) % 48, minlength=48) for r in range(8)]
+    assert all((c == per_rank[0][0]).all() for c in per_rank)                 # rotated: 30 units of every sector on every rank
+    unrot = np.bincount(hostmpi.engine_units(48 * 5, 0, 8, False) % 48, minlength=48)
+    assert (unrot == 0).sum() == 42                                           # not rotated: rank 0 only ever sees 6 sectors
