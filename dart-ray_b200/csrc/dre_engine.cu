@@ -97,10 +97,11 @@ struct dre_engine {
   struct StepGraph { cudaGraphExec_t pre = nullptr, post = nullptr; std::vector<unsigned char> key; };
   StepGraph sgraph[2][2];   // [precalc / deposit][list parity]
   // options
-  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_coop_work = 131072, opt_det = 0, opt_sector_rot = 1;
+  int opt_hash = 0, opt_use_bulk = 1, opt_batch_units = 1 << 20, opt_warps = 16, opt_stage_split = 2, opt_ctas_per_sm = 1, opt_dir_kmax = 9, opt_ftab_kmax = 8, opt_chunk = 8, opt_ring_slots = 1, opt_graphs = 1, opt_cap0 = 0, opt_split = 1, opt_coop = 0, opt_coop_work = 131072, opt_det = 0, opt_sector_rot = 1, opt_blocking_sync = 0;
   // deterministic mode: exponents of the per-wavelength bounds (running maxima; scaspe | u | lum_lost | psel) and the constants
   std::vector<int> det_e; std::vector<double> h_qc; DBuf<double> qc;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_blk = nullptr;      // blocking-sync event of the per-step wait (option blocking_sync)
   double last_kernel_ms = 0;
   long long peak_entries = 0;
   double est_H[16] = {0}, est_W[16] = {0}, est_T[16] = {0};   // list entries / tasks per unit seen so far, by rt_type
@@ -198,6 +199,7 @@ int dre_create(dre_engine** out, int device, int rank, int nranks, const void* n
     e->sm_count = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CK(cudaEventCreate(&e->ev[i]));
+    CK(cudaEventCreateWithFlags(&e->ev_blk, cudaEventBlockingSync | cudaEventDisableTiming));
     e->counters.zero(16, e->st); e->errflag.zero(1, e->st); e->counter.zero(4, e->st); e->active.zero(2, e->st);
     e->ctl.zero(1, e->st);
     CK(cudaMallocHost((void**)&e->h_ctl, sizeof(DreCtl))); CK(cudaMallocHost((void**)&e->h_err, sizeof(int)));
@@ -229,6 +231,7 @@ void dre_destroy(dre_engine* e) {
   if (e->h_ctl) cudaFreeHost(e->h_ctl);
   if (e->h_err) cudaFreeHost(e->h_err);
   for (int i = 0; i < 4; i++) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+  if (e->ev_blk) cudaEventDestroy(e->ev_blk);
   for (int i = 0; i < 8; i++) if (e->marks[i]) cudaEventDestroy(e->marks[i]);
   if (e->st) cudaStreamDestroy(e->st);
   delete e;
@@ -913,7 +916,10 @@ BatchStats run_batch_mode(dre_engine* e, DreAccum A, int unit0, int U, int capH0
       e->n_launch += enqueue_post(e, S, cur, e->st, MODE == MODE_DEP && e->opt_split);
     }
     const auto t_1 = std::chrono::steady_clock::now();
-    CK(cudaStreamSynchronize(e->st));
+    // the one wait of a step.  Option blocking_sync: sleep on an event instead of spinning in cudaStreamSynchronize -- a thread
+    // that sleeps is not the one a busy host preempts (A/B in profiles/r02_sweeps.md)
+    if (e->opt_blocking_sync) { CK(cudaEventRecord(e->ev_blk, e->st)); CK(cudaEventSynchronize(e->ev_blk)); }
+    else CK(cudaStreamSynchronize(e->st));
     CK(cudaGetLastError());
     const DreCtl c = *e->h_ctl;
     if (verbose >= 2) {
@@ -1825,6 +1831,7 @@ int dre_set_option(dre_engine* e, const char* name, double value) {
   else if (s == "ftab_kmax") e->opt_ftab_kmax = std::max(0, std::min(8, (int)value));
   else if (s == "batch_units") e->opt_batch_units = std::max(48, (int)value);
   else if (s == "sector_rotation") e->opt_sector_rot = value != 0 ? 1 : 0;
+  else if (s == "blocking_sync") e->opt_blocking_sync = value != 0 ? 1 : 0;
   else if (s == "warps") e->opt_warps = std::max(1, std::min(32, (int)value));
   else if (s == "ctas_per_sm") e->opt_ctas_per_sm = std::max(1, std::min(8, (int)value));
   else if (s == "graphs") e->opt_graphs = value ? 1 : 0;
