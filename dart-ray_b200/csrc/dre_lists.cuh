@@ -152,7 +152,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_jobs(ScanJobs J, DreCtl* 
 // ---------------------------------------------------------------------------------------
 // step kernels
 // ---------------------------------------------------------------------------------------
-// Sibling table of a step: slots in use for a LOW list of nW entries (at most nW entries are extracted: load <= 1/2)
+// Sibling table of a step: slots in use for a LOW list of nW entries (at most nW entries are extracted: load <= 1/2).
+// 2 * nW + 64 stays far inside an int: the list capacity is bounded by the 32-GiB list budget (< 3e7 entries, dre_run_pass_resident).
 #define DRE_HEMPTY 0xffffffffffffffffull
 __device__ __forceinline__ int dre_hsize(const DreStep& S, int nW) { return min(S.hcap, 2 * nW + 64); }
 __device__ __forceinline__ unsigned dre_hslot(unsigned long long key, int hsize) {
